@@ -91,3 +91,30 @@ def hist_inputs(seed=601, n=4, h=32, w=64, c=19):
     gt[0, 0, :5] = -1
     pred = np.where(r.uniform(size=gt.shape) < 0.7, np.clip(gt, 0, c - 1), r.randint(0, c, size=gt.shape))
     return pred.astype(np.int64), gt
+
+
+# ---------------------------------------------------------------- SelfTrain.step() case
+WEAK_PARAMS = {"RandomSized": [[72, 96], [144, 192]],
+               "RandomCrop": [[4, 20], [68, 84], [8, 40], [136, 168]],
+               "RandomHorizontallyFlip": [True, False]}
+
+
+def full2weak_feat(seed=403):
+    return randn(seed, 2, 256, 20, 40)
+
+
+def step_inputs(seed=404):
+    """Inputs of the whole-step golden case, drawn in the order make_golden.py draws them."""
+    r = rs(seed)
+    src_img = r.standard_normal((2, 1, 64, 128)).astype(np.float32)
+    src_lab = r.randint(0, 13, size=(2, 64, 128)).astype(np.int64)
+    tgt_img = r.standard_normal((2, 1, 64, 128)).astype(np.float32)
+    tgt_full = r.standard_normal((2, 1, 80, 160)).astype(np.float32)
+    lp_soft = softmax_np(r.standard_normal((2, 13, 64, 128)).astype(np.float32) * 3, 1)
+    lp_hard = r.choice([5, 11, 12, 12, 12], size=(2, 1, 64, 128)).astype(np.int64)
+    return dict(src_img=src_img, src_lab=src_lab, tgt_img=tgt_img, tgt_full=tgt_full, lp_soft=lp_soft,
+                lp_hard=lp_hard)
+
+
+def cap_vectors(seed=303, m=3100, k=256):
+    return rs(seed).standard_normal((m, k)).astype(np.float32)

@@ -234,17 +234,12 @@ def golden_self_train(ref, out):
             return w_
 
         obj4.get_prototype_weight = spy_w
-        r = gi.rs(404)
-        src_img = torch.from_numpy(r.standard_normal((2, 1, 64, 128)).astype(np.float32))
-        src_lab = torch.from_numpy(r.randint(0, 13, size=(2, 64, 128)).astype(np.int64))
-        tgt_img = torch.from_numpy(r.standard_normal((2, 1, 64, 128)).astype(np.float32))
-        tgt_full = torch.from_numpy(r.standard_normal((2, 1, 80, 160)).astype(np.float32))
-        lp_soft = torch.from_numpy(gi.softmax_np(r.standard_normal((2, 13, 64, 128)).astype(np.float32) * 3, 1))
-        lp_hard = torch.from_numpy(r.choice([5, 11, 12, 12, 12], size=(2, 1, 64, 128)).astype(np.int64))
-        weak2 = {"RandomSized": [torch.tensor([72, 96]), torch.tensor([144, 192])],
-                 "RandomCrop": [torch.tensor([4, 20]), torch.tensor([68, 84]), torch.tensor([8, 40]),
-                                torch.tensor([136, 168])],
-                 "RandomHorizontallyFlip": torch.tensor([True, False])}
+        si = gi.step_inputs()
+        src_img, src_lab, tgt_img, tgt_full, lp_soft, lp_hard = (torch.from_numpy(si[k]) for k in (
+            "src_img", "src_lab", "tgt_img", "tgt_full", "lp_soft", "lp_hard"))
+        weak2 = {"RandomSized": [torch.tensor(v) for v in gi.WEAK_PARAMS["RandomSized"]],
+                 "RandomCrop": [torch.tensor(v) for v in gi.WEAK_PARAMS["RandomCrop"]],
+                 "RandomHorizontallyFlip": torch.tensor(gi.WEAK_PARAMS["RandomHorizontallyFlip"])}
         loss_t, loss_s = obj4.step(src_img, src_lab, tgt_img, tgt_full, lp_soft, lp_hard, weak2, None)
         out["step_%s_loss_target" % tag] = loss_t.detach().numpy()
         out["step_%s_loss_source" % tag] = loss_s.detach().numpy()
