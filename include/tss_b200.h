@@ -1,0 +1,218 @@
+/*
+ * tss_b200.h -- C ABI of the B200-native self-training label path.
+ *
+ * The reference (MuliangDu-sudo/thermal-semantic-segmentation @ 8a37af1) is pure
+ * Python and has no FFI of its own; the boundary it offers is a set of Python
+ * callables on torch tensors / numpy arrays.  Each entry
+ * point below replaces the arithmetic of the reference lines cited beside it and is
+ * what a ctypes binding on the reference side binds.
+ *
+ * Conventions (all entry points):
+ *   - every pointer is a raw DEVICE pointer unless its name ends in _host;
+ *   - tensors are dense, row-major ("NCHW contiguous" as the reference keeps them);
+ *   - the caller owns all memory: the library never allocates, frees or synchronises;
+ *     scratch space is passed in, its size comes from the matching *_workspace_bytes;
+ *   - work is enqueued on `stream` (a cudaStream_t passed as void*) and returns at once;
+ *   - return value: 0 on success, a TSS_E_* code for a rejected argument, or
+ *     1000 + cudaError_t for a CUDA failure; tss_last_error_string() explains it
+ *     (thread-local).  No C++ exceptions cross this boundary, no global mutable state.
+ *   - num_classes is limited to TSS_MAX_CLASSES.
+ */
+#ifndef TSS_B200_H_
+#define TSS_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TSS_VERSION 100
+#define TSS_MAX_CLASSES 32
+
+/* status codes */
+#define TSS_OK 0
+#define TSS_E_ARG 1        /* null pointer / non-positive extent / bad enum */
+#define TSS_E_CLASSES 2    /* num_classes outside [1, TSS_MAX_CLASSES] or unsupported by this kernel */
+#define TSS_E_ALIGN 3      /* pointer alignment requirement not met */
+#define TSS_E_WORKSPACE 4  /* workspace too small */
+#define TSS_E_CUDA 1000    /* 1000 + cudaError_t */
+
+/* integer element types of label maps */
+#define TSS_U8 0
+#define TSS_I32 1
+#define TSS_I64 2
+
+int tss_version(void);
+const char* tss_last_error_string(void);
+/* number of kernels this library has launched in the calling process (bench "gpu_launches") */
+uint64_t tss_launch_count(void);
+/* tuning hooks (benchmarks only): set a kernel variant, return the previous one; -1 = query */
+int tss_tune_confusion_variant(int v);   /* 0 shared-memory atomics, 1 packed private counters (uint8) */
+int tss_tune_pl_force_tile(int v);       /* 1 = use the tiled kernel even when H==h and W==w */
+
+/* ---------------------------------------------------------------------------------------------
+ * A14  confusion matrix -- replaces utils/eval_tools.py:4-9 (_fast_hist) and the per-image
+ * accumulation of evaluate() :49-51.  hist[C*C] (int64, rows = ground truth, cols = prediction) is
+ * ACCUMULATED (+=).  A pixel counts iff 0 <= gt < C.  The reference does not range-check pred: a
+ * counted pixel with pred outside [0, C) makes np.bincount / reshape raise (or silently alias another
+ * bin); here such pixels are left out of hist and counted in *bad_keys (uint64, accumulated; may be
+ * NULL), and the host mirror raises ValueError when it is non-zero.
+ * pred/gt: n elements of `dtype` (TSS_U8 / TSS_I32 / TSS_I64). */
+int tss_confusion(const void* pred, const void* gt, int dtype, int64_t n, int num_classes,
+                  int64_t* hist, uint64_t* bad_keys, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * A2   low-resolution softmax -- generate_pseudo_label.py:75 (soft branch) and the first softmax
+ * of :82-83.  logits/probs: [N, C, P] fp32 (P = h*w). */
+int tss_softmax_nchw(const float* logits, float* probs, int64_t n_img, int num_classes, int64_t plane,
+                     void* stream);
+
+/* A1-A4 fused pseudo-label kernel.  One pass: bilinear upsample (align_corners=True) of the C planes
+ * of `src` [N,C,h,w] to [H,W] -> per-pixel reduction over classes -> storage casts -> threshold.
+ *   mode TSS_PL_UP_SOFTMAX       src = logits;  softmax AFTER upsampling, then max/argmax
+ *                                (self_training.py:53-55 order + generate_pseudo_label.py:85; with
+ *                                 H==h, W==w this is exactly the no-flip hard branch :85)
+ *   mode TSS_PL_UP_ARGMAX        src = logits;  argmax only, conf = max logit
+ *                                (segmentation_evaluate.py:38-42)
+ *   mode TSS_PL_PROB_UP          src = probabilities; conf = max, label = argmax
+ *   mode TSS_PL_PROB_UP_SOFTMAX  src = probabilities; a second softmax over the upsampled
+ *                                probabilities, then max (generate_pseudo_label.py:82-85 as committed)
+ *   flip TSS_FLIP_NONE | TSS_FLIP_CLASS (torch.fliplr on NCHW = reversed class axis, what
+ *        generate_pseudo_label.py:10,84 really does) | TSS_FLIP_WIDTH (the intended mirror):
+ *        out = (up(src) + flip(up(src_flip))) / 2 before the reduction (:84).  src_flip may be NULL
+ *        iff flip == TSS_FLIP_NONE.
+ * Outputs (each may be NULL): label_out [N,H,W] uint8 (:91), conf16_out [N,H,W] IEEE fp16 bits,
+ * round-to-nearest-even (:94), conf32_out fp32, label_thr_out [N,H,W] uint8 = the threshold block
+ * data/freiburg_dataset.py:115-123 applied to (label, fp16 conf): ignore_index where
+ * fp16(conf) <= fp16(thr_host[label]) or keep_host[label] == 0.  thr_host / keep_host: HOST arrays of
+ * num_classes entries (NULL = no threshold / keep all). */
+#define TSS_PL_UP_SOFTMAX 0
+#define TSS_PL_UP_ARGMAX 1
+#define TSS_PL_PROB_UP 2
+#define TSS_PL_PROB_UP_SOFTMAX 3
+#define TSS_FLIP_NONE 0
+#define TSS_FLIP_CLASS 1
+#define TSS_FLIP_WIDTH 2
+int tss_pseudo_label(const float* src, const float* src_flip, int64_t n_img, int num_classes, int h, int w,
+                     int H, int W, int mode, int flip, uint8_t* label_out, uint16_t* conf16_out,
+                     float* conf32_out, uint8_t* label_thr_out, const float* thr_host,
+                     const uint8_t* keep_host, int ignore_index, void* stream);
+
+/* A1   plain bilinear upsample, align_corners=True: self_training.py:62,69-77 (soft labels, feat, out).
+ * src [planes, h, w] -> dst [planes, H, W] fp32. */
+int tss_upsample_bilinear(const float* src, float* dst, int64_t planes, int h, int w, int H, int W,
+                          void* stream);
+
+/* A4   threshold block on STORED labels: data/freiburg_dataset.py:115-123.  label_in uint8 [n],
+ * conf16 fp16 bits [n] -> label_out uint8 [n]. */
+int tss_threshold_labels(const uint8_t* label_in, const uint16_t* conf16, int64_t n, int num_classes,
+                         const float* thr_host, const uint8_t* keep_host, int ignore_index,
+                         uint8_t* label_out, void* stream);
+
+/* A4   nearest-neighbour gather used for PIL's Image.resize(NEAREST) (data/freiburg_dataset.py:124)
+ * and F.interpolate(mode='nearest') (self_training.py:103): dst[p, y, x] = src[p, ytab[y], xtab[x]].
+ * ytab/xtab are DEVICE int32 tables the host mirror fills with the library's exact index rule. */
+int tss_gather_nearest_u8(const uint8_t* src, uint8_t* dst, int64_t planes, int h, int w, int H, int W,
+                          const int32_t* ytab, const int32_t* xtab, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * A5   per-(image, class) segmented sum of features by label -- replaces the (n, t) double loop of
+ * Class_Features.calculate_mean_vector (cal_prototype.py:118-144) and
+ * SelfTrain.calculate_mean_vector (self_training.py:176-202).
+ *
+ * Step 1, tss_proto_labels: logits [N,C,P] -> per pixel argmax (ties -> lowest class, as torch),
+ *   optionally intersected with labels_val [N,P] fp32 (values >= C go to `overflow_channel`,
+ *   process_label :146-151 / :204-209) and gated by conf >= conf_thresh (use_conf_gate != 0,
+ *   self_training.py:180-181).  Writes seg_label [N,P] uint8 (class whose sum the pixel joins, 255 =
+ *   none), count_all [N,C] int32 (ungated one-hot count: the "< 10" rule :135 / :196) and count_gated
+ *   [N,C] int32 (the divisor :128,:140 / :189,:198), plus tile records for step 2 in `records`
+ *   (tss_proto_records_bytes(N, P) bytes): per tile of TSS_PROTO_TILE pixels the pixel offsets sorted
+ *   by class and the class segment boundaries.
+ * Step 2, tss_proto_accumulate: feat [N,K,P] fp32 (K % 32 == 0) streamed once through shared memory
+ *   (bulk async copies + mbarrier ring); sums [N,C,K] fp32 are zeroed by the call, then accumulated.
+ * Step 3, tss_proto_finalize: vectors [N,C,K] = sums / count_gated; valid [N,C] uint8 =
+ *   count_gated > 0 && count_all >= 10 (the two `continue`s); vector_sum [N,C] fp32 (for the
+ *   `vector.sum() == 0` skip of update_objective_SingleVector :154 / :212). */
+#define TSS_PROTO_TILE 512
+size_t tss_proto_records_bytes(int64_t n_img, int64_t plane);
+int tss_proto_labels(const float* logits, const float* labels_val, int64_t n_img, int num_classes,
+                     int64_t plane, int overflow_channel, int use_conf_gate, float conf_thresh,
+                     uint8_t* seg_label, int32_t* count_all, int32_t* count_gated, void* records,
+                     void* stream);
+int tss_proto_accumulate(const float* feat, const void* records, int64_t n_img, int64_t channels,
+                         int64_t plane, int num_classes, float* sums, void* stream);
+int tss_proto_finalize(const float* sums, const int32_t* count_all, const int32_t* count_gated,
+                       int64_t n_img, int num_classes, int64_t channels, int min_pixels, float* vectors,
+                       uint8_t* valid, float* vector_sum, void* stream);
+
+/* A6   sequential prototype update -- update_objective_SingleVector (cal_prototype.py:153-169,
+ * self_training.py:211-227) applied to the vectors of one batch in the reference's list order
+ * (image-major, then class).  Classes are independent, so one thread block walks each class's images
+ * in order with the reference's own fp32 operation sequence.  protos [C,K] and num [C] fp32 are
+ * updated in place.  mode: TSS_UPDATE_MEAN | TSS_UPDATE_MOVING_AVERAGE; start_mean != 0 forces 'mean'
+ * while num < 100; cap = 3000 in the reference. */
+#define TSS_UPDATE_MEAN 0
+#define TSS_UPDATE_MOVING_AVERAGE 1
+int tss_proto_update(float* protos, float* num, const float* vectors, const uint8_t* valid,
+                     const float* vector_sum, int64_t n_img, int num_classes, int64_t channels, int mode,
+                     int start_mean, double momentum, double cap, void* stream);
+/* Sharded form: the same update expressed through its closed-form weights so
+ * that ranks can combine with one all-reduce.  For every class, with the contributing vectors of THIS
+ * rank occupying positions [first_index[c], first_index[c] + m_local) of the global order of
+ * total[c] contributions: partial[c,:] = sum_j w_j * v_j (fp32 out, fp64 weights), and scale0[c] = the
+ * factor the old prototype keeps.  The caller all-reduces partial, then
+ * protos = scale0 * protos + partial, num = num_after.  contrib_count [C] int32 receives m_local
+ * when first_index == NULL (counting pass). */
+int tss_proto_update_partial(const float* vectors, const uint8_t* valid, const float* vector_sum,
+                             int64_t n_img, int num_classes, int64_t channels, int mode, int start_mean,
+                             double momentum, double cap, const float* num_before,
+                             const int32_t* first_index, const int32_t* total, int32_t* contrib_count,
+                             float* partial, float* scale0, float* num_after, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * A7/A8/A10  feature-to-prototype distance, soft weights, label rectification -- replaces
+ * SelfTrain.feat_prototype_distance (self_training.py:160-165), get_prototype_weight :139-142 and
+ * the rectify block :106-112.  feat [N,K,P] fp32 (K % 32 == 0), protos [C,K] fp32.
+ *   dist_out   [N,C,P] fp32 or NULL : ||proto_c - feat||_2 (direct difference form, fp32)
+ *   weight_out [N,C,P] fp32 or NULL : softmax_c(-(d - min_c d) * temperature)
+ *   if soft != NULL: rect = weight * soft [N,C,P]; label = argmax_c rect; label = ignore_index where
+ *   max_c(rect / sum_c rect) < train_thred; label = hard[px] where hard != NULL and
+ *   hard[px] != ignore_index.  hard: [N,P] of hard_dtype; label_out [N,P] int64. */
+int tss_proto_distance(const float* feat, const float* protos, int64_t n_img, int64_t channels,
+                       int64_t plane, int num_classes, float temperature, float* dist_out,
+                       float* weight_out, const float* soft, const void* hard, int hard_dtype,
+                       float train_thred, int ignore_index, int64_t* label_out, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * A11/A12  cross-entropy with ignore_index and reverse cross-entropy -- nn.CrossEntropyLoss
+ * (self_training.py:27,57,114; utils/loss.py:145) and SelfTrain.rce (self_training.py:167-174).
+ * logits [N,C,P] fp32, target [N,P] (target_dtype).  out_host-independent: results land in `out`
+ * (DEVICE, 4 doubles): {sum_px ce, sum_px rce, valid pixel count, pixels whose label is outside
+ * [0, C] and != ignore (the reference raises there)}.  The host mirror forms
+ * ce = out[0]/out[2], rce = out[1]/(out[2] + 1e-6).  workspace: tss_loss_workspace_bytes(). */
+size_t tss_loss_workspace_bytes(void);
+int tss_ce_rce_fwd(const float* logits, const void* target, int target_dtype, int64_t n_img,
+                   int num_classes, int64_t plane, int ignore_index, int with_rce, double* out,
+                   void* workspace, void* stream);
+/* grad[N,C,P] = ce_scale * d(sum ce)/dx + rce_scale * d(sum rce)/dx, scales read from the DEVICE
+ * array scales[2] (so that no host sync is needed between forward and backward). */
+int tss_ce_rce_bwd(const float* logits, const void* target, int target_dtype, int64_t n_img,
+                   int num_classes, int64_t plane, int ignore_index, const float* scales, float* grad,
+                   void* stream);
+
+/* A13  focal loss -- FocalLoss.forward (utils/loss.py:164-184): loss_px = -(1-pt)^gamma * alpha[y] *
+ * log pt with pt detached; no ignore handling.  out (DEVICE, 2 doubles) = {sum loss, pixel count}.
+ * alpha: DEVICE [C] fp32 or NULL.  bwd: grad = scale[0] * d(sum loss)/dx. */
+int tss_focal_fwd(const float* logits, const void* target, int target_dtype, int64_t n_img,
+                  int num_classes, int64_t plane, float gamma, const float* alpha, double* out,
+                  void* workspace, void* stream);
+int tss_focal_bwd(const float* logits, const void* target, int target_dtype, int64_t n_img,
+                  int num_classes, int64_t plane, float gamma, const float* alpha, const float* scale,
+                  float* grad, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TSS_B200_H_ */

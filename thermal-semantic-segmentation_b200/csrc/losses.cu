@@ -1,0 +1,298 @@
+// A11-A13: cross-entropy with ignore_index, reverse cross-entropy, focal loss -- forward sums and
+// input gradients (self_training.py:27,114-118,167-174; utils/loss.py:142-184).
+// HBM-bound: each logit is read once (4C + label bytes per pixel), gradients written once.
+// Per-pixel terms are accumulated in fp64 per thread -> per CTA -> a fixed-order final reduction, so the
+// loss is bit-reproducible run to run.
+#include "common.cuh"
+
+namespace tss {
+
+constexpr int kLossThreads = 256;
+constexpr int kLossMaxBlocks = kNumSMs * 8;
+
+template <int CT>
+struct PixelSoftmax {
+    float p[CT];   // exp(x - max), later normalised on demand
+    float m, s;
+    __device__ __forceinline__ void load(const float* x, int C, int64_t plane) {
+        m = -INFINITY;
+#pragma unroll
+        for (int c = 0; c < CT; ++c)
+            if (c < C) {
+                p[c] = ldg_stream_f(x + c * plane);
+                m = fmaxf(m, p[c]);
+            }
+        s = 0.f;
+#pragma unroll
+        for (int c = 0; c < CT; ++c)
+            if (c < C) {
+                p[c] = expf(p[c] - m);
+                s += p[c];
+            }
+    }
+    // log-softmax of class y given the raw logit xy
+    __device__ __forceinline__ float logp(float xy) const { return (xy - m) - logf(s); }
+};
+
+template <typename T>
+__device__ __forceinline__ long long target_at(const void* t, int64_t i) { return load_label<T>(t, i); }
+
+__device__ __forceinline__ void block_reduce4(double (&v)[4], double* out4) {
+    __shared__ double sh[4][kLossThreads / 32];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) v[i] = warp_sum_d(v[i]);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (lane == 0)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) sh[i][warp] = v[i];
+    __syncthreads();
+    if (threadIdx.x < 4) {
+        double t = 0.0;
+        for (int w = 0; w < kLossThreads / 32; ++w) t += sh[threadIdx.x][w];
+        out4[threadIdx.x] = t;
+    }
+}
+
+__global__ void __launch_bounds__(256) reduce_partials_kernel(const double* __restrict__ part, int blocks, double* __restrict__ out) {
+    __shared__ double sh[4][8];
+    double v[4] = {0, 0, 0, 0};
+    for (int b = threadIdx.x; b < blocks; b += 256)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) v[i] += part[b * 4 + i];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) v[i] = warp_sum_d(v[i]);
+    if ((threadIdx.x & 31) == 0)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) sh[i][threadIdx.x >> 5] = v[i];
+    __syncthreads();
+    if (threadIdx.x < 4) {
+        double t = 0.0;
+        for (int w = 0; w < 8; ++w) t += sh[threadIdx.x][w];
+        out[threadIdx.x] = t;
+    }
+}
+
+// -log(clamp(0, 1e-4, 1)) in fp32, as torch.log(torch.clamp(one_hot, min=1e-4)) yields off the label
+__device__ __forceinline__ float rce_log_floor() { return -logf(1e-4f); }
+
+template <int CT, typename T>
+__global__ void __launch_bounds__(kLossThreads)
+ce_rce_fwd_kernel(const float* __restrict__ logits, const void* __restrict__ target, int64_t N, int C, int64_t P,
+                  int ignore, int with_rce, double* __restrict__ part) {
+    double acc[4] = {0, 0, 0, 0};
+    const int64_t total = N * P;
+    const float A = rce_log_floor();
+    for (int64_t i = blockIdx.x * static_cast<int64_t>(kLossThreads) + threadIdx.x; i < total;
+         i += static_cast<int64_t>(gridDim.x) * kLossThreads) {
+        const long long y = target_at<T>(target, i);
+        if (y == ignore) continue;
+        if (y < 0 || y >= C) { acc[3] += 1.0; continue; }
+        const int64_t n = i / P, p = i - n * P;
+        const float* x = logits + n * C * P + p;
+        PixelSoftmax<CT> sm;
+        sm.load(x, C, P);
+        // -log_softmax[y] = log(s) - (x_y - m); x_y re-read (L1 hit) because p[] already holds the exponentials
+        acc[0] += static_cast<double>(logf(sm.s) - (__ldg(x + y * P) - sm.m));
+        acc[2] += 1.0;
+        if (with_rce) {
+            float r = 0.f;
+#pragma unroll
+            for (int c = 0; c < CT; ++c)
+                if (c < C && c != static_cast<int>(y)) r += fminf(fmaxf(__fdiv_rn(sm.p[c], sm.s), 1e-7f), 1.0f);
+            acc[1] += static_cast<double>(A * r);
+        }
+    }
+    block_reduce4(acc, part + blockIdx.x * 4);
+}
+
+template <int CT, typename T>
+__global__ void __launch_bounds__(kLossThreads)
+ce_rce_bwd_kernel(const float* __restrict__ logits, const void* __restrict__ target, int64_t N, int C, int64_t P,
+                  int ignore, const float* __restrict__ scales, float* __restrict__ grad) {
+    const float ce_scale = scales[0], rce_scale = scales[1];
+    const float A = rce_log_floor();
+    const int64_t total = N * P;
+    for (int64_t i = blockIdx.x * static_cast<int64_t>(kLossThreads) + threadIdx.x; i < total;
+         i += static_cast<int64_t>(gridDim.x) * kLossThreads) {
+        const long long y = target_at<T>(target, i);
+        const int64_t n = i / P, p = i - n * P;
+        float* g = grad + n * C * P + p;
+        if (y == ignore || y < 0 || y >= C) {
+#pragma unroll
+            for (int c = 0; c < CT; ++c)
+                if (c < C) g[c * P] = 0.f;
+            continue;
+        }
+        PixelSoftmax<CT> sm;
+        sm.load(logits + n * C * P + p, C, P);
+        float S = 0.f;  // sum over j != y of [1e-7 <= p_j <= 1] p_j  (clamp passes gradient inside its range)
+#pragma unroll
+        for (int c = 0; c < CT; ++c)
+            if (c < C) {
+                sm.p[c] = __fdiv_rn(sm.p[c], sm.s);
+                if (c != static_cast<int>(y) && sm.p[c] >= 1e-7f && sm.p[c] <= 1.0f) S += sm.p[c];
+            }
+        const float rs = rce_scale * A;
+#pragma unroll
+        for (int c = 0; c < CT; ++c)
+            if (c < C) {
+                const float pc = sm.p[c];
+                const bool is_y = c == static_cast<int>(y);
+                const float gate = (!is_y && pc >= 1e-7f && pc <= 1.0f) ? 1.f : 0.f;
+                g[c * P] = ce_scale * (pc - (is_y ? 1.f : 0.f)) + rs * pc * (gate - S);
+            }
+    }
+}
+
+__device__ __forceinline__ float focal_weight(float pt, float gamma) {
+    const float q = 1.0f - pt;
+    if (gamma == 0.f) return 1.0f;
+    if (gamma == 1.f) return q;
+    if (gamma == 2.f) return q * q;
+    return powf(q, gamma);
+}
+
+template <int CT, typename T>
+__global__ void __launch_bounds__(kLossThreads)
+focal_fwd_kernel(const float* __restrict__ logits, const void* __restrict__ target, int64_t N, int C, int64_t P,
+                 float gamma, const float* __restrict__ alpha, double* __restrict__ part) {
+    double acc[4] = {0, 0, 0, 0};
+    const int64_t total = N * P;
+    for (int64_t i = blockIdx.x * static_cast<int64_t>(kLossThreads) + threadIdx.x; i < total;
+         i += static_cast<int64_t>(gridDim.x) * kLossThreads) {
+        const long long y = target_at<T>(target, i);
+        if (y < 0 || y >= C) { acc[3] += 1.0; continue; }
+        const int64_t n = i / P, p = i - n * P;
+        PixelSoftmax<CT> sm;
+        sm.load(logits + n * C * P + p, C, P);
+        float logpt = (__ldg(logits + n * C * P + p + y * P) - sm.m) - logf(sm.s);
+        const float pt = expf(logpt);
+        if (alpha) logpt *= alpha[y];
+        acc[0] += static_cast<double>(-1.0f * focal_weight(pt, gamma) * logpt);
+        acc[1] += 1.0;
+    }
+    block_reduce4(acc, part + blockIdx.x * 4);
+}
+
+template <int CT, typename T>
+__global__ void __launch_bounds__(kLossThreads)
+focal_bwd_kernel(const float* __restrict__ logits, const void* __restrict__ target, int64_t N, int C, int64_t P,
+                 float gamma, const float* __restrict__ alpha, const float* __restrict__ scale, float* __restrict__ grad) {
+    const float sc = scale[0];
+    const int64_t total = N * P;
+    for (int64_t i = blockIdx.x * static_cast<int64_t>(kLossThreads) + threadIdx.x; i < total;
+         i += static_cast<int64_t>(gridDim.x) * kLossThreads) {
+        const long long y = target_at<T>(target, i);
+        const int64_t n = i / P, p = i - n * P;
+        float* g = grad + n * C * P + p;
+        if (y < 0 || y >= C) {
+#pragma unroll
+            for (int c = 0; c < CT; ++c)
+                if (c < C) g[c * P] = 0.f;
+            continue;
+        }
+        PixelSoftmax<CT> sm;
+        sm.load(logits + n * C * P + p, C, P);
+        const float pt = expf((__ldg(logits + n * C * P + p + y * P) - sm.m) - logf(sm.s));
+        // pt is detached in the reference (logpt.data.exp()): d loss / d x_c = -w * alpha_y * (delta_cy - p_c)
+        const float coef = -sc * focal_weight(pt, gamma) * (alpha ? alpha[y] : 1.0f);
+#pragma unroll
+        for (int c = 0; c < CT; ++c)
+            if (c < C) g[c * P] = coef * ((c == static_cast<int>(y) ? 1.f : 0.f) - __fdiv_rn(sm.p[c], sm.s));
+    }
+}
+
+static int loss_grid(int64_t total) {
+    int64_t b = (total + kLossThreads - 1) / kLossThreads;
+    if (b > kLossMaxBlocks) b = kLossMaxBlocks;
+    return static_cast<int>(b < 1 ? 1 : b);
+}
+
+#define TSS_DISPATCH_CT_T(KERNEL, C, DT, GRID, ST, ...)                                                       \
+    do {                                                                                                      \
+        if ((C) <= 13) {                                                                                      \
+            if ((DT) == TSS_U8) KERNEL<13, uint8_t><<<GRID, kLossThreads, 0, ST>>>(__VA_ARGS__);              \
+            else if ((DT) == TSS_I32) KERNEL<13, int32_t><<<GRID, kLossThreads, 0, ST>>>(__VA_ARGS__);        \
+            else KERNEL<13, int64_t><<<GRID, kLossThreads, 0, ST>>>(__VA_ARGS__);                             \
+        } else if ((C) <= 19) {                                                                               \
+            if ((DT) == TSS_U8) KERNEL<19, uint8_t><<<GRID, kLossThreads, 0, ST>>>(__VA_ARGS__);              \
+            else if ((DT) == TSS_I32) KERNEL<19, int32_t><<<GRID, kLossThreads, 0, ST>>>(__VA_ARGS__);        \
+            else KERNEL<19, int64_t><<<GRID, kLossThreads, 0, ST>>>(__VA_ARGS__);                             \
+        } else {                                                                                              \
+            if ((DT) == TSS_U8) KERNEL<TSS_MAX_CLASSES, uint8_t><<<GRID, kLossThreads, 0, ST>>>(__VA_ARGS__); \
+            else if ((DT) == TSS_I32) KERNEL<TSS_MAX_CLASSES, int32_t><<<GRID, kLossThreads, 0, ST>>>(__VA_ARGS__); \
+            else KERNEL<TSS_MAX_CLASSES, int64_t><<<GRID, kLossThreads, 0, ST>>>(__VA_ARGS__);                \
+        }                                                                                                     \
+    } while (0)
+
+static int check_loss_args(const char* who, const void* logits, const void* target, int dt, int64_t N, int C, int64_t P) {
+    TSS_REQUIRE(logits && target, TSS_E_ARG, "%s: null pointer", who);
+    TSS_REQUIRE(N >= 0 && P > 0, TSS_E_ARG, "%s: bad extents", who);
+    TSS_REQUIRE(C >= 1 && C <= TSS_MAX_CLASSES, TSS_E_CLASSES, "%s: num_classes %d", who, C);
+    TSS_REQUIRE(dt == TSS_U8 || dt == TSS_I32 || dt == TSS_I64, TSS_E_ARG, "%s: bad target dtype %d", who, dt);
+    return TSS_OK;
+}
+
+}  // namespace tss
+
+extern "C" size_t tss_loss_workspace_bytes(void) { return static_cast<size_t>(tss::kLossMaxBlocks) * 4 * sizeof(double); }
+
+extern "C" int tss_ce_rce_fwd(const float* logits, const void* target, int target_dtype, int64_t n_img, int num_classes,
+                              int64_t plane, int ignore_index, int with_rce, double* out, void* workspace, void* stream) {
+    using namespace tss;
+    if (int r = check_loss_args("tss_ce_rce_fwd", logits, target, target_dtype, n_img, num_classes, plane)) return r;
+    TSS_REQUIRE(out && workspace, TSS_E_ARG, "tss_ce_rce_fwd: null out/workspace");
+    cudaStream_t st = as_stream(stream);
+    const int grid = loss_grid(n_img * plane);
+    double* part = static_cast<double*>(workspace);
+    TSS_DISPATCH_CT_T(ce_rce_fwd_kernel, num_classes, target_dtype, grid, st, logits, target, n_img, num_classes, plane,
+                      ignore_index, with_rce, part);
+    TSS_LAUNCH_CHECK("tss_ce_rce_fwd");
+    reduce_partials_kernel<<<1, 256, 0, st>>>(part, grid, out);
+    TSS_LAUNCH_CHECK("tss_ce_rce_fwd(reduce)");
+    return TSS_OK;
+}
+
+extern "C" int tss_ce_rce_bwd(const float* logits, const void* target, int target_dtype, int64_t n_img, int num_classes,
+                              int64_t plane, int ignore_index, const float* scales, float* grad, void* stream) {
+    using namespace tss;
+    if (int r = check_loss_args("tss_ce_rce_bwd", logits, target, target_dtype, n_img, num_classes, plane)) return r;
+    TSS_REQUIRE(scales && grad, TSS_E_ARG, "tss_ce_rce_bwd: null scales/grad");
+    if (n_img == 0) return TSS_OK;
+    cudaStream_t st = as_stream(stream);
+    const int grid = loss_grid(n_img * plane);
+    TSS_DISPATCH_CT_T(ce_rce_bwd_kernel, num_classes, target_dtype, grid, st, logits, target, n_img, num_classes, plane,
+                      ignore_index, scales, grad);
+    TSS_LAUNCH_CHECK("tss_ce_rce_bwd");
+    return TSS_OK;
+}
+
+extern "C" int tss_focal_fwd(const float* logits, const void* target, int target_dtype, int64_t n_img, int num_classes,
+                             int64_t plane, float gamma, const float* alpha, double* out, void* workspace, void* stream) {
+    using namespace tss;
+    if (int r = check_loss_args("tss_focal_fwd", logits, target, target_dtype, n_img, num_classes, plane)) return r;
+    TSS_REQUIRE(out && workspace, TSS_E_ARG, "tss_focal_fwd: null out/workspace");
+    cudaStream_t st = as_stream(stream);
+    const int grid = loss_grid(n_img * plane);
+    double* part = static_cast<double*>(workspace);
+    TSS_DISPATCH_CT_T(focal_fwd_kernel, num_classes, target_dtype, grid, st, logits, target, n_img, num_classes, plane, gamma,
+                      alpha, part);
+    TSS_LAUNCH_CHECK("tss_focal_fwd");
+    reduce_partials_kernel<<<1, 256, 0, st>>>(part, grid, out);
+    TSS_LAUNCH_CHECK("tss_focal_fwd(reduce)");
+    return TSS_OK;
+}
+
+extern "C" int tss_focal_bwd(const float* logits, const void* target, int target_dtype, int64_t n_img, int num_classes,
+                             int64_t plane, float gamma, const float* alpha, const float* scale, float* grad, void* stream) {
+    using namespace tss;
+    if (int r = check_loss_args("tss_focal_bwd", logits, target, target_dtype, n_img, num_classes, plane)) return r;
+    TSS_REQUIRE(scale && grad, TSS_E_ARG, "tss_focal_bwd: null scale/grad");
+    if (n_img == 0) return TSS_OK;
+    cudaStream_t st = as_stream(stream);
+    const int grid = loss_grid(n_img * plane);
+    TSS_DISPATCH_CT_T(focal_bwd_kernel, num_classes, target_dtype, grid, st, logits, target, n_img, num_classes, plane, gamma,
+                      alpha, scale, grad);
+    TSS_LAUNCH_CHECK("tss_focal_bwd");
+    return TSS_OK;
+}

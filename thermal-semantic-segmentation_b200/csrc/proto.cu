@@ -1,0 +1,484 @@
+// A5/A6: per-(image, class) segmented sums of the 1/8-stride features by argmax label, and the
+// prototype update (cal_prototype.py:118-169, self_training.py:176-227).
+//
+// Data layout in HBM: feat [N, K, P] fp32 exactly as the network leaves it (P = h*w is ODD for every
+// DeepLab shape, so channel rows are only 4-byte aligned).  The reference re-reads feat up to C times
+// and materialises a [K,h,w] product per (image, class); here feat is streamed ONCE:
+//
+//   proto_label_kernel   logits -> argmax label per pixel, class counts, and per 512-pixel tile a
+//                        class-sorted list of pixel offsets + class segment boundaries ("records").
+//   proto_accum_kernel   persistent, one CTA per SM.  A producer warp stages tiles of 32 channel rows x
+//                        512 pixels into shared memory with 1-D bulk async copies (TMA engine, UBLKCP)
+//                        completing on an mbarrier ring; every lane copies the 16-byte-aligned superset
+//                        of its (misaligned) row, rows are skewed so that "lane = channel" reads are
+//                        bank-conflict free.  Eight consumer warps walk the tile's pixels in class-sorted
+//                        order: the pixel index is warp-uniform, each lane adds its channel's value to
+//                        ONE register accumulator per class segment -- no atomics, no select chains.
+//                        Global fp32 atomics happen once per class per (image, channel group) per CTA.
+#include "common.cuh"
+
+namespace tss {
+
+constexpr int kPT = TSS_PROTO_TILE;        // pixels per tile
+constexpr int kKT = 32;                    // channels per tile: one per lane
+constexpr int kConsumers = 8;              // consumer warps
+constexpr int kAccThreads = (kConsumers + 1) * 32;
+constexpr int kRowStride = kPT + 36;       // floats; room for head misalignment (3) + 16 B round-up (3) + skew (28)
+constexpr int kRecBytes = kPT * 2 + 128;   // uint16 idx[kPT] + uint16 off[64]
+constexpr int kStages = 3;
+
+static_assert(kRowStride % 4 == 0, "rows must start 16-byte aligned");
+static_assert(kRecBytes % 16 == 0, "records are bulk-copied");
+
+struct TileRecord {
+    uint16_t idx[kPT];
+    uint16_t off[64];
+};
+
+// ------------------------------------------------------------------------------------------------
+template <int CT>
+__global__ void __launch_bounds__(256)
+proto_label_kernel(const float* __restrict__ logits, const float* __restrict__ labels_val, int C, int64_t P,
+                   int overflow, int use_gate, float thresh, uint8_t* __restrict__ seg_label,
+                   int32_t* __restrict__ cnt_all, int32_t* __restrict__ cnt_gated, TileRecord* __restrict__ records) {
+    __shared__ int wcnt[16][TSS_MAX_CLASSES + 1];
+    __shared__ int call[TSS_MAX_CLASSES], cgate[TSS_MAX_CLASSES];
+    __shared__ int boff[TSS_MAX_CLASSES + 2];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int64_t tile = blockIdx.x, n = blockIdx.y;
+    const int64_t tiles = gridDim.x;
+    const int64_t p0 = tile * kPT;
+    for (int i = tid; i < 16 * (TSS_MAX_CLASSES + 1); i += 256) (&wcnt[0][0])[i] = 0;
+    if (tid < TSS_MAX_CLASSES) { call[tid] = 0; cgate[tid] = 0; }
+    __syncthreads();
+    int bucket[2], rank[2];
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+        const int pl = r * 256 + tid;
+        const int64_t p = p0 + pl;
+        int lab = 255;
+        if (p < P) {
+            const float* x = logits + n * C * P + p;
+            float v[CT];
+            float m = 0.f;
+            int t = 0;
+#pragma unroll
+            for (int c = 0; c < CT; ++c)
+                if (c < C) {
+                    v[c] = ldg_stream_f(x + c * P);
+                    if (c == 0 || v[c] > m) { m = v[c]; t = c; }
+                }
+            bool hot = true;
+            if (labels_val != nullptr) {
+                const float lv = labels_val[n * P + p];
+                const int lvc = (lv < static_cast<float>(C)) ? static_cast<int>(lv) : overflow;
+                hot = (lvc == t);
+            }
+            bool gate = true;
+            if (use_gate) {
+                float s = 0.f;
+                const float mb = m * kLog2e;
+#pragma unroll
+                for (int c = 0; c < CT; ++c)
+                    if (c < C) s += ex2_approx(fmaf(v[c], kLog2e, -mb));
+                gate = __fdiv_rn(1.0f, s) >= thresh;
+            }
+            if (hot) {
+                atomicAdd(&call[t], 1);
+                if (gate) { atomicAdd(&cgate[t], 1); lab = t; }
+            }
+            seg_label[n * P + p] = static_cast<uint8_t>(lab);
+        }
+        bucket[r] = (lab == 255) ? C : lab;
+        const unsigned int peers = __match_any_sync(0xffffffffu, bucket[r]);
+        rank[r] = __popc(peers & ((1u << lane) - 1u));
+        if (rank[r] == 0) wcnt[r * 8 + warp][bucket[r]] = __popc(peers);
+    }
+    __syncthreads();
+    // exclusive scan in (class, segment) order -> start of every (segment, class) run
+    if (tid <= C) {
+        int tot = 0;
+        for (int s = 0; s < 16; ++s) tot += wcnt[s][tid];
+        boff[tid + 1] = tot;
+    }
+    __syncthreads();
+    if (tid == 0) {
+        boff[0] = 0;
+        for (int b = 0; b <= C; ++b) boff[b + 1] += boff[b];
+    }
+    __syncthreads();
+    if (tid <= C) {
+        int run = boff[tid];
+        for (int s = 0; s < 16; ++s) {
+            const int c = wcnt[s][tid];
+            wcnt[s][tid] = run;
+            run += c;
+        }
+    }
+    __syncthreads();
+    TileRecord* rec = records + n * tiles + tile;
+#pragma unroll
+    for (int r = 0; r < 2; ++r) rec->idx[wcnt[r * 8 + warp][bucket[r]] + rank[r]] = static_cast<uint16_t>(r * 256 + tid);
+    if (tid < 64) rec->off[tid] = static_cast<uint16_t>(tid <= C + 1 ? boff[tid] : kPT);
+    if (tid < C) {
+        if (call[tid]) atomicAdd(&cnt_all[n * C + tid], call[tid]);
+        if (cgate[tid]) atomicAdd(&cnt_gated[n * C + tid], cgate[tid]);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+struct AccSmem {
+    // dynamic shared memory carve-up (byte offsets)
+    static constexpr int rows_bytes = kStages * kKT * kRowStride * 4;
+    static constexpr int rec_off = rows_bytes;
+    static constexpr int bar_off = rec_off + kStages * kRecBytes;
+    static constexpr int total = bar_off + 2 * kStages * 8;
+};
+
+__device__ __forceinline__ int row_skew_words(int lane) {
+    // B_lane = lane*kRowStride + 4*g: choose g so that (B_lane / 4) mod 8 == (lane >> 2) & 7.  With the head
+    // misalignment o_lane = (e0 + lane*P) & 3 (distinct for lane & 3 when P is odd) the 32 lanes of a
+    // "same pixel, lane = channel" read hit 32 distinct banks.
+    constexpr int s = kRowStride / 4;
+    return 4 * (((lane >> 2) - lane * s) & 7);
+}
+
+template <int CT>
+__global__ void __launch_bounds__(kAccThreads, 1)
+proto_accum_kernel(const float* __restrict__ feat, const TileRecord* __restrict__ records, int64_t N, int64_t K,
+                   int64_t P, int C, float* __restrict__ sums) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    float* rows = reinterpret_cast<float*>(smem);
+    unsigned char* recs = smem + AccSmem::rec_off;
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem + AccSmem::bar_off);
+    uint64_t* empty = full + kStages;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int64_t T = (P + kPT - 1) / kPT;
+    const int64_t KG = K / kKT;
+    const int64_t jobs = N * KG * T;
+    const int64_t j0 = jobs * blockIdx.x / gridDim.x, j1 = jobs * (blockIdx.x + 1) / gridDim.x;
+    if (tid == 0) {
+        for (int s = 0; s < kStages; ++s) {
+            mbar_init(&full[s], 32);
+            mbar_init(&empty[s], kConsumers);
+        }
+        mbar_fence_init();
+    }
+    __syncthreads();
+    const int64_t total_elems = N * K * P;
+
+    if (warp == kConsumers) {
+        // ===== producer warp: lane l stages channel row l of every tile job
+        int stage = 0;
+        uint32_t phase = 0;
+        for (int64_t j = j0; j < j1; ++j) {
+            const int64_t t = j % T;
+            const int64_t u = j / T;          // unit = (image, channel group)
+            const int64_t kg = u % KG, n = u / KG;
+            const int64_t p0 = t * kPT;
+            const int len = static_cast<int>(min(static_cast<int64_t>(kPT), P - p0));
+            mbar_wait(&empty[stage], phase ^ 1u);
+            const int64_t e0 = (n * K + kg * kKT + lane) * P + p0;
+            const int o = static_cast<int>(e0 & 3);
+            const int64_t ea = e0 - o;
+            uint32_t nbytes = static_cast<uint32_t>(((o + len) * 4 + 15) & ~15);
+            int patch = 0;
+            if ((ea + nbytes / 4) > total_elems) {  // never read past the end of the tensor
+                nbytes = static_cast<uint32_t>((total_elems - ea) * 4) & ~15u;
+                patch = (o + len) - static_cast<int>(nbytes / 4);
+            }
+            float* dst = rows + (stage * kKT + lane) * kRowStride + row_skew_words(lane);
+            for (int i = 0; i < patch; ++i) dst[nbytes / 4 + i] = feat[ea + nbytes / 4 + i];
+            const uint32_t tx = nbytes + (lane == 0 ? kRecBytes : 0);
+            mbar_arrive_expect_tx(&full[stage], tx);
+            if (nbytes) bulk_g2s(dst, feat + ea, nbytes, &full[stage]);
+            if (lane == 0) bulk_g2s(recs + stage * kRecBytes, records + n * T + t, kRecBytes, &full[stage]);
+            if (++stage == kStages) { stage = 0; phase ^= 1u; }
+        }
+    } else {
+        // ===== consumer warps: class-sorted walk, lane = channel
+        float acc[CT];
+#pragma unroll
+        for (int c = 0; c < CT; ++c) acc[c] = 0.f;
+        int stage = 0;
+        uint32_t phase = 0;
+        int64_t cur_unit = -1;
+        const int s0 = warp * (kPT / kConsumers), s1 = s0 + kPT / kConsumers;
+        auto flush = [&](int64_t u) {
+            const int64_t kg = u % KG, n = u / KG;
+            float* out = sums + (n * C) * K + kg * kKT + lane;
+#pragma unroll
+            for (int c = 0; c < CT; ++c)
+                if (c < C) {
+                    if (acc[c] != 0.f) atomicAdd(out + c * K, acc[c]);
+                    acc[c] = 0.f;
+                }
+        };
+        for (int64_t j = j0; j < j1; ++j) {
+            const int64_t t = j % T;
+            const int64_t u = j / T;
+            if (u != cur_unit) {
+                if (cur_unit >= 0) flush(cur_unit);
+                cur_unit = u;
+            }
+            const int64_t kg = u % KG, n = u / KG;
+            const int64_t e0 = (n * K + kg * kKT + lane) * P + t * kPT;
+            const float* row = rows + (stage * kKT + lane) * kRowStride + row_skew_words(lane) + static_cast<int>(e0 & 3);
+            const TileRecord* rec = reinterpret_cast<const TileRecord*>(recs + stage * kRecBytes);
+            mbar_wait(&full[stage], phase);
+#pragma unroll
+            for (int c = 0; c < CT; ++c) {
+                if (c < C) {
+                    const int a = max(s0, static_cast<int>(rec->off[c]));
+                    const int b = min(s1, static_cast<int>(rec->off[c + 1]));
+                    if (a < b) {
+                        float t0 = 0.f, t1 = 0.f;
+                        int i = a;
+                        for (; i + 1 < b; i += 2) {
+                            t0 += row[rec->idx[i]];
+                            t1 += row[rec->idx[i + 1]];
+                        }
+                        if (i < b) t0 += row[rec->idx[i]];
+                        acc[c] += t0 + t1;
+                    }
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty[stage]);
+            if (++stage == kStages) { stage = 0; phase ^= 1u; }
+        }
+        if (cur_unit >= 0) flush(cur_unit);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+proto_finalize_kernel(const float* __restrict__ sums, const int32_t* __restrict__ cnt_all,
+                      const int32_t* __restrict__ cnt_gated, int C, int64_t K, int min_pixels,
+                      float* __restrict__ vectors, uint8_t* __restrict__ valid, float* __restrict__ vector_sum) {
+    __shared__ float part[8];
+    const int64_t nc = blockIdx.x;  // n*C + c
+    const int cg = cnt_gated[nc], ca = cnt_all[nc];
+    const bool ok = cg > 0 && ca >= min_pixels;
+    const float denom = static_cast<float>(cg);
+    float s = 0.f;
+    for (int64_t k = threadIdx.x; k < K; k += 256) {
+        const float v = ok ? __fdiv_rn(sums[nc * K + k], denom) : 0.f;
+        vectors[nc * K + k] = v;
+        s += v;
+    }
+    s = warp_sum(s);
+    if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float tot = 0.f;
+        for (int w = 0; w < 8; ++w) tot += part[w];
+        vector_sum[nc] = tot;
+        valid[nc] = ok ? 1 : 0;
+    }
+}
+
+// one CTA per class; images in order; the reference's own fp32 operation sequence
+__global__ void __launch_bounds__(256)
+proto_update_kernel(float* __restrict__ protos, float* __restrict__ num, const float* __restrict__ vectors,
+                    const uint8_t* __restrict__ valid, const float* __restrict__ vector_sum, int64_t N, int C,
+                    int64_t K, int mode, int start_mean, float m, float one_minus_m, float cap) {
+    const int c = blockIdx.x;
+    float cnt = num[c];
+    for (int64_t n = 0; n < N; ++n) {
+        const int64_t nc = n * C + c;
+        if (!valid[nc] || vector_sum[nc] == 0.f) continue;
+        const bool mean = (mode == TSS_UPDATE_MEAN) || (start_mean && cnt < 100.f);
+        const float* v = vectors + nc * K;
+        if (mean) {
+            const float cnt1 = cnt + 1.f;
+            for (int64_t k = threadIdx.x; k < K; k += 256) {
+                const float p = protos[c * K + k];
+                protos[c * K + k] = __fdiv_rn(__fadd_rn(__fmul_rn(p, cnt), v[k]), cnt1);
+            }
+            cnt = fminf(cnt1, cap);
+        } else {
+            for (int64_t k = threadIdx.x; k < K; k += 256) {
+                const float p = protos[c * K + k];
+                protos[c * K + k] = __fadd_rn(__fmul_rn(p, one_minus_m), __fmul_rn(m, v[k]));
+            }
+            cnt = fminf(cnt + 1.f, cap);
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) num[c] = cnt;
+}
+
+// closed-form weights of the same recurrence, for the sharded (all-reduce) form
+__global__ void __launch_bounds__(256)
+proto_update_partial_kernel(const float* __restrict__ vectors, const uint8_t* __restrict__ valid,
+                            const float* __restrict__ vector_sum, int64_t N, int C, int64_t K, int mode,
+                            int start_mean, double m, double cap, const float* __restrict__ num_before,
+                            const int32_t* __restrict__ first_index, const int32_t* __restrict__ total,
+                            int32_t* __restrict__ contrib_count, float* __restrict__ partial,
+                            float* __restrict__ scale0, float* __restrict__ num_after) {
+    extern __shared__ double wts[];  // [N] weight of image n's vector (0 when it does not contribute)
+    const int c = blockIdx.x;
+    __shared__ int m_local;
+    if (threadIdx.x == 0) {
+        int cnt = 0;
+        for (int64_t n = 0; n < N; ++n) cnt += (valid[n * C + c] && vector_sum[n * C + c] != 0.f) ? 1 : 0;
+        m_local = cnt;
+        if (contrib_count) contrib_count[c] = cnt;
+    }
+    __syncthreads();
+    if (first_index == nullptr) return;
+    if (threadIdx.x == 0) {
+        const int first = first_index[c], M = total[c];
+        const double n0 = static_cast<double>(num_before[c]);
+        // walk the global sequence backwards: suffix = product of a_i for i > j
+        double suffix = 1.0;
+        int local = m_local - 1;
+        // image order of local contributions
+        int64_t n_of = N - 1;
+        for (int j = M - 1; j >= 0; --j) {
+            const double nj = fmin(n0 + j, cap);
+            const bool mean = (mode == TSS_UPDATE_MEAN) || (start_mean && nj < 100.0);
+            const double a = mean ? nj / (nj + 1.0) : 1.0 - m;
+            const double b = mean ? 1.0 / (nj + 1.0) : m;
+            if (j >= first && j < first + m_local) {
+                while (!(valid[n_of * C + c] && vector_sum[n_of * C + c] != 0.f)) { wts[n_of] = 0.0; --n_of; }
+                wts[n_of] = b * suffix;
+                --n_of;
+                --local;
+            }
+            suffix *= a;
+        }
+        for (; n_of >= 0; --n_of) wts[n_of] = 0.0;
+        scale0[c] = static_cast<float>(suffix);
+        num_after[c] = static_cast<float>(fmin(n0 + M, cap));
+    }
+    __syncthreads();
+    for (int64_t k = threadIdx.x; k < K; k += 256) {
+        double s = 0.0;
+        for (int64_t n = 0; n < N; ++n) {
+            const double w = wts[n];
+            if (w != 0.0) s += w * static_cast<double>(vectors[(n * C + c) * K + k]);
+        }
+        partial[c * K + k] = static_cast<float>(s);
+    }
+}
+
+}  // namespace tss
+
+extern "C" size_t tss_proto_records_bytes(int64_t n_img, int64_t plane) {
+    if (n_img <= 0 || plane <= 0) return 0;
+    const int64_t tiles = (plane + tss::kPT - 1) / tss::kPT;
+    return static_cast<size_t>(n_img * tiles) * tss::kRecBytes;
+}
+
+extern "C" int tss_proto_labels(const float* logits, const float* labels_val, int64_t n_img, int num_classes,
+                                int64_t plane, int overflow_channel, int use_conf_gate, float conf_thresh,
+                                uint8_t* seg_label, int32_t* count_all, int32_t* count_gated, void* records,
+                                void* stream) {
+    using namespace tss;
+    TSS_REQUIRE(logits && seg_label && count_all && count_gated && records, TSS_E_ARG, "tss_proto_labels: null pointer");
+    TSS_REQUIRE(n_img >= 0 && plane > 0 && n_img <= 65535, TSS_E_ARG, "tss_proto_labels: bad extents");
+    TSS_REQUIRE(num_classes >= 1 && num_classes <= TSS_MAX_CLASSES, TSS_E_CLASSES, "tss_proto_labels: num_classes %d", num_classes);
+    TSS_REQUIRE((reinterpret_cast<uintptr_t>(records) & 15) == 0, TSS_E_ALIGN, "tss_proto_labels: records must be 16-byte aligned");
+    if (n_img == 0) return TSS_OK;
+    cudaStream_t st = as_stream(stream);
+    cudaError_t e = cudaMemsetAsync(count_all, 0, sizeof(int32_t) * n_img * num_classes, st);
+    if (e == cudaSuccess) e = cudaMemsetAsync(count_gated, 0, sizeof(int32_t) * n_img * num_classes, st);
+    if (e != cudaSuccess) return cuda_status(e, "tss_proto_labels: memset");
+    const int64_t tiles = (plane + kPT - 1) / kPT;
+    dim3 grid(static_cast<unsigned>(tiles), static_cast<unsigned>(n_img));
+    auto* rec = static_cast<TileRecord*>(records);
+    if (num_classes <= 13)
+        proto_label_kernel<13><<<grid, 256, 0, st>>>(logits, labels_val, num_classes, plane, overflow_channel, use_conf_gate, conf_thresh, seg_label, count_all, count_gated, rec);
+    else if (num_classes <= 19)
+        proto_label_kernel<19><<<grid, 256, 0, st>>>(logits, labels_val, num_classes, plane, overflow_channel, use_conf_gate, conf_thresh, seg_label, count_all, count_gated, rec);
+    else
+        proto_label_kernel<TSS_MAX_CLASSES><<<grid, 256, 0, st>>>(logits, labels_val, num_classes, plane, overflow_channel, use_conf_gate, conf_thresh, seg_label, count_all, count_gated, rec);
+    TSS_LAUNCH_CHECK("tss_proto_labels");
+    return TSS_OK;
+}
+
+namespace tss {
+template <int CT>
+static int launch_accum(const float* feat, const TileRecord* rec, int64_t N, int64_t K, int64_t P, int C, float* sums,
+                        cudaStream_t st) {
+    cudaError_t e = cudaFuncSetAttribute(proto_accum_kernel<CT>, cudaFuncAttributeMaxDynamicSharedMemorySize, AccSmem::total);
+    if (e != cudaSuccess) return cuda_status(e, "tss_proto_accumulate: smem attribute");
+    const int64_t jobs = N * (K / kKT) * ((P + kPT - 1) / kPT);
+    const int grid = static_cast<int>(jobs < kNumSMs ? jobs : kNumSMs);
+    proto_accum_kernel<CT><<<grid, kAccThreads, AccSmem::total, st>>>(feat, rec, N, K, P, C, sums);
+    TSS_LAUNCH_CHECK("tss_proto_accumulate");
+    return TSS_OK;
+}
+}  // namespace tss
+
+extern "C" int tss_proto_accumulate(const float* feat, const void* records, int64_t n_img, int64_t channels,
+                                    int64_t plane, int num_classes, float* sums, void* stream) {
+    using namespace tss;
+    TSS_REQUIRE(feat && records && sums, TSS_E_ARG, "tss_proto_accumulate: null pointer");
+    TSS_REQUIRE(n_img >= 0 && plane > 0 && channels > 0, TSS_E_ARG, "tss_proto_accumulate: bad extents");
+    TSS_REQUIRE(channels % kKT == 0, TSS_E_ARG, "tss_proto_accumulate: channels (%lld) must be a multiple of 32", static_cast<long long>(channels));
+    TSS_REQUIRE(num_classes >= 1 && num_classes <= TSS_MAX_CLASSES, TSS_E_CLASSES, "tss_proto_accumulate: num_classes %d", num_classes);
+    TSS_REQUIRE((reinterpret_cast<uintptr_t>(feat) & 15) == 0 && (reinterpret_cast<uintptr_t>(records) & 15) == 0, TSS_E_ALIGN,
+                "tss_proto_accumulate: feat and records must be 16-byte aligned");
+    if (n_img == 0) return TSS_OK;
+    cudaStream_t st = as_stream(stream);
+    cudaError_t e = cudaMemsetAsync(sums, 0, sizeof(float) * n_img * num_classes * channels, st);
+    if (e != cudaSuccess) return cuda_status(e, "tss_proto_accumulate: memset");
+    auto* rec = static_cast<const TileRecord*>(records);
+    if (num_classes <= 13) return launch_accum<13>(feat, rec, n_img, channels, plane, num_classes, sums, st);
+    if (num_classes <= 19) return launch_accum<19>(feat, rec, n_img, channels, plane, num_classes, sums, st);
+    return launch_accum<TSS_MAX_CLASSES>(feat, rec, n_img, channels, plane, num_classes, sums, st);
+}
+
+extern "C" int tss_proto_finalize(const float* sums, const int32_t* count_all, const int32_t* count_gated,
+                                  int64_t n_img, int num_classes, int64_t channels, int min_pixels, float* vectors,
+                                  uint8_t* valid, float* vector_sum, void* stream) {
+    using namespace tss;
+    TSS_REQUIRE(sums && count_all && count_gated && vectors && valid && vector_sum, TSS_E_ARG, "tss_proto_finalize: null pointer");
+    TSS_REQUIRE(n_img >= 0 && channels > 0 && num_classes >= 1 && num_classes <= TSS_MAX_CLASSES, TSS_E_ARG, "tss_proto_finalize: bad extents");
+    if (n_img == 0) return TSS_OK;
+    proto_finalize_kernel<<<static_cast<unsigned>(n_img * num_classes), 256, 0, as_stream(stream)>>>(
+        sums, count_all, count_gated, num_classes, channels, min_pixels, vectors, valid, vector_sum);
+    TSS_LAUNCH_CHECK("tss_proto_finalize");
+    return TSS_OK;
+}
+
+extern "C" int tss_proto_update(float* protos, float* num, const float* vectors, const uint8_t* valid,
+                                const float* vector_sum, int64_t n_img, int num_classes, int64_t channels, int mode,
+                                int start_mean, double momentum, double cap, void* stream) {
+    using namespace tss;
+    TSS_REQUIRE(protos && num && vectors && valid && vector_sum, TSS_E_ARG, "tss_proto_update: null pointer");
+    TSS_REQUIRE(n_img >= 0 && channels > 0 && num_classes >= 1 && num_classes <= TSS_MAX_CLASSES, TSS_E_ARG, "tss_proto_update: bad extents");
+    TSS_REQUIRE(mode == TSS_UPDATE_MEAN || mode == TSS_UPDATE_MOVING_AVERAGE, TSS_E_ARG, "tss_proto_update: bad mode %d", mode);
+    if (n_img == 0) return TSS_OK;
+    // python evaluates (1 - momentum) in double before the fp32 tensor multiply
+    proto_update_kernel<<<num_classes, 256, 0, as_stream(stream)>>>(protos, num, vectors, valid, vector_sum, n_img, num_classes,
+                                                                    channels, mode, start_mean, static_cast<float>(momentum),
+                                                                    static_cast<float>(1.0 - momentum), static_cast<float>(cap));
+    TSS_LAUNCH_CHECK("tss_proto_update");
+    return TSS_OK;
+}
+
+extern "C" int tss_proto_update_partial(const float* vectors, const uint8_t* valid, const float* vector_sum,
+                                        int64_t n_img, int num_classes, int64_t channels, int mode, int start_mean,
+                                        double momentum, double cap, const float* num_before,
+                                        const int32_t* first_index, const int32_t* total, int32_t* contrib_count,
+                                        float* partial, float* scale0, float* num_after, void* stream) {
+    using namespace tss;
+    TSS_REQUIRE(vectors && valid && vector_sum, TSS_E_ARG, "tss_proto_update_partial: null pointer");
+    TSS_REQUIRE(n_img >= 0 && n_img <= 16384 && channels > 0 && num_classes >= 1 && num_classes <= TSS_MAX_CLASSES, TSS_E_ARG,
+                "tss_proto_update_partial: bad extents (at most 16384 images per call)");
+    TSS_REQUIRE(first_index != nullptr || contrib_count != nullptr, TSS_E_ARG, "tss_proto_update_partial: nothing to do");
+    TSS_REQUIRE(first_index == nullptr || (total && partial && scale0 && num_after && num_before), TSS_E_ARG,
+                "tss_proto_update_partial: weighted pass needs total, partial, scale0, num_before, num_after");
+    const size_t sh = sizeof(double) * static_cast<size_t>(n_img > 0 ? n_img : 1);
+    cudaError_t e = cudaFuncSetAttribute(proto_update_partial_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
+    if (e != cudaSuccess) return cuda_status(e, "tss_proto_update_partial: smem attribute");
+    proto_update_partial_kernel<<<num_classes, 256, sh, as_stream(stream)>>>(vectors, valid, vector_sum, n_img, num_classes, channels,
+                                                                             mode, start_mean, momentum, cap, num_before, first_index,
+                                                                             total, contrib_count, partial, scale0, num_after);
+    TSS_LAUNCH_CHECK("tss_proto_update_partial");
+    return TSS_OK;
+}

@@ -1,0 +1,484 @@
+// A1-A4: fused bilinear upsample -> per-pixel softmax / argmax / confidence -> fp16 + uint8 storage
+// casts -> class-wise threshold into ignore_index (generate_pseudo_label.py:74-94,
+// data/freiburg_dataset.py:115-123, segmentation_evaluate.py:38-42).
+//
+// pl_tile_kernel: one CTA = one 128-wide x TY-high tile of one image.
+//   phase 1  horizontal taps: for every source row the tile touches (NR rows) and every class, the
+//            x-interpolated value of each of the tile's 128 output columns goes to shared memory
+//            (lx0*a + lx1*b: the reference's operation order, horizontal first);
+//   phase 2  every thread owns 4 consecutive output pixels of a row: two 128-bit shared loads per class
+//            give the two vertical taps, the C interpolated logits stay in registers, then max/argmax,
+//            C ex2 on the SFU, reciprocal, storage casts and threshold; one 32-bit label store and one
+//            64-bit fp16 store per thread (a warp writes 128 B / 256 B contiguous).
+//   The C*H*W upsampled tensor the reference materialises (1 GB at 16x13x640x1920) never exists.
+// pl_direct_kernel: same pixel reduction on full-resolution input (H==h, W==w), 128-bit coalesced
+//   loads of the C planes -- the HBM-bound variant (4C+3 B/px).
+#include "common.cuh"
+
+namespace tss {
+
+constexpr int kTX = 128;          // tile width: 32 lanes x 4 px
+constexpr int kPLThreads = 256;   // 8 warps, each walks rows wy, wy+8, ...
+
+struct PLArgs {
+    const float* src;
+    const float* src2;
+    uint8_t* label;
+    __half* conf16;
+    float* conf32;
+    uint8_t* label_thr;
+    int C, h, w, H, W;
+    float sy, sx;
+    int mode, flip;
+    int TY, NR;
+    int vec_ok;
+    int has_thr, ignore;
+    unsigned int keep_mask;
+    float thr16[TSS_MAX_CLASSES];  // thresholds already rounded to fp16 (numpy compares in fp16)
+};
+
+struct Tap {
+    int i0, i1;
+    float l0, l1;
+};
+// ATen area_pixel_compute_source_index, align_corners=True: src = scale * dst, all fp32
+__device__ __forceinline__ Tap make_tap(float scale, int dst, int n_in) {
+    Tap t;
+    const float s = scale * static_cast<float>(dst);
+    t.i0 = min(static_cast<int>(s), n_in - 1);
+    t.i1 = t.i0 + (t.i0 < n_in - 1 ? 1 : 0);
+    t.l1 = s - static_cast<float>(t.i0);
+    t.l0 = 1.0f - t.l1;
+    return t;
+}
+
+// per-pixel reduction over classes; v[] = the C values of one pixel
+template <int CT>
+__device__ __forceinline__ void reduce_pixel(const float (&v)[CT], int C, int mode, float& conf, int& label) {
+    float m = v[0];
+    int idx = 0;
+#pragma unroll
+    for (int c = 1; c < CT; ++c) {
+        if (c < C) {
+            const bool gt = v[c] > m;  // strict: ties keep the lowest class, as torch.max / argmax
+            m = gt ? v[c] : m;
+            idx = gt ? c : idx;
+        }
+    }
+    label = idx;
+    if (mode == TSS_PL_UP_SOFTMAX || mode == TSS_PL_PROB_UP_SOFTMAX) {
+        const float mb = m * kLog2e;
+        float s = 0.f;
+#pragma unroll
+        for (int c = 0; c < CT; ++c)
+            if (c < C) s += ex2_approx(fmaf(v[c], kLog2e, -mb));
+        conf = __fdiv_rn(1.0f, s);
+    } else {
+        conf = m;
+    }
+}
+
+__device__ __forceinline__ uint8_t apply_threshold(const PLArgs& a, int label, float conf) {
+    // fp16(conf) <= fp16(thr[label])  ->  ignore; classes outside the whitelist -> ignore
+    const float c16 = __half2float(__float2half_rn(conf));
+    const bool reject = a.has_thr && (c16 <= a.thr16[label]);
+    const bool keep = (a.keep_mask >> label) & 1u;
+    return static_cast<uint8_t>((reject || !keep) ? a.ignore : label);
+}
+
+__device__ __forceinline__ void store_quad(const PLArgs& a, int64_t off, int valid, const float (&conf)[4],
+                                           const int (&lab)[4]) {
+    if (a.vec_ok && valid == 4) {
+        if (a.label)
+            *reinterpret_cast<uint32_t*>(a.label + off) =
+                static_cast<uint32_t>(lab[0]) | (static_cast<uint32_t>(lab[1]) << 8) |
+                (static_cast<uint32_t>(lab[2]) << 16) | (static_cast<uint32_t>(lab[3]) << 24);
+        if (a.conf16) {
+            __half2 lo = __floats2half2_rn(conf[0], conf[1]);
+            __half2 hi = __floats2half2_rn(conf[2], conf[3]);
+            uint2 pk;
+            pk.x = *reinterpret_cast<uint32_t*>(&lo);
+            pk.y = *reinterpret_cast<uint32_t*>(&hi);
+            *reinterpret_cast<uint2*>(a.conf16 + off) = pk;
+        }
+        if (a.conf32) *reinterpret_cast<float4*>(a.conf32 + off) = make_float4(conf[0], conf[1], conf[2], conf[3]);
+        if (a.label_thr) {
+            uint32_t t = 0;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) t |= static_cast<uint32_t>(apply_threshold(a, lab[i], conf[i])) << (8 * i);
+            *reinterpret_cast<uint32_t*>(a.label_thr + off) = t;
+        }
+    } else {
+        for (int i = 0; i < valid; ++i) {
+            if (a.label) a.label[off + i] = static_cast<uint8_t>(lab[i]);
+            if (a.conf16) a.conf16[off + i] = __float2half_rn(conf[i]);
+            if (a.conf32) a.conf32[off + i] = conf[i];
+            if (a.label_thr) a.label_thr[off + i] = apply_threshold(a, lab[i], conf[i]);
+        }
+    }
+}
+
+template <int CT, bool FLIP>
+__global__ void __launch_bounds__(kPLThreads, 2) pl_tile_kernel(const PLArgs a) {
+    extern __shared__ __align__(16) float hs[];  // [FLIP ? 2 : 1][C][NR][kTX]
+    const int C = a.C, NR = a.NR;
+    const int tid = threadIdx.x;
+    const int x0 = blockIdx.x * kTX, y0 = blockIdx.y * a.TY;
+    const int64_t n = blockIdx.z;
+    const int rb = min(static_cast<int>(a.sy * static_cast<float>(y0)), a.h - 1);
+    const int plane_sz = C * NR * kTX;
+
+    // ---- phase 1: horizontal interpolation of the NR source rows this tile needs
+    {
+        const int tx = tid & (kTX - 1);
+        const int gx = min(x0 + tx, a.W - 1);
+        const Tap t = make_tap(a.sx, gx, a.w);
+        Tap t2 = t;
+        if (FLIP && a.flip == TSS_FLIP_WIDTH) t2 = make_tap(a.sx, a.W - 1 - gx, a.w);
+        const float* base = a.src + n * C * static_cast<int64_t>(a.h) * a.w;
+        const float* base2 = FLIP ? a.src2 + n * C * static_cast<int64_t>(a.h) * a.w : nullptr;
+        for (int j = tid / kTX; j < C * NR; j += kPLThreads / kTX) {
+            const int c = j / NR, r = j - c * NR;
+            const int row = min(rb + r, a.h - 1);
+            const float* p = base + (static_cast<int64_t>(c) * a.h + row) * a.w;
+            hs[j * kTX + tx] = fmaf(t.l1, __ldg(p + t.i1), t.l0 * __ldg(p + t.i0));
+            if (FLIP) {
+                const int c2 = (a.flip == TSS_FLIP_CLASS) ? (C - 1 - c) : c;
+                const float* q = base2 + (static_cast<int64_t>(c2) * a.h + row) * a.w;
+                hs[plane_sz + j * kTX + tx] = fmaf(t2.l1, __ldg(q + t2.i1), t2.l0 * __ldg(q + t2.i0));
+            }
+        }
+    }
+    __syncthreads();
+
+    // ---- phase 2: vertical interpolation + per-pixel reduction, 4 px per thread
+    const int warp = tid >> 5, lane = tid & 31;
+    const int xq = x0 + 4 * lane;
+    if (xq >= a.W) return;
+    const int valid = min(4, a.W - xq);
+    for (int ry = warp; ry < a.TY; ry += kPLThreads / 32) {
+        const int y = y0 + ry;
+        if (y >= a.H) break;
+        const Tap ty = make_tap(a.sy, y, a.h);
+        const int r0 = ty.i0 - rb, r1 = ty.i1 - rb;
+        float v[4][CT];
+#pragma unroll
+        for (int c = 0; c < CT; ++c) {
+            if (c < C) {
+                const float4 t0 = *reinterpret_cast<const float4*>(hs + (c * NR + r0) * kTX + 4 * lane);
+                const float4 t1 = *reinterpret_cast<const float4*>(hs + (c * NR + r1) * kTX + 4 * lane);
+                v[0][c] = fmaf(ty.l1, t1.x, ty.l0 * t0.x);
+                v[1][c] = fmaf(ty.l1, t1.y, ty.l0 * t0.y);
+                v[2][c] = fmaf(ty.l1, t1.z, ty.l0 * t0.z);
+                v[3][c] = fmaf(ty.l1, t1.w, ty.l0 * t0.w);
+                if (FLIP) {
+                    const float4 u0 = *reinterpret_cast<const float4*>(hs + plane_sz + (c * NR + r0) * kTX + 4 * lane);
+                    const float4 u1 = *reinterpret_cast<const float4*>(hs + plane_sz + (c * NR + r1) * kTX + 4 * lane);
+                    v[0][c] = (v[0][c] + fmaf(ty.l1, u1.x, ty.l0 * u0.x)) * 0.5f;
+                    v[1][c] = (v[1][c] + fmaf(ty.l1, u1.y, ty.l0 * u0.y)) * 0.5f;
+                    v[2][c] = (v[2][c] + fmaf(ty.l1, u1.z, ty.l0 * u0.z)) * 0.5f;
+                    v[3][c] = (v[3][c] + fmaf(ty.l1, u1.w, ty.l0 * u0.w)) * 0.5f;
+                }
+            }
+        }
+        float conf[4];
+        int lab[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) reduce_pixel<CT>(v[i], C, a.mode, conf[i], lab[i]);
+        store_quad(a, (n * a.H + y) * static_cast<int64_t>(a.W) + xq, valid, conf, lab);
+    }
+}
+
+// full-resolution input: grid-stride over pixel quads of the flattened [N, H*W] map
+template <int CT>
+__global__ void __launch_bounds__(256) pl_direct_kernel(const PLArgs a, int64_t n_img) {
+    const int C = a.C;
+    const int64_t plane = static_cast<int64_t>(a.H) * a.W;
+    const int64_t quads_per_img = (plane + 3) / 4;
+    const int64_t total = n_img * quads_per_img;
+    for (int64_t q = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; q < total;
+         q += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+        const int64_t n = q / quads_per_img;
+        const int64_t p = (q - n * quads_per_img) * 4;
+        const int valid = static_cast<int>(min(static_cast<int64_t>(4), plane - p));
+        const float* base = a.src + n * C * plane + p;
+        float v[4][CT];
+        if (a.vec_ok && valid == 4) {
+#pragma unroll
+            for (int c = 0; c < CT; ++c)
+                if (c < C) {
+                    const float4 t = ldg_stream_f4(base + c * plane);
+                    v[0][c] = t.x; v[1][c] = t.y; v[2][c] = t.z; v[3][c] = t.w;
+                }
+        } else {
+#pragma unroll
+            for (int c = 0; c < CT; ++c)
+                if (c < C)
+                    for (int i = 0; i < 4; ++i) v[i][c] = (i < valid) ? base[c * plane + i] : 0.f;
+        }
+        float conf[4];
+        int lab[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) reduce_pixel<CT>(v[i], C, a.mode, conf[i], lab[i]);
+        store_quad(a, n * plane + p, valid, conf, lab);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// A2 low-resolution softmax over the class axis of [N, C, P]
+template <int CT>
+__global__ void __launch_bounds__(256) softmax_nchw_kernel(const float* __restrict__ x, float* __restrict__ y,
+                                                           int64_t n_img, int C, int64_t plane) {
+    const int64_t total = n_img * plane;
+    for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
+         i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+        const int64_t n = i / plane, p = i - n * plane;
+        const float* px = x + n * C * plane + p;
+        float v[CT];
+        float m = -INFINITY;
+#pragma unroll
+        for (int c = 0; c < CT; ++c)
+            if (c < C) {
+                v[c] = px[c * plane];
+                m = fmaxf(m, v[c]);
+            }
+        float s = 0.f;
+#pragma unroll
+        for (int c = 0; c < CT; ++c)
+            if (c < C) {
+                v[c] = expf(v[c] - m);  // full-precision exp: these probabilities are a stored product
+                s += v[c];
+            }
+        float* py = y + n * C * plane + p;
+#pragma unroll
+        for (int c = 0; c < CT; ++c)
+            if (c < C) py[c * plane] = __fdiv_rn(v[c], s);
+    }
+}
+
+// A1 plain bilinear upsample of [planes, h, w] -> [planes, H, W]
+__global__ void __launch_bounds__(256) upsample_kernel(const float* __restrict__ src, float* __restrict__ dst,
+                                                       int64_t planes, int h, int w, int H, int W, float sy, float sx) {
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    const int y = blockIdx.y;
+    if (x >= W) return;
+    const Tap tx = make_tap(sx, x, w), ty = make_tap(sy, y, h);
+    for (int64_t pl = blockIdx.z; pl < planes; pl += gridDim.z) {
+        const float* p = src + pl * static_cast<int64_t>(h) * w;
+        const float top = fmaf(tx.l1, __ldg(p + ty.i0 * w + tx.i1), tx.l0 * __ldg(p + ty.i0 * w + tx.i0));
+        const float bot = fmaf(tx.l1, __ldg(p + ty.i1 * w + tx.i1), tx.l0 * __ldg(p + ty.i1 * w + tx.i0));
+        dst[(pl * H + y) * static_cast<int64_t>(W) + x] = fmaf(ty.l1, bot, ty.l0 * top);
+    }
+}
+
+__global__ void __launch_bounds__(256) threshold_kernel(const uint8_t* __restrict__ lab, const __half* __restrict__ conf,
+                                                        int64_t n, PLArgs a, uint8_t* __restrict__ out) {
+    for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < n;
+         i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+        const int l = lab[i];
+        uint8_t r = static_cast<uint8_t>(a.ignore);
+        if (l < a.C) {
+            const bool reject = a.has_thr && (__half2float(conf[i]) <= a.thr16[l]);
+            const bool keep = (a.keep_mask >> l) & 1u;
+            r = static_cast<uint8_t>((reject || !keep) ? a.ignore : l);
+        }
+        out[i] = r;
+    }
+}
+
+__global__ void __launch_bounds__(256) gather_nearest_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst,
+                                                             int64_t planes, int h, int w, int H, int W,
+                                                             const int32_t* __restrict__ ytab, const int32_t* __restrict__ xtab) {
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    const int y = blockIdx.y;
+    if (x >= W) return;
+    const int sx = xtab[x], sy = ytab[y];
+    for (int64_t pl = blockIdx.z; pl < planes; pl += gridDim.z)
+        dst[(pl * H + y) * static_cast<int64_t>(W) + x] = src[(pl * h + sy) * static_cast<int64_t>(w) + sx];
+}
+
+static float scale_of(int n_in, int n_out) {
+    // ATen area_pixel_compute_scale<float>(align_corners=true)
+    return n_out > 1 ? static_cast<float>(n_in - 1) / static_cast<float>(n_out - 1) : 0.0f;
+}
+
+static void fill_threshold(PLArgs& a, int C, const float* thr_host, const uint8_t* keep_host, int ignore_index) {
+    a.has_thr = thr_host != nullptr;
+    a.ignore = ignore_index;
+    a.keep_mask = 0;
+    for (int c = 0; c < TSS_MAX_CLASSES; ++c) {
+        a.thr16[c] = (thr_host && c < C) ? __half2float(__float2half_rn(thr_host[c])) : 0.f;
+        if (c < C && (keep_host == nullptr || keep_host[c])) a.keep_mask |= 1u << c;
+    }
+}
+
+template <int CT>
+static int launch_tile(const PLArgs& a, int64_t n_img, size_t smem, cudaStream_t st) {
+    dim3 grid((a.W + kTX - 1) / kTX, (a.H + a.TY - 1) / a.TY, static_cast<unsigned>(n_img));
+    cudaError_t e;
+    if (a.flip != TSS_FLIP_NONE) {
+        e = cudaFuncSetAttribute(pl_tile_kernel<CT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+        if (e != cudaSuccess) return cuda_status(e, "tss_pseudo_label: smem attribute");
+        pl_tile_kernel<CT, true><<<grid, kPLThreads, smem, st>>>(a);
+    } else {
+        e = cudaFuncSetAttribute(pl_tile_kernel<CT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+        if (e != cudaSuccess) return cuda_status(e, "tss_pseudo_label: smem attribute");
+        pl_tile_kernel<CT, false><<<grid, kPLThreads, smem, st>>>(a);
+    }
+    TSS_LAUNCH_CHECK("tss_pseudo_label(tile)");
+    return TSS_OK;
+}
+
+template <int CT>
+static int launch_direct(const PLArgs& a, int64_t n_img, cudaStream_t st) {
+    const int64_t quads = n_img * ((static_cast<int64_t>(a.H) * a.W + 3) / 4);
+    int64_t blocks = (quads + 255) / 256;
+    const int64_t cap = static_cast<int64_t>(kNumSMs) * 16;
+    if (blocks > cap) blocks = cap;
+    pl_direct_kernel<CT><<<static_cast<int>(blocks), 256, 0, st>>>(a, n_img);
+    TSS_LAUNCH_CHECK("tss_pseudo_label(direct)");
+    return TSS_OK;
+}
+
+static int g_pl_force_tile = 0;
+
+}  // namespace tss
+
+extern "C" int tss_tune_pl_force_tile(int v) {
+    int old = tss::g_pl_force_tile;
+    if (v >= 0) tss::g_pl_force_tile = v;
+    return old;
+}
+
+extern "C" int tss_pseudo_label(const float* src, const float* src_flip, int64_t n_img, int num_classes, int h, int w,
+                                int H, int W, int mode, int flip, uint8_t* label_out, uint16_t* conf16_out,
+                                float* conf32_out, uint8_t* label_thr_out, const float* thr_host,
+                                const uint8_t* keep_host, int ignore_index, void* stream) {
+    using namespace tss;
+    TSS_REQUIRE(src != nullptr, TSS_E_ARG, "tss_pseudo_label: null src");
+    TSS_REQUIRE(n_img >= 0 && h > 0 && w > 0 && H > 0 && W > 0, TSS_E_ARG, "tss_pseudo_label: bad extents");
+    TSS_REQUIRE(n_img <= 65535, TSS_E_ARG, "tss_pseudo_label: at most 65535 images per call");
+    TSS_REQUIRE(num_classes >= 1 && num_classes <= TSS_MAX_CLASSES, TSS_E_CLASSES,
+                "tss_pseudo_label: num_classes %d outside [1, %d]", num_classes, TSS_MAX_CLASSES);
+    TSS_REQUIRE(mode >= TSS_PL_UP_SOFTMAX && mode <= TSS_PL_PROB_UP_SOFTMAX, TSS_E_ARG, "tss_pseudo_label: bad mode %d", mode);
+    TSS_REQUIRE(flip >= TSS_FLIP_NONE && flip <= TSS_FLIP_WIDTH, TSS_E_ARG, "tss_pseudo_label: bad flip %d", flip);
+    TSS_REQUIRE(flip == TSS_FLIP_NONE || src_flip != nullptr, TSS_E_ARG, "tss_pseudo_label: flip without src_flip");
+    TSS_REQUIRE(ignore_index >= 0 && ignore_index <= 255, TSS_E_ARG, "tss_pseudo_label: ignore_index outside uint8");
+    if (n_img == 0) return TSS_OK;
+    cudaStream_t st = as_stream(stream);
+    PLArgs a;
+    a.src = src;
+    a.src2 = src_flip;
+    a.label = label_out;
+    a.conf16 = reinterpret_cast<__half*>(conf16_out);
+    a.conf32 = conf32_out;
+    a.label_thr = label_thr_out;
+    a.C = num_classes; a.h = h; a.w = w; a.H = H; a.W = W;
+    a.sy = scale_of(h, H);
+    a.sx = scale_of(w, W);
+    a.mode = mode;
+    a.flip = flip;
+    fill_threshold(a, num_classes, thr_host, keep_host, ignore_index);
+    auto al = [](const void* p, uintptr_t m) { return p == nullptr || (reinterpret_cast<uintptr_t>(p) & (m - 1)) == 0; };
+    a.vec_ok = (W % 4 == 0) && al(label_out, 4) && al(conf16_out, 8) && al(conf32_out, 16) && al(label_thr_out, 4);
+    a.TY = 0; a.NR = 0;
+
+    if (h == H && w == W && flip == TSS_FLIP_NONE && !g_pl_force_tile) {
+        // full-resolution input: straight 128-bit loads, no staging
+        a.vec_ok = a.vec_ok && ((static_cast<int64_t>(H) * W) % 4 == 0) && al(src, 16);
+        if (num_classes <= 13) return num_classes == 13 ? launch_direct<13>(a, n_img, st) : launch_direct<13>(a, n_img, st);
+        if (num_classes <= 19) return launch_direct<19>(a, n_img, st);
+        return launch_direct<TSS_MAX_CLASSES>(a, n_img, st);
+    }
+
+    // tile height: the largest of {64,32,16,8} whose staged rows fit the shared-memory budget
+    const int planes = flip != TSS_FLIP_NONE ? 2 : 1;
+    const size_t budget_soft = 100 * 1024, budget_hard = 220 * 1024;
+    int best_ty = 0, best_nr = 0;
+    size_t best_sm = 0;
+    const int tys[4] = {64, 32, 16, 8};
+    for (int pass = 0; pass < 2 && !best_ty; ++pass) {
+        for (int k = 0; k < 4 && !best_ty; ++k) {
+            const int TY = tys[k];
+            int nr = 1;
+            for (int y0 = 0; y0 < H; y0 += TY) {  // exact row span with the kernel's own fp32 arithmetic
+                const int ylast = (y0 + TY - 1 < H ? y0 + TY - 1 : H - 1);
+                int rb = static_cast<int>(a.sy * static_cast<float>(y0));
+                if (rb > h - 1) rb = h - 1;
+                int i0 = static_cast<int>(a.sy * static_cast<float>(ylast));
+                if (i0 > h - 1) i0 = h - 1;
+                const int i1 = i0 + (i0 < h - 1 ? 1 : 0);
+                if (i1 - rb + 1 > nr) nr = i1 - rb + 1;
+            }
+            const size_t sm = static_cast<size_t>(planes) * num_classes * nr * kTX * sizeof(float);
+            if (sm <= (pass == 0 ? budget_soft : budget_hard)) {
+                best_ty = TY; best_nr = nr; best_sm = sm;
+            }
+        }
+    }
+    TSS_REQUIRE(best_ty != 0, TSS_E_ARG, "tss_pseudo_label: tile does not fit shared memory (C=%d, scale %f)", num_classes, a.sy);
+    a.TY = best_ty;
+    a.NR = best_nr;
+    if (num_classes <= 13) return launch_tile<13>(a, n_img, best_sm, st);
+    if (num_classes <= 19) return launch_tile<19>(a, n_img, best_sm, st);
+    return launch_tile<TSS_MAX_CLASSES>(a, n_img, best_sm, st);
+}
+
+extern "C" int tss_softmax_nchw(const float* logits, float* probs, int64_t n_img, int num_classes, int64_t plane,
+                                void* stream) {
+    using namespace tss;
+    TSS_REQUIRE(logits && probs && n_img >= 0 && plane > 0, TSS_E_ARG, "tss_softmax_nchw: bad arguments");
+    TSS_REQUIRE(num_classes >= 1 && num_classes <= TSS_MAX_CLASSES, TSS_E_CLASSES, "tss_softmax_nchw: num_classes %d", num_classes);
+    if (n_img == 0) return TSS_OK;
+    const int64_t total = n_img * plane;
+    int64_t blocks = (total + 255) / 256;
+    if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;
+    if (num_classes <= 13) softmax_nchw_kernel<13><<<static_cast<int>(blocks), 256, 0, as_stream(stream)>>>(logits, probs, n_img, num_classes, plane);
+    else if (num_classes <= 19) softmax_nchw_kernel<19><<<static_cast<int>(blocks), 256, 0, as_stream(stream)>>>(logits, probs, n_img, num_classes, plane);
+    else softmax_nchw_kernel<TSS_MAX_CLASSES><<<static_cast<int>(blocks), 256, 0, as_stream(stream)>>>(logits, probs, n_img, num_classes, plane);
+    TSS_LAUNCH_CHECK("tss_softmax_nchw");
+    return TSS_OK;
+}
+
+extern "C" int tss_upsample_bilinear(const float* src, float* dst, int64_t planes, int h, int w, int H, int W, void* stream) {
+    using namespace tss;
+    TSS_REQUIRE(src && dst && planes >= 0 && h > 0 && w > 0 && H > 0 && W > 0, TSS_E_ARG, "tss_upsample_bilinear: bad arguments");
+    TSS_REQUIRE(H <= 65535, TSS_E_ARG, "tss_upsample_bilinear: H too large");
+    if (planes == 0) return TSS_OK;
+    dim3 grid((W + 255) / 256, H, static_cast<unsigned>(planes < 64 ? planes : 64));
+    upsample_kernel<<<grid, 256, 0, as_stream(stream)>>>(src, dst, planes, h, w, H, W, scale_of(h, H), scale_of(w, W));
+    TSS_LAUNCH_CHECK("tss_upsample_bilinear");
+    return TSS_OK;
+}
+
+extern "C" int tss_threshold_labels(const uint8_t* label_in, const uint16_t* conf16, int64_t n, int num_classes,
+                                    const float* thr_host, const uint8_t* keep_host, int ignore_index,
+                                    uint8_t* label_out, void* stream) {
+    using namespace tss;
+    TSS_REQUIRE(label_in && label_out && n >= 0, TSS_E_ARG, "tss_threshold_labels: bad arguments");
+    TSS_REQUIRE(thr_host == nullptr || conf16 != nullptr, TSS_E_ARG, "tss_threshold_labels: thresholds without conf");
+    TSS_REQUIRE(num_classes >= 1 && num_classes <= TSS_MAX_CLASSES, TSS_E_CLASSES, "tss_threshold_labels: num_classes %d", num_classes);
+    TSS_REQUIRE(ignore_index >= 0 && ignore_index <= 255, TSS_E_ARG, "tss_threshold_labels: ignore_index outside uint8");
+    if (n == 0) return TSS_OK;
+    PLArgs a{};
+    a.C = num_classes;
+    fill_threshold(a, num_classes, thr_host, keep_host, ignore_index);
+    int64_t blocks = (n + 255) / 256;
+    if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;
+    threshold_kernel<<<static_cast<int>(blocks), 256, 0, as_stream(stream)>>>(label_in, reinterpret_cast<const __half*>(conf16), n, a, label_out);
+    TSS_LAUNCH_CHECK("tss_threshold_labels");
+    return TSS_OK;
+}
+
+extern "C" int tss_gather_nearest_u8(const uint8_t* src, uint8_t* dst, int64_t planes, int h, int w, int H, int W,
+                                     const int32_t* ytab, const int32_t* xtab, void* stream) {
+    using namespace tss;
+    TSS_REQUIRE(src && dst && ytab && xtab && planes >= 0 && h > 0 && w > 0 && H > 0 && W > 0, TSS_E_ARG,
+                "tss_gather_nearest_u8: bad arguments");
+    TSS_REQUIRE(H <= 65535, TSS_E_ARG, "tss_gather_nearest_u8: H too large");
+    if (planes == 0) return TSS_OK;
+    dim3 grid((W + 255) / 256, H, static_cast<unsigned>(planes < 64 ? planes : 64));
+    gather_nearest_kernel<<<grid, 256, 0, as_stream(stream)>>>(src, dst, planes, h, w, H, W, ytab, xtab);
+    TSS_LAUNCH_CHECK("tss_gather_nearest_u8");
+    return TSS_OK;
+}

@@ -1,0 +1,410 @@
+"""Tensor-level host API over the C ABI (include/tss_b200.h).
+
+PyTorch is plumbing here: it owns device memory and the stream; every piece of label arithmetic runs in
+the hand-written sm_100a kernels of libtss_b200.so.  CPU tensors are rejected -- there is no fallback.
+"""
+from __future__ import annotations
+
+import ctypes
+from dataclasses import dataclass
+from typing import Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import TssError, check, lib  # noqa: F401
+
+MAX_CLASSES = 32
+PL_UP_SOFTMAX, PL_UP_ARGMAX, PL_PROB_UP, PL_PROB_UP_SOFTMAX = 0, 1, 2, 3
+FLIP_NONE, FLIP_CLASS, FLIP_WIDTH = 0, 1, 2
+UPDATE_MEAN, UPDATE_MOVING_AVERAGE = 0, 1
+_DT = {torch.uint8: 0, torch.int32: 1, torch.int64: 2}
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _dev(t: torch.Tensor, dtype=None, name: str = "tensor") -> torch.Tensor:
+    if not isinstance(t, torch.Tensor):
+        raise TypeError("%s: expected a torch.Tensor, got %s" % (name, type(t).__name__))
+    if not t.is_cuda:
+        raise TssError("%s is on %s: b200seg runs on CUDA only (no CPU fallback)" % (name, t.device))
+    if dtype is not None and t.dtype != dtype:
+        t = t.to(dtype)
+    return t.contiguous()
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return None if t is None else ctypes.c_void_p(t.data_ptr())
+
+
+def _label_tensor(t: torch.Tensor, name: str) -> torch.Tensor:
+    t = _dev(t, name=name)
+    if t.dtype not in _DT:
+        t = t.to(torch.int64)
+    return t
+
+
+# ------------------------------------------------------------------------------------------- A14
+def confusion_matrix(pred: torch.Tensor, gt: torch.Tensor, num_classes: int,
+                     hist: Optional[torch.Tensor] = None, bad: Optional[torch.Tensor] = None):
+    """hist[C,C] int64 (+= when given), rows = ground truth.  Returns (hist, bad_keys) device tensors."""
+    pred, gt = _label_tensor(pred, "pred"), _label_tensor(gt, "gt")
+    if pred.dtype != gt.dtype:
+        pred, gt = pred.to(torch.int64), gt.to(torch.int64)
+    if pred.numel() != gt.numel():
+        raise ValueError("pred and gt differ in size: %d vs %d" % (pred.numel(), gt.numel()))
+    if hist is None:
+        hist = torch.zeros(num_classes, num_classes, dtype=torch.int64, device=pred.device)
+    if bad is None:
+        bad = torch.zeros(1, dtype=torch.int64, device=pred.device)
+    check(lib().tss_confusion(_ptr(pred), _ptr(gt), _DT[pred.dtype], pred.numel(), num_classes, _ptr(hist),
+                              _ptr(bad), _stream()), "tss_confusion")
+    return hist, bad
+
+
+# ------------------------------------------------------------------------------------------- A1-A4
+def softmax_nchw(logits: torch.Tensor) -> torch.Tensor:
+    x = _dev(logits, torch.float32, "logits")
+    n, c = x.shape[0], x.shape[1]
+    plane = x[0, 0].numel()
+    out = torch.empty_like(x)
+    check(lib().tss_softmax_nchw(_ptr(x), _ptr(out), n, c, plane, _stream()), "tss_softmax_nchw")
+    return out
+
+
+def _host_tables(num_classes, thr, keep):
+    thr_arr = keep_arr = None
+    if thr is not None:
+        thr_np = np.asarray(thr, dtype=np.float32)
+        if thr_np.ndim == 0:
+            thr_np = np.full(num_classes, float(thr_np), np.float32)
+        if thr_np.size != num_classes:
+            raise ValueError("thr must be a scalar or have num_classes entries")
+        thr_arr = (ctypes.c_float * num_classes)(*thr_np.tolist())
+    if keep is not None:
+        mask = np.zeros(num_classes, np.uint8)
+        k = np.asarray(list(keep))
+        if k.dtype == np.bool_ and k.size == num_classes:
+            mask[:] = k
+        else:
+            mask[k.astype(np.int64)] = 1
+        keep_arr = (ctypes.c_uint8 * num_classes)(*mask.tolist())
+    return thr_arr, keep_arr
+
+
+@dataclass
+class PseudoLabels:
+    label: Optional[torch.Tensor]       # [N,H,W] uint8 argmax
+    conf16: Optional[torch.Tensor]      # [N,H,W] float16 confidence as the reference stores it
+    conf32: Optional[torch.Tensor]      # [N,H,W] float32 confidence before the storage cast
+    label_thr: Optional[torch.Tensor]   # [N,H,W] uint8 after the class-wise threshold / whitelist
+
+
+def pseudo_label(src: torch.Tensor, size: Optional[Sequence[int]] = None, mode: int = PL_UP_SOFTMAX,
+                 src_flip: Optional[torch.Tensor] = None, flip: int = FLIP_NONE, thr=None, keep=None,
+                 ignore_index: int = 255, want_label: bool = True, want_conf16: bool = True,
+                 want_conf32: bool = False, want_thr: Optional[bool] = None) -> PseudoLabels:
+    """Fused upsample -> softmax -> argmax/confidence -> storage casts -> threshold (tss_pseudo_label)."""
+    x = _dev(src, torch.float32, "src")
+    if x.dim() != 4:
+        raise ValueError("src must be [N,C,h,w]")
+    n, c, h, w = x.shape
+    H, W = (h, w) if size is None else (int(size[0]), int(size[1]))
+    x2 = None
+    if flip != FLIP_NONE:
+        if src_flip is None:
+            raise ValueError("flip requested without src_flip")
+        x2 = _dev(src_flip, torch.float32, "src_flip")
+        if x2.shape != x.shape:
+            raise ValueError("src_flip shape differs from src")
+    if want_thr is None:
+        want_thr = thr is not None or keep is not None
+    dev = x.device
+    label = torch.empty((n, H, W), dtype=torch.uint8, device=dev) if want_label else None
+    conf16 = torch.empty((n, H, W), dtype=torch.float16, device=dev) if want_conf16 else None
+    conf32 = torch.empty((n, H, W), dtype=torch.float32, device=dev) if want_conf32 else None
+    label_thr = torch.empty((n, H, W), dtype=torch.uint8, device=dev) if want_thr else None
+    thr_arr, keep_arr = _host_tables(c, thr, keep)
+    check(lib().tss_pseudo_label(_ptr(x), _ptr(x2), n, c, h, w, H, W, mode, flip, _ptr(label), _ptr(conf16),
+                                 _ptr(conf32), _ptr(label_thr),
+                                 ctypes.cast(thr_arr, ctypes.c_void_p) if thr_arr is not None else None,
+                                 ctypes.cast(keep_arr, ctypes.c_void_p) if keep_arr is not None else None,
+                                 int(ignore_index), _stream()), "tss_pseudo_label")
+    return PseudoLabels(label, conf16, conf32, label_thr)
+
+
+def upsample_bilinear(x: torch.Tensor, size: Sequence[int]) -> torch.Tensor:
+    """Bilinear, align_corners=True, of the last two dims of a contiguous fp32 tensor."""
+    x = _dev(x, torch.float32, "x")
+    h, w = x.shape[-2], x.shape[-1]
+    H, W = int(size[0]), int(size[1])
+    out = torch.empty(x.shape[:-2] + (H, W), dtype=torch.float32, device=x.device)
+    planes = x.numel() // (h * w) if h * w else 0
+    check(lib().tss_upsample_bilinear(_ptr(x), _ptr(out), planes, h, w, H, W, _stream()), "tss_upsample_bilinear")
+    return out
+
+
+def threshold_labels(label: torch.Tensor, conf16: Optional[torch.Tensor], num_classes: int, thr=None, keep=None,
+                     ignore_index: int = 255) -> torch.Tensor:
+    lab = _dev(label, torch.uint8, "label")
+    cf = None if conf16 is None else _dev(conf16, torch.float16, "conf16")
+    out = torch.empty_like(lab)
+    thr_arr, keep_arr = _host_tables(num_classes, thr, keep)
+    check(lib().tss_threshold_labels(_ptr(lab), _ptr(cf), lab.numel(), num_classes,
+                                     ctypes.cast(thr_arr, ctypes.c_void_p) if thr_arr is not None else None,
+                                     ctypes.cast(keep_arr, ctypes.c_void_p) if keep_arr is not None else None,
+                                     int(ignore_index), _ptr(out), _stream()), "tss_threshold_labels")
+    return out
+
+
+def pil_nearest_table(n_in: int, n_out: int) -> np.ndarray:
+    """Pillow NEAREST index rule: start 0.5*scale, accumulate += scale in double, truncate
+    (libImaging/Geometry.c ImagingScaleAffine; data/freiburg_dataset.py:124)."""
+    scale = float(n_in) / float(n_out)
+    pos = scale * 0.5
+    out = np.empty(n_out, np.int32)
+    for i in range(n_out):
+        out[i] = int(pos)
+        pos += scale
+    return np.minimum(out, n_in - 1).astype(np.int32)
+
+
+def torch_nearest_table(n_in: int, n_out: int) -> np.ndarray:
+    """ATen 'nearest' rule: floor(dst * float(in)/out) in fp32 (self_training.py:103)."""
+    scale = np.float32(n_in) / np.float32(n_out)
+    idx = np.floor(np.arange(n_out, dtype=np.float32) * scale).astype(np.int64)
+    return np.minimum(idx, n_in - 1).astype(np.int32)
+
+
+def resize_nearest_u8(label: torch.Tensor, size_hw: Sequence[int], rule: str = "pil") -> torch.Tensor:
+    lab = _dev(label, torch.uint8, "label")
+    h, w = lab.shape[-2], lab.shape[-1]
+    H, W = int(size_hw[0]), int(size_hw[1])
+    mk = pil_nearest_table if rule == "pil" else torch_nearest_table
+    ytab = torch.from_numpy(mk(h, H)).to(lab.device)
+    xtab = torch.from_numpy(mk(w, W)).to(lab.device)
+    out = torch.empty(lab.shape[:-2] + (H, W), dtype=torch.uint8, device=lab.device)
+    planes = lab.numel() // (h * w)
+    check(lib().tss_gather_nearest_u8(_ptr(lab), _ptr(out), planes, h, w, H, W, _ptr(ytab), _ptr(xtab), _stream()),
+          "tss_gather_nearest_u8")
+    return out
+
+
+# ------------------------------------------------------------------------------------------- A5/A6
+@dataclass
+class ClassMeans:
+    """Per-(image, class) masked means of one batch, all on device."""
+    vectors: torch.Tensor      # [N,C,K] fp32 (zero where not valid)
+    valid: torch.Tensor        # [N,C] uint8: passes the count>0 and count>=10 rules
+    vector_sum: torch.Tensor   # [N,C] fp32: sum over K (the reference skips updates whose sum is exactly 0)
+    count_all: torch.Tensor    # [N,C] int32 ungated one-hot pixel count
+    count_gated: torch.Tensor  # [N,C] int32 gated count (the divisor)
+    seg_label: torch.Tensor    # [N,P] uint8 class each pixel was summed into (255 = none)
+    sums: torch.Tensor         # [N,C,K] fp32 raw segmented sums
+
+
+def class_means(feat: torch.Tensor, logits: torch.Tensor, num_classes: int, labels_val: Optional[torch.Tensor] = None,
+                overflow_channel: Optional[int] = None, conf_thresh: Optional[float] = None,
+                use_conf_gate: bool = False, min_pixels: int = 10) -> ClassMeans:
+    f = _dev(feat, torch.float32, "feat")
+    x = _dev(logits, torch.float32, "logits")
+    n, k = f.shape[0], f.shape[1]
+    plane = f[0, 0].numel()
+    if x.shape[0] != n or x.shape[1] != num_classes or x[0, 0].numel() != plane:
+        raise ValueError("logits %s do not match feat %s / num_classes %d" % (tuple(x.shape), tuple(f.shape), num_classes))
+    lv = None
+    if labels_val is not None:
+        lv = _dev(labels_val, torch.float32, "labels_val")
+        if lv.numel() != n * plane:
+            raise ValueError("labels_val must be [N,1,h,w]")
+    dev = f.device
+    L = lib()
+    rec = torch.empty(max(int(L.tss_proto_records_bytes(n, plane)), 16), dtype=torch.uint8, device=dev)
+    seg = torch.empty((n, plane), dtype=torch.uint8, device=dev)
+    ca = torch.empty((n, num_classes), dtype=torch.int32, device=dev)
+    cg = torch.empty((n, num_classes), dtype=torch.int32, device=dev)
+    st = _stream()
+    check(L.tss_proto_labels(_ptr(x), _ptr(lv), n, num_classes, plane,
+                             num_classes if overflow_channel is None else int(overflow_channel),
+                             1 if use_conf_gate else 0, float(-1.0 if conf_thresh is None else conf_thresh),
+                             _ptr(seg), _ptr(ca), _ptr(cg), _ptr(rec), st), "tss_proto_labels")
+    sums = torch.empty((n, num_classes, k), dtype=torch.float32, device=dev)
+    check(L.tss_proto_accumulate(_ptr(f), _ptr(rec), n, k, plane, num_classes, _ptr(sums), st), "tss_proto_accumulate")
+    vec = torch.empty_like(sums)
+    valid = torch.empty((n, num_classes), dtype=torch.uint8, device=dev)
+    vsum = torch.empty((n, num_classes), dtype=torch.float32, device=dev)
+    check(L.tss_proto_finalize(_ptr(sums), _ptr(ca), _ptr(cg), n, num_classes, k, int(min_pixels), _ptr(vec), _ptr(valid),
+                               _ptr(vsum), st), "tss_proto_finalize")
+    return ClassMeans(vec, valid, vsum, ca, cg, seg, sums)
+
+
+def prototype_update(protos: torch.Tensor, num: torch.Tensor, means: ClassMeans, mode: int, start_mean: bool,
+                     momentum: float, cap: float = 3000.0) -> None:
+    """In-place sequential update of protos [C,K] / num [C] with one batch (reference list order)."""
+    for t, nm in ((protos, "protos"), (num, "num")):
+        if not (t.is_cuda and t.dtype == torch.float32 and t.is_contiguous()):
+            raise TssError("%s must be a contiguous fp32 CUDA tensor (updated in place)" % nm)
+    n, c, k = means.vectors.shape
+    if protos.shape != (c, k) or num.numel() != c:
+        raise ValueError("protos %s / num %s do not match means [%d,%d,%d]" % (tuple(protos.shape), tuple(num.shape), n, c, k))
+    check(lib().tss_proto_update(_ptr(protos), _ptr(num), _ptr(means.vectors), _ptr(means.valid), _ptr(means.vector_sum),
+                                 n, c, k, mode, 1 if start_mean else 0, float(momentum), float(cap), _stream()),
+          "tss_proto_update")
+
+
+def prototype_update_partial(means: ClassMeans, num_before: torch.Tensor, mode: int, start_mean: bool, momentum: float,
+                             first_index: Optional[torch.Tensor], total: Optional[torch.Tensor], cap: float = 3000.0):
+    """Closed-form (sharded) update.  first_index=None: returns the per-class contribution counts [C] int32.
+    Otherwise returns (partial [C,K], scale0 [C], num_after [C])."""
+    n, c, k = means.vectors.shape
+    dev = means.vectors.device
+    L = lib()
+    if first_index is None:
+        cnt = torch.empty(c, dtype=torch.int32, device=dev)
+        check(L.tss_proto_update_partial(_ptr(means.vectors), _ptr(means.valid), _ptr(means.vector_sum), n, c, k, mode,
+                                         1 if start_mean else 0, float(momentum), float(cap), None, None, None, _ptr(cnt),
+                                         None, None, None, _stream()), "tss_proto_update_partial")
+        return cnt
+    nb = _dev(num_before, torch.float32, "num_before")
+    fi = _dev(first_index, torch.int32, "first_index")
+    tot = _dev(total, torch.int32, "total")
+    partial = torch.empty((c, k), dtype=torch.float32, device=dev)
+    scale0 = torch.empty(c, dtype=torch.float32, device=dev)
+    num_after = torch.empty(c, dtype=torch.float32, device=dev)
+    check(L.tss_proto_update_partial(_ptr(means.vectors), _ptr(means.valid), _ptr(means.vector_sum), n, c, k, mode,
+                                     1 if start_mean else 0, float(momentum), float(cap), _ptr(nb), _ptr(fi), _ptr(tot),
+                                     None, _ptr(partial), _ptr(scale0), _ptr(num_after), _stream()),
+          "tss_proto_update_partial")
+    return partial, scale0, num_after
+
+
+# ------------------------------------------------------------------------------------------- A7/A8/A10
+def prototype_distance(feat: torch.Tensor, protos: torch.Tensor, temperature: float = 1.0, want_dist: bool = True,
+                       want_weight: bool = False, soft: Optional[torch.Tensor] = None,
+                       hard: Optional[torch.Tensor] = None, train_thred: float = 0.0, ignore_index: int = 255):
+    """Returns (dist [N,C,h,w] | None, weight [N,C,h,w] | None, label [N,1,h,w] int64 | None)."""
+    f = _dev(feat, torch.float32, "feat")
+    p = _dev(protos, torch.float32, "protos")
+    n, k, h, w = f.shape
+    c = p.shape[0]
+    if p.shape[1] != k:
+        raise ValueError("protos [C,%d] do not match feat channels %d" % (p.shape[1], k))
+    plane = h * w
+    dev = f.device
+    dist = torch.empty((n, c, h, w), dtype=torch.float32, device=dev) if want_dist else None
+    wt = torch.empty((n, c, h, w), dtype=torch.float32, device=dev) if want_weight else None
+    sf = hd = lab = None
+    hd_dt = 0
+    if soft is not None:
+        sf = _dev(soft, torch.float32, "soft")
+        if sf.shape != (n, c, h, w):
+            raise ValueError("soft %s must be [N,C,h,w] = %s" % (tuple(sf.shape), (n, c, h, w)))
+        lab = torch.empty((n, 1, h, w), dtype=torch.int64, device=dev)
+        if hard is not None:
+            hd = _label_tensor(hard, "hard")
+            if hd.numel() != n * plane:
+                raise ValueError("hard must have N*h*w elements")
+            hd_dt = _DT[hd.dtype]
+    check(lib().tss_proto_distance(_ptr(f), _ptr(p), n, k, plane, c, float(temperature), _ptr(dist), _ptr(wt), _ptr(sf),
+                                   _ptr(hd), hd_dt, float(train_thred), int(ignore_index), _ptr(lab), _stream()),
+          "tss_proto_distance")
+    return dist, wt, lab
+
+
+# ------------------------------------------------------------------------------------------- A11-A13
+def _loss_workspace(dev) -> torch.Tensor:
+    return torch.empty(int(lib().tss_loss_workspace_bytes()), dtype=torch.uint8, device=dev)
+
+
+class _CeRce(torch.autograd.Function):
+    """alpha * CE(ignore_index, mean) + beta * RCE, forward and input gradient in the CUDA kernels."""
+
+    @staticmethod
+    def forward(ctx, logits, target, ignore_index, alpha, beta, with_rce):
+        x = _dev(logits, torch.float32, "logits")
+        t = _label_tensor(target, "target")
+        n, c = x.shape[0], x.shape[1]
+        plane = x[0, 0].numel()
+        if t.numel() != n * plane:
+            raise ValueError("target must have N*H*W elements")
+        out = torch.empty(4, dtype=torch.float64, device=x.device)
+        check(lib().tss_ce_rce_fwd(_ptr(x), _ptr(t), _DT[t.dtype], n, c, plane, int(ignore_index), 1 if with_rce else 0,
+                                   _ptr(out), _ptr(_loss_workspace(x.device)), _stream()), "tss_ce_rce_fwd")
+        ctx.save_for_backward(x, t, out)
+        ctx.meta = (int(ignore_index), float(alpha), float(beta), bool(with_rce))
+        valid = out[2]
+        ce = (out[0] / valid).to(torch.float32)               # nan when nothing is valid, as torch
+        rce = (out[1] / (valid + 1e-6)).to(torch.float32)
+        total = alpha * ce + (beta * rce if with_rce else 0.0)
+        return total, ce, rce, out[3]
+
+    @staticmethod
+    def backward(ctx, g_total, g_ce, g_rce, _g_bad):
+        x, t, out = ctx.saved_tensors
+        ignore_index, alpha, beta, with_rce = ctx.meta
+        n, c = x.shape[0], x.shape[1]
+        plane = x[0, 0].numel()
+        valid = out[2]
+        gce = g_total * alpha + g_ce
+        grce = (g_total * beta if with_rce else torch.zeros_like(g_total)) + g_rce
+        scales = torch.stack([(gce.double() / valid), (grce.double() / (valid + 1e-6))]).to(torch.float32).contiguous()
+        grad = torch.empty_like(x)
+        check(lib().tss_ce_rce_bwd(_ptr(x), _ptr(t), _DT[t.dtype], n, c, plane, ignore_index, _ptr(scales), _ptr(grad),
+                                   _stream()), "tss_ce_rce_bwd")
+        return grad, None, None, None, None, None
+
+
+def cross_entropy(logits, target, ignore_index: int = -100) -> torch.Tensor:
+    """nn.CrossEntropyLoss(ignore_index, reduction='mean') on [N,C,...] logits."""
+    return _CeRce.apply(logits, target, ignore_index, 1.0, 0.0, False)[0]
+
+
+def ce_rce(logits, target, ignore_index: int, alpha: float, beta: float):
+    """(alpha*CE + beta*RCE, CE, RCE, bad_label_count) -- self_training.py:114-118."""
+    return _CeRce.apply(logits, target, ignore_index, alpha, beta, True)
+
+
+def reverse_cross_entropy(logits, target, ignore_index: int) -> torch.Tensor:
+    return _CeRce.apply(logits, target, ignore_index, 0.0, 1.0, True)[2]
+
+
+class _Focal(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logits, target, gamma, alpha, size_average):
+        x = _dev(logits, torch.float32, "logits")
+        t = _label_tensor(target, "target")
+        n, c = x.shape[0], x.shape[1]
+        plane = x[0, 0].numel() if x.dim() > 2 else 1
+        if x.dim() == 2:  # [M, C] rows: treat as N=M images of one pixel
+            plane = 1
+        a = None if alpha is None else _dev(alpha, torch.float32, "alpha")
+        out = torch.empty(4, dtype=torch.float64, device=x.device)
+        check(lib().tss_focal_fwd(_ptr(x), _ptr(t), _DT[t.dtype], n, c, plane, float(gamma), _ptr(a), _ptr(out),
+                                  _ptr(_loss_workspace(x.device)), _stream()), "tss_focal_fwd")
+        ctx.save_for_backward(x, t, out, a if a is not None else torch.empty(0, device=x.device))
+        ctx.meta = (float(gamma), a is not None, bool(size_average))
+        loss = out[0] / out[1] if size_average else out[0]
+        return loss.to(torch.float32), out[3]
+
+    @staticmethod
+    def backward(ctx, g, _g_bad):
+        x, t, out, a = ctx.saved_tensors
+        gamma, has_alpha, size_average = ctx.meta
+        n, c = x.shape[0], x.shape[1]
+        plane = x[0, 0].numel() if x.dim() > 2 else 1
+        scale = (g.double() / out[1] if size_average else g.double()).to(torch.float32).reshape(1).contiguous()
+        grad = torch.empty_like(x)
+        check(lib().tss_focal_bwd(_ptr(x), _ptr(t), _DT[t.dtype], n, c, plane, gamma, _ptr(a) if has_alpha else None,
+                                  _ptr(scale), _ptr(grad), _stream()), "tss_focal_bwd")
+        return grad, None, None, None, None
+
+
+def focal_loss(logits, target, gamma: float = 0.0, alpha: Optional[torch.Tensor] = None, size_average: bool = True):
+    return _Focal.apply(logits, target, gamma, alpha, size_average)[0]
+
+
+def launch_count() -> int:
+    return int(lib().tss_launch_count())
