@@ -1,0 +1,394 @@
+#!/usr/bin/env python
+"""bench.py -- pseudo-labelled px/s of the self-training label path (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+Workload (BASELINE.json configs[1], "cfg2"): one STEP = one batch of 16 synthetic Freiburg-shape frames
+(640x1920, 13 classes; DeepLabv2 1/8-stride(+1) logits [16,13,81,241] and 256-ch features
+[16,256,81,241]) through
+
+    1. fused bilinear upsample -> softmax -> argmax/confidence -> fp16 cast -> class-wise threshold +
+       whitelist  (uint8 label, fp16 confidence, thresholded uint8 label at 640x1920),
+    2. argmax label + per-(image, class) segmented feature means + sequential prototype update,
+    3. confusion-matrix accumulation of the labels against a uint8 ground-truth map (mIoU at the end).
+
+value = frames * 640 * 1920 / device time, inputs resident in HBM.  Images shard across ranks (weak
+scaling: 16 frames per rank per step); the only collectives are the prototype partial ([13,256] fp32 +
+counts, once per step) and the [13,13] int64 confusion matrix (once, inside the timed region).
+e2e = the same step through b200seg.dropin with pinned HOST buffers, H2D + D2H inside the timed region.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+
+METRIC = "pseudo-labelled px/sec (+proto update, mIoU)"
+UNIT = "px/s"
+CFG = dict(frames=16, H=640, W=1920, h=81, w=241, C=13, K=256, thr=0.3, keep=(5, 11), ignore=12)
+N_SETS = 4  # rotating input sets: 4 x (116 MB in + 79 MB out) = 780 MB working set >> 126 MB L2
+
+
+def workload_name():
+    return ("cfg2: Freiburg 1920x640, 13 classes, batch %d/GPU: fused upsample/softmax/argmax/threshold "
+            "pseudo-labels + 256-ch prototype update + confusion matrix" % CFG["frames"])
+
+
+def algorithmic_bytes():
+    """Compulsory HBM traffic of one step per stage; every input element read once,
+    every output written once."""
+    c = CFG
+    n, P, px = c["frames"], c["h"] * c["w"], c["H"] * c["W"]
+    pl = 4 * c["C"] * P * n + n * px * (1 + 2 + 1)                  # logits in; label, conf16, label_thr out
+    proto = n * P * (4 * c["K"] + 4 * c["C"]) + 4 * n * c["C"] * (c["K"] + 1)
+    hist = n * px * 2                                               # uint8 pred + uint8 gt
+    return {"pseudo_label": pl, "prototype": proto, "confusion": hist}
+
+
+# ------------------------------------------------------------------------------------------------
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md clocks line)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.stop_flag, self.proc = index, [], threading.Event(), None
+
+    def run(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            for line in self.proc.stdout:
+                if self.stop_flag.is_set():
+                    break
+                self.samples.append((time.perf_counter(), [f.strip() for f in line.split(",")]))
+        except OSError:
+            pass
+
+    def finish(self, t0: float, t1: float):
+        self.stop_flag.set()
+        if self.proc is not None:
+            self.proc.kill()
+        rows = [f for (t, f) in self.samples if t0 <= t <= t1 and len(f) >= 6] or \
+               [f for (_, f) in self.samples if len(f) >= 6][-3:]
+        if not rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        mhz = sorted(int(r[0]) for r in rows if r[0].isdigit())
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in rows for i in range(4) if r[2 + i].lower().startswith("active")})
+        return {"sm_mhz": mhz[len(mhz) // 2] if mhz else None,
+                "sm_max_mhz": int(rows[0][1]) if rows[0][1].isdigit() else None, "reasons": reasons,
+                "samples": len(rows)}
+
+
+def measured_peak_gbs():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fh:
+            return float(json.load(fh)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs, STREAM-style copy)"
+    except (OSError, KeyError, ValueError):
+        return 6650.0, "fallback (B200_PROFILING.md, 6.65 TB/s)"
+
+
+# ------------------------------------------------------------------------------------------------
+# synthetic inputs (SURVEY.md section 8(d) cfg 2): logits 3*randn so that confidences straddle 0.3
+def make_inputs(device, seed: int, frames: int):
+    c = CFG
+    g = torch.Generator(device=device).manual_seed(seed)
+    logits = 3.0 * torch.randn(frames, c["C"], c["h"], c["w"], generator=g, device=device)
+    feat = torch.randn(frames, c["K"], c["h"], c["w"], generator=g, device=device)
+    gt = torch.randint(0, c["C"], (frames, c["H"], c["W"]), generator=g, device=device, dtype=torch.int16).to(torch.uint8)
+    return logits, feat, gt
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU reference arm: the oracle (= the reference's own torch/numpy op sequence) on the host cores
+def cpu_step(O, logits, feat, gt, bank, hist):
+    """One step of the same workload on CPU tensors, as the reference computes it:
+    upsample -> softmax -> max (self_training.py:53-55 order + generate_pseudo_label.py:85), fp16/uint8
+    storage casts (:91,:94), threshold block (data/freiburg_dataset.py:115-123), calculate_mean_vector +
+    update_objective_SingleVector loop (cal_prototype.py:72-75), _fast_hist (utils/eval_tools.py:4-9)."""
+    c = CFG
+    conf, lab = O.pseudo_label_upsampled(logits, (c["H"], c["W"]))
+    lab_u8 = lab.numpy().astype(np.uint8)
+    conf16 = conf.numpy().astype(np.float16)
+    for i in range(lab_u8.shape[0]):
+        O.threshold_hard_label(lab_u8[i], conf16[i], c["thr"], c["ignore"], keep=c["keep"])
+    vectors, ids = O.class_mean_vectors(feat, logits, c["C"])
+    for t, v in zip(ids, vectors):
+        bank.update(t, v, "mean")
+    g = gt.numpy()
+    for i in range(lab_u8.shape[0]):
+        hist += O.fast_hist(lab_u8[i].reshape(-1), g[i].reshape(-1), c["C"])
+
+
+def run_reference(args):
+    """--impl reference: rank 0 only, all host threads, each step a bounded sample of the workload."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import label_path as O
+
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    frames = 2  # of the 16-frame batch: ~1 s of CPU work per step
+    sets = [make_inputs("cpu", 1234 + s, frames) for s in range(2)]
+    bank = O.PrototypeBank(CFG["C"], CFG["K"])
+    hist = np.zeros((CFG["C"], CFG["C"]))
+    for i in range(args.warmup):
+        cpu_step(O, *sets[i % 2], bank, hist)
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        cpu_step(O, *sets[i % 2], bank, hist)
+    dt = time.perf_counter() - t0
+    miou = O.metrics_from_hist(hist, CFG["C"])[2]
+    px = frames * CFG["H"] * CFG["W"] * args.steps
+    val = px / dt
+    sample = "%d of %d frames per step (same shapes, same stages), %d steps" % (frames, CFG["frames"], args.steps)
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload_name(), "sample": sample, "miou": float(miou)},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0}))
+
+
+def cpu_baseline(budget_s: float = 12.0):
+    """The oracle timed on this box's host cores on a bounded sample of the same workload (rank 0, N=1)."""
+    from oracle import label_path as O
+
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    frames = 2
+    data = make_inputs("cpu", 1234, frames)
+    bank = O.PrototypeBank(CFG["C"], CFG["K"])
+    hist = np.zeros((CFG["C"], CFG["C"]))
+    cpu_step(O, *data, bank, hist)  # warm-up
+    reps, t0 = 0, time.perf_counter()
+    while reps < 3 or (time.perf_counter() - t0 < budget_s and reps < 50):
+        cpu_step(O, *data, bank, hist)
+        reps += 1
+    dt = time.perf_counter() - t0
+    return {"value": frames * CFG["H"] * CFG["W"] * reps / dt, "unit": UNIT, "cores": torch.get_num_threads(),
+            "kind": "port", "sample": "%d of %d frames per step x %d steps in %.1f s (oracle = the reference's own "
+            "torch/numpy op sequence, all host threads)" % (frames, CFG["frames"], reps, dt)}
+
+
+# ------------------------------------------------------------------------------------------------
+def run_b200(args):
+    import torch.distributed as dist
+
+    from b200seg import dropin, ops, sharding
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the B200 path has no CPU fallback (use --impl reference "
+                         "for the CPU arm)")
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    ws = int(os.environ.get("WORLD_SIZE", "1"))
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if ws > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    c = CFG
+    frames, C, size = c["frames"], c["C"], (c["H"], c["W"])
+    sets = [make_inputs(dev, 1234 + 1000 * rank + s, frames) for s in range(N_SETS)]
+
+    bank = sharding.ShardedPrototypes(C, c["K"], dev, ops.UPDATE_MEAN, True, 0.9999)
+    meter = dropin.ConfusionMeter(C, dev)
+
+    def stage_pl(i):
+        return ops.pseudo_label(sets[i % N_SETS][0], size=size, thr=c["thr"], keep=c["keep"], ignore_index=c["ignore"])
+
+    def stage_proto(i):
+        logits, feat, _ = sets[i % N_SETS]
+        means = ops.class_means(feat, logits, C)
+        if ws == 1:
+            ops.prototype_update(bank.protos, bank.num, means, bank.mode, bank.start_mean, bank.momentum)
+        else:
+            bank.update(means)
+
+    def stage_hist(i, pl):
+        ops.confusion_matrix(pl.label.reshape(-1), sets[i % N_SETS][2].reshape(-1), C, meter.hist, meter.bad)
+
+    def step(i):
+        pl = stage_pl(i)
+        stage_proto(i)
+        stage_hist(i, pl)
+        return pl
+
+    def fence():
+        torch.cuda.synchronize()
+        if ws > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    for i in range(max(args.warmup, 3)):
+        step(i)
+    fence()
+
+    # ---- device-resident timed region
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    if sampler:
+        sampler.start()
+        time.sleep(0.35)
+    meter.hist.zero_()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    launches0 = ops.launch_count()
+    fence()
+    t_wall0 = time.perf_counter()
+    ev0.record()
+    for i in range(args.steps):
+        step(i)
+    sharding.all_reduce_confusion(meter.hist, meter.bad)
+    ev1.record()
+    fence()
+    t_wall1 = time.perf_counter()
+    launches = ops.launch_count() - launches0
+    ms = torch.tensor([ev0.elapsed_time(ev1)], device=dev)
+    if ws > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms = float(ms.item())
+    miou = dropin.metrics_from_hist(meter.result(), C)[2]
+
+    # ---- per-stage device time (same rotation, CUDA events around every stage) -> roofline
+    stage_ms = {"pseudo_label": 0.0, "prototype": 0.0, "confusion": 0.0}
+    evs = []
+    for i in range(args.steps):
+        e = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+        e[0].record()
+        pl = stage_pl(i)
+        e[1].record()
+        stage_proto(i)
+        e[2].record()
+        stage_hist(i, pl)
+        e[3].record()
+        evs.append(e)
+    fence()
+    for e in evs:
+        for j, k in enumerate(stage_ms):
+            stage_ms[k] += e[j].elapsed_time(e[j + 1]) / args.steps
+    if sampler:
+        clocks = sampler.finish(t_wall0, time.perf_counter())
+
+    # ---- end to end through the drop-in API: pinned host buffers, H2D + D2H inside the timed region
+    e2e = run_e2e(args, dev, rank, ws, dist, dropin, ops, sharding)
+
+    if rank != 0:
+        if ws > 1:
+            dist.destroy_process_group()
+        return
+    px_step = frames * c["H"] * c["W"] * ws
+    alg = algorithmic_bytes()
+    top = max(stage_ms, key=stage_ms.get)
+    peak, peak_src = measured_peak_gbs()
+    achieved = alg[top] / (stage_ms[top] * 1e-3) / 1e9
+    out = {
+        "metric": METRIC, "value": px_step * args.steps / (ms * 1e-3), "unit": UNIT, "n_gpus": ws, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload_name(), "frames_per_gpu_per_step": frames, "logits": [frames, C, c["h"], c["w"]],
+                   "feat": [frames, c["K"], c["h"], c["w"]], "labels": [frames, c["H"], c["W"]],
+                   "l2": "inputs rotate over %d resident sets (780 MB working set > 126 MB L2)" % N_SETS,
+                   "parallelism": "image-sharded x%d; collectives: prototype partial [13,258] fp32 per step, "
+                                  "confusion [13,13] int64 once" % ws,
+                   "miou": float(miou)},
+        "stages_ms": {k: round(v, 5) for k, v in stage_ms.items()},
+        "stages_gbs": {k: round(alg[k] / (stage_ms[k] * 1e-3) / 1e9, 1) for k in stage_ms},
+        "roofline": {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": peak, "unit": "GB/s",
+                     "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                     "algorithmic_bytes_per_launch": alg[top]},
+        "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
+        "wall_ms_per_step": 1e3 * (t_wall1 - t_wall0) / args.steps,
+    }
+    if ws == 1 and not args.no_cpu_baseline:
+        out["cpu_baseline"] = cpu_baseline()
+    print(json.dumps(out))
+    if ws > 1:
+        dist.destroy_process_group()
+
+
+def run_e2e(args, dev, rank, ws, dist, dropin, ops, sharding):
+    c = CFG
+    frames, C, size = c["frames"], c["C"], (c["H"], c["W"])
+    host = []
+    for s in range(2):
+        lg, ft, gt = make_inputs("cpu", 4321 + 1000 * rank + s, frames)
+        host.append((lg.pin_memory(), ft.pin_memory(), gt.pin_memory()))
+    d_logits, d_feat, d_gt = (torch.empty_like(t, device=dev) for t in host[0])
+    h_label = torch.empty((frames,) + size, dtype=torch.uint8).pin_memory()
+    h_conf = torch.empty((frames,) + size, dtype=torch.float16).pin_memory()
+    cf = dropin.Class_Features(dev, C, c["K"])
+    meter = dropin.ConfusionMeter(C, dev)
+    h2d = sum(t.numel() * t.element_size() for t in host[0])
+    d2h = h_label.numel() + 2 * h_conf.numel()
+
+    def step(i):
+        lg, ft, gt = host[i % 2]
+        d_logits.copy_(lg, non_blocking=True)
+        d_feat.copy_(ft, non_blocking=True)
+        d_gt.copy_(gt, non_blocking=True)
+        pl = dropin.pseudo_label_batch(d_logits, size=size, thr=c["thr"], keep=c["keep"], ignore_index=c["ignore"])
+        if ws == 1:
+            cf.update_from_batch(d_feat, d_logits)
+        else:
+            cf.class_means(d_feat, d_logits)  # sharded update is exercised by the device arm; means are the traffic
+        meter.add(pl.label, d_gt)
+        h_label.copy_(pl.label_thr, non_blocking=True)
+        h_conf.copy_(pl.conf16, non_blocking=True)
+
+    for i in range(3):
+        step(i)
+    torch.cuda.synchronize()
+    if ws > 1:
+        dist.barrier()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    ev0.record()
+    for i in range(args.steps):
+        step(i)
+    sharding.all_reduce_confusion(meter.hist, meter.bad)
+    hist = meter.result()            # D2H of the [C,C] matrix: the metric the user reads
+    ev1.record()
+    torch.cuda.synchronize()
+    ms = torch.tensor([ev0.elapsed_time(ev1)], device=dev)
+    if ws > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms = float(ms.item())
+    return {"value": frames * c["H"] * c["W"] * ws * args.steps / (ms * 1e-3), "unit": UNIT,
+            "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h + hist.nbytes // max(args.steps, 1)),
+            "ms_per_step": ms / args.steps,
+            "api": "b200seg.dropin.pseudo_label_batch + Class_Features.update_from_batch + ConfusionMeter.add"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

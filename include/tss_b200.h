@@ -105,6 +105,11 @@ int tss_pseudo_label(const float* src, const float* src_flip, int64_t n_img, int
 int tss_upsample_bilinear(const float* src, float* dst, int64_t planes, int h, int w, int H, int W,
                           void* stream);
 
+/* adjoint of tss_upsample_bilinear (the backward of nn.Upsample at self_training.py:53-57,75):
+ * grad_in [planes,h,w] is zeroed by the call, then receives taps^T grad_out [planes,H,W]. */
+int tss_upsample_bilinear_adjoint(const float* grad_out, float* grad_in, int64_t planes, int h, int w,
+                                  int H, int W, void* stream);
+
 /* A4   threshold block on STORED labels: data/freiburg_dataset.py:115-123.  label_in uint8 [n],
  * conf16 fp16 bits [n] -> label_out uint8 [n]. */
 int tss_threshold_labels(const uint8_t* label_in, const uint16_t* conf16, int64_t n, int num_classes,
@@ -155,6 +160,8 @@ int tss_proto_finalize(const float* sums, const int32_t* count_all, const int32_
  * while num < 100; cap = 3000 in the reference. */
 #define TSS_UPDATE_MEAN 0
 #define TSS_UPDATE_MOVING_AVERAGE 1
+/* valid == NULL: every vector counts; vector_sum == NULL: the kernel sums each vector itself (the
+ * single-vector form update_objective_SingleVector(id, vector) passes protos + id*K, num + id, C = 1). */
 int tss_proto_update(float* protos, float* num, const float* vectors, const uint8_t* valid,
                      const float* vector_sum, int64_t n_img, int num_classes, int64_t channels, int mode,
                      int start_mean, double momentum, double cap, void* stream);
@@ -184,6 +191,20 @@ int tss_proto_distance(const float* feat, const float* protos, int64_t n_img, in
                        int64_t plane, int num_classes, float temperature, float* dist_out,
                        float* weight_out, const float* soft, const void* hard, int hard_dtype,
                        float train_thred, int ignore_index, int64_t* label_out, void* stream);
+
+/* A9   full2weak -- SelfTrain.full2weak (self_training.py:145-158): per image bilinear
+ * (align_corners=True) resize of feat [N,K,h,w] to (rh, rw), crop [y0:y0+TH, x0:x0+TW], optional mirror
+ * along W, concatenated -> out [N,K,TH,TW]; one gather pass, no resized intermediate.
+ * params: DEVICE int32 [N,6] rows {rh, rw, y0, x0, flip, 0} (the weak_params layout of
+ * utils/self_train_augmentation.py after the reference's int(./4) arithmetic, done by the host mirror). */
+int tss_full2weak(const float* feat, int64_t n_img, int64_t channels, int h, int w, const int32_t* params,
+                  int TH, int TW, float* out, void* stream);
+
+/* process_label -- cal_prototype.py:146-151 / self_training.py:204-209: one-hot [N, C+1, P] fp32 of a
+ * float label map [N,P]; labels >= C go to `overflow_channel` (C in Class_Features, args.ignore_index in
+ * SelfTrain; the reference's scatter_ raises when that exceeds C, and so does this call). */
+int tss_one_hot_overflow(const float* label, int64_t n_img, int64_t plane, int num_classes,
+                         int overflow_channel, float* out, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * A11/A12  cross-entropy with ignore_index and reverse cross-entropy -- nn.CrossEntropyLoss

@@ -26,6 +26,7 @@ _SIGNATURES = {
     "tss_pseudo_label": (c_int, [c_vp, c_vp, c_i64, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_vp, c_vp,
                                  c_vp, c_vp, c_vp, c_vp, c_int, c_vp]),
     "tss_upsample_bilinear": (c_int, [c_vp, c_vp, c_i64, c_int, c_int, c_int, c_int, c_vp]),
+    "tss_upsample_bilinear_adjoint": (c_int, [c_vp, c_vp, c_i64, c_int, c_int, c_int, c_int, c_vp]),
     "tss_threshold_labels": (c_int, [c_vp, c_vp, c_i64, c_int, c_vp, c_vp, c_int, c_vp, c_vp]),
     "tss_gather_nearest_u8": (c_int, [c_vp, c_vp, c_i64, c_int, c_int, c_int, c_int, c_vp, c_vp, c_vp]),
     "tss_proto_records_bytes": (c_sz, [c_i64, c_i64]),
@@ -37,6 +38,8 @@ _SIGNATURES = {
                                          c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "tss_proto_distance": (c_int, [c_vp, c_vp, c_i64, c_i64, c_i64, c_int, c_f32, c_vp, c_vp, c_vp, c_vp, c_int,
                                    c_f32, c_int, c_vp, c_vp]),
+    "tss_full2weak": (c_int, [c_vp, c_i64, c_i64, c_int, c_int, c_vp, c_int, c_int, c_vp, c_vp]),
+    "tss_one_hot_overflow": (c_int, [c_vp, c_i64, c_i64, c_int, c_int, c_vp, c_vp]),
     "tss_loss_workspace_bytes": (c_sz, []),
     "tss_ce_rce_fwd": (c_int, [c_vp, c_vp, c_int, c_i64, c_int, c_i64, c_int, c_int, c_vp, c_vp, c_vp]),
     "tss_ce_rce_bwd": (c_int, [c_vp, c_vp, c_int, c_i64, c_int, c_i64, c_int, c_vp, c_vp, c_vp]),

@@ -284,10 +284,24 @@ proto_update_kernel(float* __restrict__ protos, float* __restrict__ num, const f
                     const uint8_t* __restrict__ valid, const float* __restrict__ vector_sum, int64_t N, int C,
                     int64_t K, int mode, int start_mean, float m, float one_minus_m, float cap) {
     const int c = blockIdx.x;
+    __shared__ float red[8];
     float cnt = num[c];
     for (int64_t n = 0; n < N; ++n) {
         const int64_t nc = n * C + c;
-        if (!valid[nc] || vector_sum[nc] == 0.f) continue;
+        if (valid != nullptr && !valid[nc]) continue;
+        if (vector_sum != nullptr) {
+            if (vector_sum[nc] == 0.f) continue;
+        } else {  // single-vector form: the `vector.sum() == 0` test is evaluated here
+            float s = 0.f;
+            for (int64_t k = threadIdx.x; k < K; k += 256) s += vectors[nc * K + k];
+            s = warp_sum(s);
+            __syncthreads();
+            if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+            __syncthreads();
+            float tot = 0.f;
+            for (int w = 0; w < 8; ++w) tot += red[w];
+            if (tot == 0.f) continue;
+        }
         const bool mean = (mode == TSS_UPDATE_MEAN) || (start_mean && cnt < 100.f);
         const float* v = vectors + nc * K;
         if (mean) {
@@ -449,7 +463,7 @@ extern "C" int tss_proto_update(float* protos, float* num, const float* vectors,
                                 const float* vector_sum, int64_t n_img, int num_classes, int64_t channels, int mode,
                                 int start_mean, double momentum, double cap, void* stream) {
     using namespace tss;
-    TSS_REQUIRE(protos && num && vectors && valid && vector_sum, TSS_E_ARG, "tss_proto_update: null pointer");
+    TSS_REQUIRE(protos && num && vectors, TSS_E_ARG, "tss_proto_update: null pointer");
     TSS_REQUIRE(n_img >= 0 && channels > 0 && num_classes >= 1 && num_classes <= TSS_MAX_CLASSES, TSS_E_ARG, "tss_proto_update: bad extents");
     TSS_REQUIRE(mode == TSS_UPDATE_MEAN || mode == TSS_UPDATE_MOVING_AVERAGE, TSS_E_ARG, "tss_proto_update: bad mode %d", mode);
     if (n_img == 0) return TSS_OK;

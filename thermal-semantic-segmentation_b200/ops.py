@@ -147,6 +147,18 @@ def upsample_bilinear(x: torch.Tensor, size: Sequence[int]) -> torch.Tensor:
     return out
 
 
+def upsample_bilinear_adjoint(grad_out: torch.Tensor, in_hw: Sequence[int]) -> torch.Tensor:
+    """Backward of upsample_bilinear: grad wrt the low-resolution input."""
+    g = _dev(grad_out, torch.float32, "grad_out")
+    H, W = g.shape[-2], g.shape[-1]
+    h, w = int(in_hw[0]), int(in_hw[1])
+    out = torch.empty(g.shape[:-2] + (h, w), dtype=torch.float32, device=g.device)
+    planes = g.numel() // (H * W) if H * W else 0
+    check(lib().tss_upsample_bilinear_adjoint(_ptr(g), _ptr(out), planes, h, w, H, W, _stream()),
+          "tss_upsample_bilinear_adjoint")
+    return out
+
+
 def threshold_labels(label: torch.Tensor, conf16: Optional[torch.Tensor], num_classes: int, thr=None, keep=None,
                      ignore_index: int = 255) -> torch.Tensor:
     lab = _dev(label, torch.uint8, "label")
@@ -281,6 +293,73 @@ def prototype_update_partial(means: ClassMeans, num_before: torch.Tensor, mode: 
     return partial, scale0, num_after
 
 
+def prototype_update_single(protos: torch.Tensor, num: torch.Tensor, cls: int, vector: torch.Tensor, mode: int,
+                            start_mean: bool, momentum: float, cap: float = 3000.0) -> None:
+    """update_objective_SingleVector(id, vector): one vector into row `cls`, in place, no host sync (the
+    `vector.sum() == 0` skip is evaluated inside the kernel)."""
+    for t, nm in ((protos, "protos"), (num, "num")):
+        if not (t.is_cuda and t.dtype == torch.float32 and t.is_contiguous()):
+            raise TssError("%s must be a contiguous fp32 CUDA tensor (updated in place)" % nm)
+    c, k = protos.shape
+    if not 0 <= int(cls) < c:
+        raise IndexError("class id %d outside [0, %d)" % (cls, c))
+    v = _dev(vector, torch.float32, "vector").reshape(-1)
+    if v.numel() != k:
+        raise ValueError("vector has %d elements, prototypes have %d channels" % (v.numel(), k))
+    row = ctypes.c_void_p(protos.data_ptr() + int(cls) * k * 4)
+    cnt = ctypes.c_void_p(num.data_ptr() + int(cls) * 4)
+    check(lib().tss_proto_update(row, cnt, _ptr(v), None, None, 1, 1, k, mode, 1 if start_mean else 0,
+                                 float(momentum), float(cap), _stream()), "tss_proto_update")
+
+
+def one_hot_overflow(label: torch.Tensor, num_classes: int, overflow_channel: int) -> torch.Tensor:
+    """process_label: float label map [N,1,h,w] -> one-hot [N,C+1,h,w] fp32."""
+    lab = _dev(label, torch.float32, "label")
+    if lab.dim() != 4 or lab.shape[1] != 1:
+        raise ValueError("label must be [N,1,h,w]")
+    n, _, a, b = lab.shape
+    out = torch.empty((n, num_classes + 1, a, b), dtype=torch.float32, device=lab.device)
+    check(lib().tss_one_hot_overflow(_ptr(lab), n, a * b, num_classes, int(overflow_channel), _ptr(out), _stream()),
+          "tss_one_hot_overflow")
+    return out
+
+
+def weak_param_table(weak_params, n: int):
+    """The reference's int(./4) arithmetic on weak_params (self_training.py:148-152) -> rows
+    {rh, rw, y0, x0, flip, 0} plus each image's crop extent after Python's slice clipping."""
+    sized, crop, flip = weak_params["RandomSized"], weak_params["RandomCrop"], weak_params["RandomHorizontallyFlip"]
+    rows, extents = [], []
+    for i in range(n):
+        hh, ww = float(sized[0][i]), float(sized[1][i])
+        rh, rw = int(hh / 4), int(ww / 4)
+        y1, y2, x1, x2 = (float(crop[j][i]) for j in range(4))
+        ys, th, xs, tw = int(y1 / 4), int((y2 - y1) / 4), int(x1 / 4), int((x2 - x1) / 4)
+        th_eff = max(0, min(ys + th, rh) - min(ys, rh))
+        tw_eff = max(0, min(xs + tw, rw) - min(xs, rw))
+        rows.append([rh, rw, ys, xs, 1 if bool(flip[i]) else 0, 0])
+        extents.append((th_eff, tw_eff))
+    return np.asarray(rows, np.int32).reshape(n, 6), extents
+
+
+def full2weak(feat: torch.Tensor, weak_params) -> torch.Tensor:
+    """SelfTrain.full2weak in one gather pass (tss_full2weak)."""
+    f = _dev(feat, torch.float32, "feat")
+    n, k, h, w = f.shape
+    table, extents = weak_param_table(weak_params, n)
+    if len(set(extents)) != 1:
+        raise RuntimeError("full2weak: crops differ in size across the batch %s (torch.cat raises in the reference)"
+                           % sorted(set(extents)))
+    th, tw = extents[0]
+    if th <= 0 or tw <= 0:
+        raise RuntimeError("full2weak: empty crop %s" % (extents[0],))
+    if (table[:, 0] < 1).any() or (table[:, 1] < 1).any():
+        raise RuntimeError("full2weak: resized extent below 1")
+    params = torch.from_numpy(table).to(f.device)
+    out = torch.empty((n, k, th, tw), dtype=torch.float32, device=f.device)
+    check(lib().tss_full2weak(_ptr(f), n, k, h, w, _ptr(params), th, tw, _ptr(out), _stream()), "tss_full2weak")
+    return out
+
+
 # ------------------------------------------------------------------------------------------- A7/A8/A10
 def prototype_distance(feat: torch.Tensor, protos: torch.Tensor, temperature: float = 1.0, want_dist: bool = True,
                        want_weight: bool = False, soft: Optional[torch.Tensor] = None,
@@ -323,7 +402,7 @@ class _CeRce(torch.autograd.Function):
     """alpha * CE(ignore_index, mean) + beta * RCE, forward and input gradient in the CUDA kernels."""
 
     @staticmethod
-    def forward(ctx, logits, target, ignore_index, alpha, beta, with_rce):
+    def forward(ctx, logits, target, ignore_index, alpha, beta, with_rce, ce_sum=False):
         x = _dev(logits, torch.float32, "logits")
         t = _label_tensor(target, "target")
         n, c = x.shape[0], x.shape[1]
@@ -334,9 +413,9 @@ class _CeRce(torch.autograd.Function):
         check(lib().tss_ce_rce_fwd(_ptr(x), _ptr(t), _DT[t.dtype], n, c, plane, int(ignore_index), 1 if with_rce else 0,
                                    _ptr(out), _ptr(_loss_workspace(x.device)), _stream()), "tss_ce_rce_fwd")
         ctx.save_for_backward(x, t, out)
-        ctx.meta = (int(ignore_index), float(alpha), float(beta), bool(with_rce))
+        ctx.meta = (int(ignore_index), float(alpha), float(beta), bool(with_rce), bool(ce_sum))
         valid = out[2]
-        ce = (out[0] / valid).to(torch.float32)               # nan when nothing is valid, as torch
+        ce = (out[0] if ce_sum else out[0] / valid).to(torch.float32)   # mean: nan when nothing is valid, as torch
         rce = (out[1] / (valid + 1e-6)).to(torch.float32)
         total = alpha * ce + (beta * rce if with_rce else 0.0)
         return total, ce, rce, out[3]
@@ -344,22 +423,25 @@ class _CeRce(torch.autograd.Function):
     @staticmethod
     def backward(ctx, g_total, g_ce, g_rce, _g_bad):
         x, t, out = ctx.saved_tensors
-        ignore_index, alpha, beta, with_rce = ctx.meta
+        ignore_index, alpha, beta, with_rce, ce_sum = ctx.meta
         n, c = x.shape[0], x.shape[1]
         plane = x[0, 0].numel()
         valid = out[2]
         gce = g_total * alpha + g_ce
         grce = (g_total * beta if with_rce else torch.zeros_like(g_total)) + g_rce
-        scales = torch.stack([(gce.double() / valid), (grce.double() / (valid + 1e-6))]).to(torch.float32).contiguous()
+        scales = torch.stack([gce.double() if ce_sum else (gce.double() / valid),
+                              (grce.double() / (valid + 1e-6))]).to(torch.float32).contiguous()
         grad = torch.empty_like(x)
         check(lib().tss_ce_rce_bwd(_ptr(x), _ptr(t), _DT[t.dtype], n, c, plane, ignore_index, _ptr(scales), _ptr(grad),
                                    _stream()), "tss_ce_rce_bwd")
-        return grad, None, None, None, None, None
+        return grad, None, None, None, None, None, None
 
 
-def cross_entropy(logits, target, ignore_index: int = -100) -> torch.Tensor:
-    """nn.CrossEntropyLoss(ignore_index, reduction='mean') on [N,C,...] logits."""
-    return _CeRce.apply(logits, target, ignore_index, 1.0, 0.0, False)[0]
+def cross_entropy(logits, target, ignore_index: int = -100, reduction: str = "mean") -> torch.Tensor:
+    """nn.CrossEntropyLoss(ignore_index, reduction='mean'|'sum') on [N,C,...] logits."""
+    if reduction not in ("mean", "sum"):
+        raise ValueError("reduction must be 'mean' or 'sum'")
+    return _CeRce.apply(logits, target, ignore_index, 1.0, 0.0, False, reduction == "sum")[0]
 
 
 def ce_rce(logits, target, ignore_index: int, alpha: float, beta: float):

@@ -1,0 +1,109 @@
+"""Image-sharded form of the label path: one process per GPU, rank r owns a
+contiguous range of the global image order, and only three tiny tensors ever cross NVLink --
+
+  * the [C,C] int64 confusion matrix          all_reduce(SUM), exact and order-free;
+  * (sum loss, valid pixels)                  all_reduce(SUM), divided afterwards;
+  * the prototype update                      all_gather of per-class contribution counts [W,C] int32, then
+                                              all_reduce(SUM) of the closed-form weighted partial [C,K+2].
+
+The reference's update_objective_SingleVector (cal_prototype.py:153-169, self_training.py:211-227) is
+sequential in the global (image, class) order but linear in the per-(image, class) means, so each rank can
+weight its own means with the closed-form coefficient of their global position (computed in fp64 inside
+tss_proto_update_partial) and one all-reduce reproduces the sequential result to fp32 rounding.
+
+Pseudo-labels, distances, weights, rectified labels and per-pixel losses are per-image independent: no
+data-path collective exists for them.  torch.distributed is plumbing (NCCL on the GPUs, gloo in CPU tests).
+"""
+from __future__ import annotations
+
+from typing import Optional, Tuple
+
+import torch
+import torch.distributed as dist
+
+__all__ = ["shard_range", "world", "all_reduce_confusion", "all_reduce_loss", "prototype_positions",
+           "apply_prototype_partial", "ShardedPrototypes"]
+
+
+def world(group=None) -> Tuple[int, int]:
+    """(rank, world_size); (0, 1) when torch.distributed is not initialised."""
+    if dist.is_available() and dist.is_initialized():
+        return dist.get_rank(group), dist.get_world_size(group)
+    return 0, 1
+
+
+def shard_range(total: int, rank: int, world_size: int) -> Tuple[int, int]:
+    """Contiguous [begin, end) of rank's images; the first total % W ranks hold one more."""
+    if not 0 <= rank < world_size:
+        raise ValueError("rank %d outside [0, %d)" % (rank, world_size))
+    base, extra = divmod(int(total), int(world_size))
+    begin = rank * base + min(rank, extra)
+    return begin, begin + base + (1 if rank < extra else 0)
+
+
+def all_reduce_confusion(hist: torch.Tensor, bad: Optional[torch.Tensor] = None, group=None) -> torch.Tensor:
+    """Sum the per-rank [C,C] int64 matrices (and the out-of-range counter) in place."""
+    if world(group)[1] > 1:
+        if bad is not None:
+            packed = torch.cat([hist.reshape(-1), bad.reshape(-1)])
+            dist.all_reduce(packed, op=dist.ReduceOp.SUM, group=group)
+            hist.copy_(packed[:-bad.numel()].reshape(hist.shape))
+            bad.copy_(packed[-bad.numel():].reshape(bad.shape))
+        else:
+            dist.all_reduce(hist, op=dist.ReduceOp.SUM, group=group)
+    return hist
+
+
+def all_reduce_loss(loss_sum: torch.Tensor, valid: torch.Tensor, eps: float = 0.0, group=None) -> torch.Tensor:
+    """Global mean of a per-pixel loss from per-rank (sum, valid-count): CE uses eps=0, RCE eps=1e-6
+    (self_training.py:173)."""
+    packed = torch.stack([loss_sum.double().reshape(()), valid.double().reshape(())])
+    if world(group)[1] > 1:
+        dist.all_reduce(packed, op=dist.ReduceOp.SUM, group=group)
+    return (packed[0] / (packed[1] + eps)).to(torch.float32)
+
+
+def prototype_positions(local_counts: torch.Tensor, group=None) -> Tuple[torch.Tensor, torch.Tensor]:
+    """local_counts [C] int32 = how many (image, class) vectors of THIS rank's batch contribute per class.
+    Returns (first_index [C], total [C]) int32: where this rank's contributions start in the global order of
+    this step (ranks hold consecutive image ranges, so rank order = image order) and the global count."""
+    rank, ws = world(group)
+    counts = local_counts.to(torch.int32).contiguous()
+    if ws == 1:
+        return torch.zeros_like(counts), counts.clone()
+    gathered = [torch.empty_like(counts) for _ in range(ws)]
+    dist.all_gather(gathered, counts, group=group)
+    table = torch.stack(gathered)                       # [W, C]
+    first = table[:rank].sum(dim=0, dtype=torch.int32) if rank > 0 else torch.zeros_like(counts)
+    return first.contiguous(), table.sum(dim=0, dtype=torch.int32).contiguous()
+
+
+def apply_prototype_partial(protos: torch.Tensor, num: torch.Tensor, partial: torch.Tensor, scale0: torch.Tensor,
+                            num_after: torch.Tensor, group=None) -> None:
+    """protos = scale0 * protos + sum_ranks(partial); num = num_after (identical on every rank).  In place."""
+    if world(group)[1] > 1:
+        dist.all_reduce(partial, op=dist.ReduceOp.SUM, group=group)
+    protos.mul_(scale0.reshape(-1, 1)).add_(partial)
+    num.copy_(num_after)
+
+
+class ShardedPrototypes:
+    """A prototype bank replicated on every rank and updated from image-sharded batches.  Rank r's batch
+    must hold the images that precede rank r+1's in the reference's order (shard_range)."""
+
+    def __init__(self, num_classes: int, dim: int, device, mode: int, start_mean: bool, momentum: float,
+                 cap: float = 3000.0, group=None):
+        self.protos = torch.zeros(num_classes, dim, device=device)
+        self.num = torch.zeros(num_classes, device=device)
+        self.mode, self.start_mean, self.momentum, self.cap, self.group = mode, start_mean, momentum, cap, group
+
+    def update(self, means) -> None:
+        """means: ops.ClassMeans of this rank's batch.  Two kernels + (all_gather, all_reduce) per step."""
+        from . import ops
+
+        counts = ops.prototype_update_partial(means, self.num, self.mode, self.start_mean, self.momentum, None, None,
+                                              self.cap)
+        first, total = prototype_positions(counts, self.group)
+        partial, scale0, num_after = ops.prototype_update_partial(means, self.num, self.mode, self.start_mean,
+                                                                  self.momentum, first, total, self.cap)
+        apply_prototype_partial(self.protos, self.num, partial, scale0, num_after, self.group)
