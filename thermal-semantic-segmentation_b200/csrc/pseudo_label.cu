@@ -189,6 +189,180 @@ __global__ void __launch_bounds__(kPLThreads, 2) pl_tile_kernel(const PLArgs a) 
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// pl_up_kernel: the headline path (logits -> upsample -> softmax/argmax -> casts -> threshold) without
+// shared memory.  A warp owns a 64-pixel-wide column block and a contiguous range of output rows of the
+// flattened [N*H] row space; every lane owns TWO adjacent pixels (packed f32x2 arithmetic) and keeps the
+// horizontally interpolated values of the two source rows that bracket the current output row in
+// registers (2 rows x C classes x 2 px).  Walking down, a new source row is needed once per ~scale output
+// rows: 4 read-only loads per class (neighbouring lanes hit the same L1 lines -- the 16 MB low-res logits
+// are read from HBM once).  Per output pixel that leaves the vertical lerp, the class reduction and the
+// C exponentials -- the SFU (MUFU.EX2, 16 lanes/clk/SM) is the bound, not HBM.
+// Bit-identical to pl_tile_kernel (same operation order).
+constexpr int kUpBlockPx = 64;
+
+// value at base[off] with the address formed by ONE 32x32+64 multiply-add (off = plane/row offset in
+// elements, uniform across the CTA; base = the lane's own tap pointer)
+__device__ __forceinline__ float ldg_at(const float* base, unsigned off) {
+    const float* p;
+    asm("mad.wide.u32 %0, %1, 4, %2;" : "=l"(p) : "r"(off), "l"(base));
+    return __ldg(p);
+}
+
+template <int C>
+__device__ __forceinline__ void up_load_row(f32x2 (&dst)[C], const float* pa0, const float* pa1, const float* pb0,
+                                            const float* pb1, unsigned hw, unsigned row_off, f32x2 lx0, f32x2 lx1) {
+    unsigned off = row_off;  // one image's C planes stay below 2^30 elements (checked on the host)
+#pragma unroll
+    for (int c = 0; c < C; ++c, off += hw) {
+        const f32x2 lo = pack2(ldg_at(pa0, off), ldg_at(pb0, off));
+        const f32x2 hi = pack2(ldg_at(pa1, off), ldg_at(pb1, off));
+        dst[c] = fma2(lx1, hi, mul2(lx0, lo));  // lx1*b + (lx0*a), as the tile kernel and ATen order it
+    }
+}
+
+// Cooperative form for upsampling factors >= ~2.1: the 64 output columns of the warp touch at most 32
+// source columns, so ONE coalesced load per class fetches them (lane j holds column base+j) and every lane
+// picks its four taps with shuffles -- 1 load + 4 SHFL per class instead of 4 loads with 64-bit addresses.
+template <int C>
+__device__ __forceinline__ void up_load_row_coop(f32x2 (&dst)[C], const float* pcol, unsigned hw, unsigned row_off,
+                                                 int ra0, int ra1, int rb0, int rb1, f32x2 lx0, f32x2 lx1) {
+    unsigned off = row_off;
+    float x[C];
+#pragma unroll
+    for (int c = 0; c < C; ++c, off += hw) x[c] = ldg_at(pcol, off);
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+        const f32x2 lo = pack2(__shfl_sync(0xffffffffu, x[c], ra0), __shfl_sync(0xffffffffu, x[c], rb0));
+        const f32x2 hi = pack2(__shfl_sync(0xffffffffu, x[c], ra1), __shfl_sync(0xffffffffu, x[c], rb1));
+        dst[c] = fma2(lx1, hi, mul2(lx0, lo));
+    }
+}
+
+__device__ __forceinline__ float rcp_refined(float s) {
+    // s in [1, C]: MUFU.RCP (<= 1 ulp) + one Newton step; no special-case path
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(s));
+    return fmaf(r, fmaf(-s, r, 1.0f), r);
+}
+
+template <int C, int MODE, bool COOP>
+__global__ void __launch_bounds__(512, 1)
+pl_up_kernel(const PLArgs a, int64_t total_rows, int rows_per_seg, int col_blocks) {
+    // blockIdx.y = row segment, so the image / row bookkeeping and every row base address are uniform
+    // across the CTA (uniform datapath); warps of a CTA take neighbouring column blocks.
+    const int lane = threadIdx.x & 31;
+    const int cb = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (cb >= col_blocks) return;
+    const int64_t g0 = static_cast<int64_t>(blockIdx.y) * rows_per_seg;
+    const int64_t g1 = min(g0 + rows_per_seg, total_rows);
+    const int gx = cb * kUpBlockPx + 2 * lane;
+    const bool active = gx < a.W;              // W is even on this path: both pixels valid or neither
+    const int gxc = active ? gx : a.W - 2;
+    const Tap ta = make_tap(a.sx, gxc, a.w), tb = make_tap(a.sx, gxc + 1, a.w);
+    const f32x2 lx0 = pack2(ta.l0, tb.l0), lx1 = pack2(ta.l1, tb.l1);
+    const int64_t img_stride = static_cast<int64_t>(C) * a.h * a.w;
+    const unsigned hw = static_cast<unsigned>(a.h) * a.w;
+    // cooperative load: lane j holds source column base + j of the current row / class
+    const int base_col = make_tap(a.sx, min(cb * kUpBlockPx, a.W - 2), a.w).i0;
+    const int my_col = min(base_col + lane, a.w - 1);
+    const int ra0 = ta.i0 - base_col, ra1 = ta.i1 - base_col, rb0 = tb.i0 - base_col, rb1 = tb.i1 - base_col;
+
+    const float *pa0 = nullptr, *pa1 = nullptr, *pb0 = nullptr, *pb1 = nullptr, *pcol = nullptr;
+    f32x2 A[C], B[C];
+    int cur0 = -1, cur1 = -1;
+    int64_t n = g0 / a.H;
+    int y = static_cast<int>(g0 - n * a.H);
+    bool fresh = true;  // image changed (or first row): both bracketing rows must be loaded
+    for (int64_t g = g0; g < g1; ++g) {
+        const Tap ty = make_tap(a.sy, y, a.h);
+        if (fresh || ty.i0 != cur0 || ty.i1 != cur1) {
+            if (fresh) {
+                const float* img = a.src + n * img_stride;
+                if (COOP) {
+                    pcol = img + my_col;
+                } else {
+                    pa0 = img + ta.i0; pa1 = img + ta.i1; pb0 = img + tb.i0; pb1 = img + tb.i1;
+                }
+            }
+            if (!fresh && ty.i0 == cur1) {
+#pragma unroll
+                for (int c = 0; c < C; ++c) A[c] = B[c];
+            } else if (COOP) {
+                up_load_row_coop<C>(A, pcol, hw, static_cast<unsigned>(ty.i0 * a.w), ra0, ra1, rb0, rb1, lx0, lx1);
+            } else {
+                up_load_row<C>(A, pa0, pa1, pb0, pb1, hw, static_cast<unsigned>(ty.i0 * a.w), lx0, lx1);
+            }
+            if (ty.i1 == ty.i0) {
+#pragma unroll
+                for (int c = 0; c < C; ++c) B[c] = A[c];
+            } else if (COOP) {
+                up_load_row_coop<C>(B, pcol, hw, static_cast<unsigned>(ty.i1 * a.w), ra0, ra1, rb0, rb1, lx0, lx1);
+            } else {
+                up_load_row<C>(B, pa0, pa1, pb0, pb1, hw, static_cast<unsigned>(ty.i1 * a.w), lx0, lx1);
+            }
+            cur0 = ty.i0;
+            cur1 = ty.i1;
+            fresh = false;
+        }
+        // vertical lerp, two pixels per instruction
+        const f32x2 ly0 = pack2(ty.l0, ty.l0), ly1 = pack2(ty.l1, ty.l1);
+        float va[C], vb[C];
+#pragma unroll
+        for (int c = 0; c < C; ++c) unpack2(fma2(ly1, B[c], mul2(ly0, A[c])), va[c], vb[c]);
+        float ma = va[0], mb = vb[0];
+#pragma unroll
+        for (int c = 1; c < C; ++c) { ma = fmaxf(ma, va[c]); mb = fmaxf(mb, vb[c]); }
+        // lowest class equal to the maximum (torch.max tie rule); two half-length select chains per pixel
+        constexpr int HALF = C / 2;
+        int ia = -1, ib = -1, ja = C - 1, jb = C - 1;
+#pragma unroll
+        for (int c = HALF - 1; c >= 0; --c) {
+            ia = (va[c] == ma) ? c : ia;
+            ib = (vb[c] == mb) ? c : ib;
+        }
+#pragma unroll
+        for (int c = C - 2; c >= HALF; --c) {
+            ja = (va[c] == ma) ? c : ja;
+            jb = (vb[c] == mb) ? c : jb;
+        }
+        ia = ia >= 0 ? ia : ja;
+        ib = ib >= 0 ? ib : jb;
+        float ca = ma, cbv = mb;
+        if (MODE == TSS_PL_UP_SOFTMAX) {
+            const f32x2 l2e = pack2(kLog2e, kLog2e);
+            const f32x2 nmb = pack2(-(ma * kLog2e), -(mb * kLog2e));
+            f32x2 acc[4];
+#pragma unroll
+            for (int c = 0; c < C; ++c) {
+                float ta_, tb_;
+                unpack2(fma2(pack2(va[c], vb[c]), l2e, nmb), ta_, tb_);
+                const f32x2 e = pack2(ex2_approx(ta_), ex2_approx(tb_));
+                acc[c & 3] = c < 4 ? e : add2(acc[c & 3], e);
+            }
+            float sa, sb;
+            unpack2(add2(add2(acc[0], acc[1]), add2(acc[2], acc[3])), sa, sb);
+            ca = rcp_refined(sa);
+            cbv = rcp_refined(sb);
+        }
+        if (active) {
+            const int64_t off = (n * a.H + y) * static_cast<int64_t>(a.W) + gx;
+            const __half2 c16 = __floats2half2_rn(ca, cbv);
+            if (a.label) *reinterpret_cast<uint16_t*>(a.label + off) = static_cast<uint16_t>(ia | (ib << 8));
+            if (a.conf16) *reinterpret_cast<__half2*>(a.conf16 + off) = c16;
+            if (a.conf32) *reinterpret_cast<float2*>(a.conf32 + off) = make_float2(ca, cbv);
+            if (a.label_thr) {
+                const float2 cf = __half22float2(c16);
+                const bool ra = (a.has_thr && cf.x <= a.thr16[ia]) || !((a.keep_mask >> ia) & 1u);
+                const bool rb = (a.has_thr && cf.y <= a.thr16[ib]) || !((a.keep_mask >> ib) & 1u);
+                *reinterpret_cast<uint16_t*>(a.label_thr + off) =
+                    static_cast<uint16_t>((ra ? a.ignore : ia) | ((rb ? a.ignore : ib) << 8));
+            }
+        }
+        if (++y == a.H) { y = 0; ++n; fresh = true; }
+    }
+}
+
 // full-resolution input: grid-stride over pixel quads of the flattened [N, H*W] map
 template <int CT>
 __global__ void __launch_bounds__(256) pl_direct_kernel(const PLArgs a, int64_t n_img) {
@@ -342,6 +516,37 @@ static int launch_direct(const PLArgs& a, int64_t n_img, cudaStream_t st) {
 
 static int g_pl_force_tile = 0;
 
+template <int C, int MODE>
+static int launch_up(const PLArgs& a, int64_t n_img, cudaStream_t st) {
+    // One wave.  The kernel is compiled for <= 128 registers (512-thread bound), so an SM holds 16 warps;
+    // pick the warps per CTA that wastes the fewest column slots and keeps the SM fullest.
+    const int col_blocks = (a.W + kUpBlockPx - 1) / kUpBlockPx;
+    int best_wpc = 8, best_cps = 2;
+    double best_eff = -1.0;
+    for (int wpc = 4; wpc <= 16; ++wpc) {
+        const int cps = 16 / wpc;                                  // CTAs per SM by registers
+        const int gx = (col_blocks + wpc - 1) / wpc;
+        const double eff = (static_cast<double>(col_blocks) / (gx * wpc)) * (cps * wpc / 16.0);
+        if (eff > best_eff + 1e-9) { best_eff = eff; best_wpc = wpc; best_cps = cps; }
+    }
+    const int gx = (col_blocks + best_wpc - 1) / best_wpc;
+    const int64_t total_rows = n_img * a.H;
+    int64_t segs = static_cast<int64_t>(kNumSMs) * best_cps / gx;  // CTA slots / CTAs per row segment
+    if (segs < 1) segs = 1;
+    int64_t rps = (total_rows + segs - 1) / segs;
+    if (rps < 1) rps = 1;
+    segs = (total_rows + rps - 1) / rps;
+    TSS_REQUIRE(segs <= 65535, TSS_E_ARG, "tss_pseudo_label: too many row segments");
+    dim3 grid(static_cast<unsigned>(gx), static_cast<unsigned>(segs));
+    // the 64 output columns of a warp span floor(sx*63)+2 source columns at most (+1 for fp32 slack)
+    if ((a.sx * 63.0f + 3.0f) < 32.0f)
+        pl_up_kernel<C, MODE, true><<<grid, best_wpc * 32, 0, st>>>(a, total_rows, static_cast<int>(rps), col_blocks);
+    else
+        pl_up_kernel<C, MODE, false><<<grid, best_wpc * 32, 0, st>>>(a, total_rows, static_cast<int>(rps), col_blocks);
+    TSS_LAUNCH_CHECK("tss_pseudo_label(up)");
+    return TSS_OK;
+}
+
 }  // namespace tss
 
 extern "C" int tss_tune_pl_force_tile(int v) {
@@ -389,6 +594,17 @@ extern "C" int tss_pseudo_label(const float* src, const float* src_flip, int64_t
         if (num_classes <= 13) return num_classes == 13 ? launch_direct<13>(a, n_img, st) : launch_direct<13>(a, n_img, st);
         if (num_classes <= 19) return launch_direct<19>(a, n_img, st);
         return launch_direct<TSS_MAX_CLASSES>(a, n_img, st);
+    }
+
+    // register-resident fast path: logits in, no flip, even width, aligned outputs, C in {13, 19}
+    if (!g_pl_force_tile && flip == TSS_FLIP_NONE && (mode == TSS_PL_UP_SOFTMAX || mode == TSS_PL_UP_ARGMAX) &&
+        (W % 2 == 0) && W >= 2 && al(label_out, 2) && al(conf16_out, 4) && al(conf32_out, 8) && al(label_thr_out, 2) &&
+        (num_classes == 13 || num_classes == 19) && static_cast<int64_t>(num_classes) * h * w < (1ll << 30)) {
+        if (num_classes == 13)
+            return mode == TSS_PL_UP_SOFTMAX ? launch_up<13, TSS_PL_UP_SOFTMAX>(a, n_img, st)
+                                             : launch_up<13, TSS_PL_UP_ARGMAX>(a, n_img, st);
+        return mode == TSS_PL_UP_SOFTMAX ? launch_up<19, TSS_PL_UP_SOFTMAX>(a, n_img, st)
+                                         : launch_up<19, TSS_PL_UP_ARGMAX>(a, n_img, st);
     }
 
     // tile height: the largest of {64,32,16,8} whose staged rows fit the shared-memory budget

@@ -1,0 +1,48 @@
+"""Run one stage of the bench step a few times (for ncu / quick timing).  usage: prof_stage.py STAGE [reps]
+STAGE in pl | proto | hist | dist | ce | all."""
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import torch  # noqa: E402
+
+import bench  # noqa: E402
+from b200seg import ops  # noqa: E402
+
+stage = sys.argv[1] if len(sys.argv) > 1 else "all"
+reps = int(sys.argv[2]) if len(sys.argv) > 2 else 5
+c = bench.CFG
+dev = torch.device("cuda:0")
+sets = [bench.make_inputs(dev, 1234 + s, c["frames"]) for s in range(3)]
+protos = torch.zeros(c["C"], c["K"], device=dev)
+num = torch.zeros(c["C"], device=dev)
+hist = torch.zeros(c["C"], c["C"], dtype=torch.int64, device=dev)
+bad = torch.zeros(1, dtype=torch.int64, device=dev)
+pl0 = ops.pseudo_label(sets[0][0], size=(c["H"], c["W"]), thr=c["thr"], keep=c["keep"], ignore_index=c["ignore"])
+times = {}
+
+
+def timed(name, fn):
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    fn()
+    e1.record()
+    torch.cuda.synchronize()
+    times.setdefault(name, []).append(e0.elapsed_time(e1) * 1e3)
+
+
+for i in range(reps):
+    logits, feat, gt = sets[i % 3]
+    if stage in ("pl", "all"):
+        timed("pl", lambda: ops.pseudo_label(logits, size=(c["H"], c["W"]), thr=c["thr"], keep=c["keep"],
+                                             ignore_index=c["ignore"]))
+    if stage in ("proto", "all"):
+        def f():
+            m = ops.class_means(feat, logits, c["C"])
+            ops.prototype_update(protos, num, m, ops.UPDATE_MEAN, True, 0.9999)
+        timed("proto", f)
+    if stage in ("hist", "all"):
+        timed("hist", lambda: ops.confusion_matrix(pl0.label.reshape(-1), gt.reshape(-1), c["C"], hist, bad))
+for k, v in times.items():
+    print(k, "us:", " ".join("%.1f" % t for t in v))
