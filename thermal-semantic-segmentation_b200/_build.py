@@ -14,14 +14,15 @@ from concurrent.futures import ThreadPoolExecutor
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-OBJ_DIR = os.path.join(HERE, "build")
-LIB_PATH = os.path.join(HERE, "libtss_b200.so")
+OBJ_DIR = os.path.join(HERE, "build") if not os.environ.get("TSS_LIB") else os.environ["TSS_LIB"] + ".build"
+# TSS_LIB (tuning experiments only): build / load a variant library, compiled with the extra flags in TSS_NVCC_EXTRA
+LIB_PATH = os.environ.get("TSS_LIB") or os.path.join(HERE, "libtss_b200.so")
 STAMP = os.path.join(OBJ_DIR, "sources.sha256")
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
     "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr",
-]
+] + os.environ.get("TSS_NVCC_EXTRA", "").split()
 
 
 def _nvcc() -> str:

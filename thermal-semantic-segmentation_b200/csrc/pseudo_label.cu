@@ -35,6 +35,9 @@ struct PLArgs {
     int has_thr, ignore;
     unsigned int keep_mask;
     float thr16[TSS_MAX_CLASSES];  // thresholds already rounded to fp16 (numpy compares in fp16)
+    // one-lookup form of the threshold block: +inf for classes outside the whitelist (always rejected),
+    // -inf when no threshold is given (never rejected), else thr16
+    float thr_eff[TSS_MAX_CLASSES];
 };
 
 struct Tap {
@@ -44,11 +47,11 @@ struct Tap {
 // ATen area_pixel_compute_source_index, align_corners=True: src = scale * dst, all fp32
 __device__ __forceinline__ Tap make_tap(float scale, int dst, int n_in) {
     Tap t;
-    const float s = scale * static_cast<float>(dst);
+    const float s = __fmul_rn(scale, static_cast<float>(dst));  // rounded product: never contracted into the subtraction
     t.i0 = min(static_cast<int>(s), n_in - 1);
     t.i1 = t.i0 + (t.i0 < n_in - 1 ? 1 : 0);
-    t.l1 = s - static_cast<float>(t.i0);
-    t.l0 = 1.0f - t.l1;
+    t.l1 = __fsub_rn(s, static_cast<float>(t.i0));
+    t.l0 = __fsub_rn(1.0f, t.l1);
     return t;
 }
 
@@ -246,8 +249,47 @@ __device__ __forceinline__ float rcp_refined(float s) {
     return fmaf(r, fmaf(-s, r, 1.0f), r);
 }
 
-template <int C, int MODE, bool COOP>
-__global__ void __launch_bounds__(512, 1)
+// epilogue of one finished row: confidence, storage casts, threshold, stores.  OUTS = compile-time set of
+// outputs (bit 0 label, 1 conf16, 2 conf32, 3 label_thr) or -1 for run-time pointer tests; `off` = element
+// offset g*W + x of the pixel pair in every [N,H,W] output.
+constexpr int kOutsRuntime = -1;
+constexpr int kOutsPseudoLabel = 0b1011;  // label + conf16 + label_thr: the pseudo-label stage
+template <int MODE, int OUTS>
+__device__ __forceinline__ void up_emit(const PLArgs& a, bool valid, int64_t off, float sa, float sb, int ia, int ib) {
+    float ca = sa, cb = sb;
+    if (MODE == TSS_PL_UP_SOFTMAX) {
+        ca = rcp_refined(sa);
+        cb = rcp_refined(sb);
+    }
+    const bool w_label = OUTS == kOutsRuntime ? a.label != nullptr : (OUTS & 1) != 0;
+    const bool w_c16 = OUTS == kOutsRuntime ? a.conf16 != nullptr : (OUTS & 2) != 0;
+    const bool w_c32 = OUTS == kOutsRuntime ? a.conf32 != nullptr : (OUTS & 4) != 0;
+    const bool w_thr = OUTS == kOutsRuntime ? a.label_thr != nullptr : (OUTS & 8) != 0;
+    const __half2 c16 = __floats2half2_rn(ca, cb);
+    if (valid && w_label) *reinterpret_cast<uint16_t*>(a.label + off) = static_cast<uint16_t>(ia | (ib << 8));
+    if (valid && w_c16) *reinterpret_cast<__half2*>(a.conf16 + off) = c16;
+    if (valid && w_c32) *reinterpret_cast<float2*>(a.conf32 + off) = make_float2(ca, cb);
+    if (w_thr) {
+        const float2 cf = __half22float2(c16);
+        const int ta = (cf.x <= a.thr_eff[ia]) ? a.ignore : ia;
+        const int tb = (cf.y <= a.thr_eff[ib]) ? a.ignore : ib;
+        if (valid) *reinterpret_cast<uint16_t*>(a.label_thr + off) = static_cast<uint16_t>(ta | (tb << 8));
+    }
+}
+
+template <int C>
+struct UpCfg {  // register budget: 96 (20 warps/SM) holds C <= 13; 19 classes need the 128-register cap (16 warps/SM)
+#ifndef TSS_UP_PIPE
+#define TSS_UP_PIPE 0
+#endif
+#ifndef TSS_UP_WARPS13
+#define TSS_UP_WARPS13 16
+#endif
+    static constexpr int kWarpsPerSM = C <= 13 ? TSS_UP_WARPS13 : 16;
+};
+
+template <int C, int MODE, bool COOP, int OUTS>
+__global__ void __launch_bounds__(UpCfg<C>::kWarpsPerSM * 32, 1)
 pl_up_kernel(const PLArgs a, int64_t total_rows, int rows_per_seg, int col_blocks) {
     // blockIdx.y = row segment, so the image / row bookkeeping and every row base address are uniform
     // across the CTA (uniform datapath); warps of a CTA take neighbouring column blocks.
@@ -274,7 +316,12 @@ pl_up_kernel(const PLArgs a, int64_t total_rows, int rows_per_seg, int col_block
     int64_t n = g0 / a.H;
     int y = static_cast<int>(g0 - n * a.H);
     bool fresh = true;  // image changed (or first row): both bracketing rows must be loaded
-    for (int64_t g = g0; g < g1; ++g) {
+    bool p_valid = false;  // a finished row waits for its epilogue
+    int64_t p_off = 0;
+    float p_sa = 1.f, p_sb = 1.f;
+    int p_ia = 0, p_ib = 0;
+    int64_t off = g0 * a.W + gx;
+    for (int rows_left = static_cast<int>(g1 - g0); rows_left > 0; --rows_left) {
         const Tap ty = make_tap(a.sy, y, a.h);
         if (fresh || ty.i0 != cur0 || ty.i1 != cur1) {
             if (fresh) {
@@ -328,7 +375,7 @@ pl_up_kernel(const PLArgs a, int64_t total_rows, int rows_per_seg, int col_block
         }
         ia = ia >= 0 ? ia : ja;
         ib = ib >= 0 ? ib : jb;
-        float ca = ma, cbv = mb;
+        float sa = ma, sb = mb;  // UP_ARGMAX: the "confidence" is the max logit
         if (MODE == TSS_PL_UP_SOFTMAX) {
             const f32x2 l2e = pack2(kLog2e, kLog2e);
             const f32x2 nmb = pack2(-(ma * kLog2e), -(mb * kLog2e));
@@ -340,27 +387,24 @@ pl_up_kernel(const PLArgs a, int64_t total_rows, int rows_per_seg, int col_block
                 const f32x2 e = pack2(ex2_approx(ta_), ex2_approx(tb_));
                 acc[c & 3] = c < 4 ? e : add2(acc[c & 3], e);
             }
-            float sa, sb;
             unpack2(add2(add2(acc[0], acc[1]), add2(acc[2], acc[3])), sa, sb);
-            ca = rcp_refined(sa);
-            cbv = rcp_refined(sb);
         }
-        if (active) {
-            const int64_t off = (n * a.H + y) * static_cast<int64_t>(a.W) + gx;
-            const __half2 c16 = __floats2half2_rn(ca, cbv);
-            if (a.label) *reinterpret_cast<uint16_t*>(a.label + off) = static_cast<uint16_t>(ia | (ib << 8));
-            if (a.conf16) *reinterpret_cast<__half2*>(a.conf16 + off) = c16;
-            if (a.conf32) *reinterpret_cast<float2*>(a.conf32 + off) = make_float2(ca, cbv);
-            if (a.label_thr) {
-                const float2 cf = __half22float2(c16);
-                const bool ra = (a.has_thr && cf.x <= a.thr16[ia]) || !((a.keep_mask >> ia) & 1u);
-                const bool rb = (a.has_thr && cf.y <= a.thr16[ib]) || !((a.keep_mask >> ib) & 1u);
-                *reinterpret_cast<uint16_t*>(a.label_thr + off) =
-                    static_cast<uint16_t>((ra ? a.ignore : ia) | ((rb ? a.ignore : ib) << 8));
-            }
-        }
+        // Software pipeline: the reciprocal / casts / threshold / stores of THIS row are issued while the
+        // next row's lerps and exponentials run (they are independent instruction streams in one block).
+#if TSS_UP_PIPE
+        up_emit<MODE, OUTS>(a, p_valid, p_off, p_sa, p_sb, p_ia, p_ib);
+        p_valid = active;
+        p_off = off;
+        p_sa = sa; p_sb = sb; p_ia = ia; p_ib = ib;
+#else
+        up_emit<MODE, OUTS>(a, active, off, sa, sb, ia, ib);
+#endif
+        off += a.W;  // rows of consecutive images are contiguous in every [N,H,W] output
         if (++y == a.H) { y = 0; ++n; fresh = true; }
     }
+#if TSS_UP_PIPE
+    up_emit<MODE, OUTS>(a, p_valid, p_off, p_sa, p_sb, p_ia, p_ib);
+#endif
 }
 
 // full-resolution input: grid-stride over pixel quads of the flattened [N, H*W] map
@@ -482,7 +526,9 @@ static void fill_threshold(PLArgs& a, int C, const float* thr_host, const uint8_
     a.keep_mask = 0;
     for (int c = 0; c < TSS_MAX_CLASSES; ++c) {
         a.thr16[c] = (thr_host && c < C) ? __half2float(__float2half_rn(thr_host[c])) : 0.f;
-        if (c < C && (keep_host == nullptr || keep_host[c])) a.keep_mask |= 1u << c;
+        const bool kept = c < C && (keep_host == nullptr || keep_host[c]);
+        if (kept) a.keep_mask |= 1u << c;
+        a.thr_eff[c] = !kept ? INFINITY : (thr_host ? a.thr16[c] : -INFINITY);
     }
 }
 
@@ -518,15 +564,16 @@ static int g_pl_force_tile = 0;
 
 template <int C, int MODE>
 static int launch_up(const PLArgs& a, int64_t n_img, cudaStream_t st) {
-    // One wave.  The kernel is compiled for <= 128 registers (512-thread bound), so an SM holds 16 warps;
+    // One wave.  The kernel is compiled for a register cap that lets an SM hold UpCfg<C>::kWarpsPerSM warps;
     // pick the warps per CTA that wastes the fewest column slots and keeps the SM fullest.
     const int col_blocks = (a.W + kUpBlockPx - 1) / kUpBlockPx;
     int best_wpc = 8, best_cps = 2;
     double best_eff = -1.0;
-    for (int wpc = 4; wpc <= 16; ++wpc) {
-        const int cps = 16 / wpc;                                  // CTAs per SM by registers
+    constexpr int kW = UpCfg<C>::kWarpsPerSM;
+    for (int wpc = 4; wpc <= kW; ++wpc) {
+        const int cps = kW / wpc;                                  // CTAs per SM by registers
         const int gx = (col_blocks + wpc - 1) / wpc;
-        const double eff = (static_cast<double>(col_blocks) / (gx * wpc)) * (cps * wpc / 16.0);
+        const double eff = (static_cast<double>(col_blocks) / (gx * wpc)) * (cps * wpc / static_cast<double>(kW));
         if (eff > best_eff + 1e-9) { best_eff = eff; best_wpc = wpc; best_cps = cps; }
     }
     const int gx = (col_blocks + best_wpc - 1) / best_wpc;
@@ -539,10 +586,15 @@ static int launch_up(const PLArgs& a, int64_t n_img, cudaStream_t st) {
     TSS_REQUIRE(segs <= 65535, TSS_E_ARG, "tss_pseudo_label: too many row segments");
     dim3 grid(static_cast<unsigned>(gx), static_cast<unsigned>(segs));
     // the 64 output columns of a warp span floor(sx*63)+2 source columns at most (+1 for fp32 slack)
-    if ((a.sx * 63.0f + 3.0f) < 32.0f)
-        pl_up_kernel<C, MODE, true><<<grid, best_wpc * 32, 0, st>>>(a, total_rows, static_cast<int>(rps), col_blocks);
+    const bool coop = (a.sx * 63.0f + 3.0f) < 32.0f;
+    const bool pl_outs = MODE == TSS_PL_UP_SOFTMAX && a.label && a.conf16 && !a.conf32 && a.label_thr;
+    const int block = best_wpc * 32, r = static_cast<int>(rps);
+    if (coop && pl_outs)
+        pl_up_kernel<C, MODE, true, MODE == TSS_PL_UP_SOFTMAX ? kOutsPseudoLabel : kOutsRuntime><<<grid, block, 0, st>>>(a, total_rows, r, col_blocks);
+    else if (coop)
+        pl_up_kernel<C, MODE, true, kOutsRuntime><<<grid, block, 0, st>>>(a, total_rows, r, col_blocks);
     else
-        pl_up_kernel<C, MODE, false><<<grid, best_wpc * 32, 0, st>>>(a, total_rows, static_cast<int>(rps), col_blocks);
+        pl_up_kernel<C, MODE, false, kOutsRuntime><<<grid, block, 0, st>>>(a, total_rows, r, col_blocks);
     TSS_LAUNCH_CHECK("tss_pseudo_label(up)");
     return TSS_OK;
 }

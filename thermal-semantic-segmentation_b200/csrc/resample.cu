@@ -19,11 +19,11 @@ struct WeakParam {  // one row of the DEVICE int32 table [N, 6]
 };
 
 __device__ __forceinline__ void tap_of(float scale, int dst, int n_in, int& i0, int& i1, float& l0, float& l1) {
-    const float s = scale * static_cast<float>(dst);
+    const float s = __fmul_rn(scale, static_cast<float>(dst));  // rounded product: never contracted into the subtraction
     i0 = min(static_cast<int>(s), n_in - 1);
     i1 = i0 + (i0 < n_in - 1 ? 1 : 0);
-    l1 = s - static_cast<float>(i0);
-    l0 = 1.0f - l1;
+    l1 = __fsub_rn(s, static_cast<float>(i0));
+    l0 = __fsub_rn(1.0f, l1);
 }
 
 __global__ void __launch_bounds__(256)
