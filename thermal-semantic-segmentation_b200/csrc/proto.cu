@@ -132,8 +132,13 @@ struct AccSmem {
     static constexpr int rows_bytes = kStages * kKT * kRowStride * 4;
     static constexpr int rec_off = rows_bytes;
     static constexpr int bar_off = rec_off + kStages * kRecBytes;
-    static constexpr int total = bar_off + 2 * kStages * 8;
+    static constexpr int acc_off = bar_off + 2 * kStages * 8 + 16;          // [TSS_MAX_CLASSES][32] fp32
+    static constexpr int total = acc_off + TSS_MAX_CLASSES * 32 * 4;
 };
+
+__device__ __forceinline__ void consumer_bar() {  // named barrier 1: the consumer warps only
+    asm volatile("bar.sync 1, %0;" ::"n"(kConsumers * 32) : "memory");
+}
 
 __device__ __forceinline__ int row_skew_words(int lane) {
     // B_lane = lane*kRowStride + 4*g: choose g so that (B_lane / 4) mod 8 == (lane >> 2) & 7.  With the head
@@ -152,7 +157,9 @@ proto_accum_kernel(const float* __restrict__ feat, const TileRecord* __restrict_
     unsigned char* recs = smem + AccSmem::rec_off;
     uint64_t* full = reinterpret_cast<uint64_t*>(smem + AccSmem::bar_off);
     uint64_t* empty = full + kStages;
+    float* acc = reinterpret_cast<float*>(smem + AccSmem::acc_off);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    for (int i = tid; i < TSS_MAX_CLASSES * 32; i += kAccThreads) acc[i] = 0.f;
     const int64_t T = (P + kPT - 1) / kPT;
     const int64_t KG = K / kKT;
     const int64_t jobs = N * KG * T;
@@ -196,23 +203,25 @@ proto_accum_kernel(const float* __restrict__ feat, const TileRecord* __restrict_
             if (++stage == kStages) { stage = 0; phase ^= 1u; }
         }
     } else {
-        // ===== consumer warps: class-sorted walk, lane = channel
-        float acc[CT];
-#pragma unroll
-        for (int c = 0; c < CT; ++c) acc[c] = 0.f;
+        // ===== consumer warps: class-sorted walk, lane = channel.  Warp w owns sorted positions
+        // [w*64, w*64+64) of every tile; inside a class segment eight pixels are in flight at once (eight
+        // independent shared loads feeding a small add tree), and a segment's partial sum is flushed to the
+        // CTA's shared [C][32] accumulators.  When the (image, channel group) changes, the consumers meet on a
+        // named barrier and emit ONE global atomic per class and channel.
         int stage = 0;
         uint32_t phase = 0;
         int64_t cur_unit = -1;
         const int s0 = warp * (kPT / kConsumers), s1 = s0 + kPT / kConsumers;
         auto flush = [&](int64_t u) {
+            consumer_bar();
             const int64_t kg = u % KG, n = u / KG;
             float* out = sums + (n * C) * K + kg * kKT + lane;
-#pragma unroll
-            for (int c = 0; c < CT; ++c)
-                if (c < C) {
-                    if (acc[c] != 0.f) atomicAdd(out + c * K, acc[c]);
-                    acc[c] = 0.f;
-                }
+            for (int c = warp; c < C; c += kConsumers) {
+                const float v = acc[c * 32 + lane];
+                acc[c * 32 + lane] = 0.f;
+                if (v != 0.f) atomicAdd(out + c * K, v);
+            }
+            consumer_bar();
         };
         for (int64_t j = j0; j < j1; ++j) {
             const int64_t t = j % T;
@@ -226,22 +235,23 @@ proto_accum_kernel(const float* __restrict__ feat, const TileRecord* __restrict_
             const float* row = rows + (stage * kKT + lane) * kRowStride + row_skew_words(lane) + static_cast<int>(e0 & 3);
             const TileRecord* rec = reinterpret_cast<const TileRecord*>(recs + stage * kRecBytes);
             mbar_wait(&full[stage], phase);
+            const int end = min(s1, static_cast<int>(rec->off[C]));  // positions >= off[C] carry no class
+            int pos = s0;
+            int c = 0;
+            while (pos < end) {
+                while (static_cast<int>(rec->off[c + 1]) <= pos) ++c;  // uniform: class of `pos`
+                const int seg_end = min(end, static_cast<int>(rec->off[c + 1]));
+                float t0 = 0.f, t1 = 0.f;
+                for (; pos < seg_end; pos += 8) {
+                    const int rem = seg_end - pos;
+                    float v[8];
 #pragma unroll
-            for (int c = 0; c < CT; ++c) {
-                if (c < C) {
-                    const int a = max(s0, static_cast<int>(rec->off[c]));
-                    const int b = min(s1, static_cast<int>(rec->off[c + 1]));
-                    if (a < b) {
-                        float t0 = 0.f, t1 = 0.f;
-                        int i = a;
-                        for (; i + 1 < b; i += 2) {
-                            t0 += row[rec->idx[i]];
-                            t1 += row[rec->idx[i + 1]];
-                        }
-                        if (i < b) t0 += row[rec->idx[i]];
-                        acc[c] += t0 + t1;
-                    }
+                    for (int q = 0; q < 8; ++q) v[q] = (q < rem) ? row[rec->idx[pos + q]] : 0.f;
+                    t0 += (v[0] + v[1]) + (v[2] + v[3]);
+                    t1 += (v[4] + v[5]) + (v[6] + v[7]);
                 }
+                pos = seg_end;
+                atomicAdd(&acc[c * 32 + lane], t0 + t1);
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty[stage]);
