@@ -21,7 +21,7 @@ namespace tss {
 
 constexpr int kPT = TSS_PROTO_TILE;        // pixels per tile
 constexpr int kKT = 32;                    // channels per tile: one per lane
-constexpr int kConsumers = 8;              // consumer warps
+constexpr int kConsumers = 16;             // consumer warps (each owns kPT/kConsumers sorted positions of a tile)
 constexpr int kAccThreads = (kConsumers + 1) * 32;
 constexpr int kRowStride = kPT + 36;       // floats; room for head misalignment (3) + 16 B round-up (3) + skew (28)
 constexpr int kRecBytes = kPT * 2 + 128;   // uint16 idx[kPT] + uint16 off[64]
@@ -37,7 +37,7 @@ struct TileRecord {
 
 // ------------------------------------------------------------------------------------------------
 template <int CT>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 5)
 proto_label_kernel(const float* __restrict__ logits, const float* __restrict__ labels_val, int C, int64_t P,
                    int overflow, int use_gate, float thresh, uint8_t* __restrict__ seg_label,
                    int32_t* __restrict__ cnt_all, int32_t* __restrict__ cnt_gated, TileRecord* __restrict__ records) {
@@ -56,7 +56,7 @@ proto_label_kernel(const float* __restrict__ logits, const float* __restrict__ l
     for (int r = 0; r < 2; ++r) {
         const int pl = r * 256 + tid;
         const int64_t p = p0 + pl;
-        int lab = 255;
+        int lab = 255, hot_class = -1;
         if (p < P) {
             const float* x = logits + n * C * P + p;
             float v[CT];
@@ -84,8 +84,8 @@ proto_label_kernel(const float* __restrict__ logits, const float* __restrict__ l
                 gate = __fdiv_rn(1.0f, s) >= thresh;
             }
             if (hot) {
-                atomicAdd(&call[t], 1);
-                if (gate) { atomicAdd(&cgate[t], 1); lab = t; }
+                hot_class = t;
+                if (gate) lab = t;
             }
             seg_label[n * P + p] = static_cast<uint8_t>(lab);
         }
@@ -93,6 +93,12 @@ proto_label_kernel(const float* __restrict__ logits, const float* __restrict__ l
         const unsigned int peers = __match_any_sync(0xffffffffu, bucket[r]);
         rank[r] = __popc(peers & ((1u << lane) - 1u));
         if (rank[r] == 0) wcnt[r * 8 + warp][bucket[r]] = __popc(peers);
+        if (use_gate || labels_val != nullptr) {
+            // ungated one-hot count (the "< 10" rule) differs from the gated one: count it separately,
+            // one shared atomic per (warp, class) instead of one per pixel
+            const unsigned int hp = __match_any_sync(0xffffffffu, hot_class);
+            if (hot_class >= 0 && __popc(hp & ((1u << lane) - 1u)) == 0) atomicAdd(&call[hot_class], __popc(hp));
+        }
     }
     __syncthreads();
     // exclusive scan in (class, segment) order -> start of every (segment, class) run
@@ -121,8 +127,10 @@ proto_label_kernel(const float* __restrict__ logits, const float* __restrict__ l
     for (int r = 0; r < 2; ++r) rec->idx[wcnt[r * 8 + warp][bucket[r]] + rank[r]] = static_cast<uint16_t>(r * 256 + tid);
     if (tid < 64) rec->off[tid] = static_cast<uint16_t>(tid <= C + 1 ? boff[tid] : kPT);
     if (tid < C) {
-        if (call[tid]) atomicAdd(&cnt_all[n * C + tid], call[tid]);
-        if (cgate[tid]) atomicAdd(&cnt_gated[n * C + tid], cgate[tid]);
+        const int g = boff[tid + 1] - boff[tid];  // gated count of this class in the tile
+        const int a = (use_gate || labels_val != nullptr) ? call[tid] : g;
+        if (a) atomicAdd(&cnt_all[n * C + tid], a);
+        if (g) atomicAdd(&cnt_gated[n * C + tid], g);
     }
 }
 
@@ -204,15 +212,25 @@ proto_accum_kernel(const float* __restrict__ feat, const TileRecord* __restrict_
         }
     } else {
         // ===== consumer warps: class-sorted walk, lane = channel.  Warp w owns sorted positions
-        // [w*64, w*64+64) of every tile; inside a class segment eight pixels are in flight at once (eight
-        // independent shared loads feeding a small add tree), and a segment's partial sum is flushed to the
-        // CTA's shared [C][32] accumulators.  When the (image, channel group) changes, the consumers meet on a
-        // named barrier and emit ONE global atomic per class and channel.
+        // [w*S, w*S+S) of every tile (S = kPT / kConsumers).  The class loop is unrolled so that every class
+        // has its own REGISTER accumulator; inside a class segment eight pixels are in flight at once (eight
+        // independent shared loads feeding a small add tree).  When the (image, channel group) changes, the
+        // warps fold their registers into the CTA's shared [C][32] accumulators, meet on a named barrier and
+        // emit ONE global atomic per class and channel.
+        float racc[CT];
+#pragma unroll
+        for (int c = 0; c < CT; ++c) racc[c] = 0.f;
         int stage = 0;
         uint32_t phase = 0;
         int64_t cur_unit = -1;
         const int s0 = warp * (kPT / kConsumers), s1 = s0 + kPT / kConsumers;
         auto flush = [&](int64_t u) {
+#pragma unroll
+            for (int c = 0; c < CT; ++c)
+                if (c < C) {
+                    if (racc[c] != 0.f) atomicAdd(&acc[c * 32 + lane], racc[c]);
+                    racc[c] = 0.f;
+                }
             consumer_bar();
             const int64_t kg = u % KG, n = u / KG;
             float* out = sums + (n * C) * K + kg * kKT + lane;
@@ -235,24 +253,35 @@ proto_accum_kernel(const float* __restrict__ feat, const TileRecord* __restrict_
             const float* row = rows + (stage * kKT + lane) * kRowStride + row_skew_words(lane) + static_cast<int>(e0 & 3);
             const TileRecord* rec = reinterpret_cast<const TileRecord*>(recs + stage * kRecBytes);
             mbar_wait(&full[stage], phase);
-            const int end = min(s1, static_cast<int>(rec->off[C]));  // positions >= off[C] carry no class
-            int pos = s0;
-            int c = 0;
-            while (pos < end) {
-                while (static_cast<int>(rec->off[c + 1]) <= pos) ++c;  // uniform: class of `pos`
-                const int seg_end = min(end, static_cast<int>(rec->off[c + 1]));
-                float t0 = 0.f, t1 = 0.f;
-                for (; pos < seg_end; pos += 8) {
-                    const int rem = seg_end - pos;
-                    float v[8];
+#ifndef TSS_PROTO_NOCONSUME
+            int lo = s0;
 #pragma unroll
-                    for (int q = 0; q < 8; ++q) v[q] = (q < rem) ? row[rec->idx[pos + q]] : 0.f;
-                    t0 += (v[0] + v[1]) + (v[2] + v[3]);
-                    t1 += (v[4] + v[5]) + (v[6] + v[7]);
+            for (int c = 0; c < CT; ++c) {
+                if (c < C) {
+                    const int b = min(s1, static_cast<int>(rec->off[c + 1]));  // off[] is non-decreasing
+                    if (lo < b) {
+                        float t0 = 0.f, t1 = 0.f;
+                        // aligned groups of eight sorted positions: ONE 128-bit shared load brings the eight
+                        // pixel indices (the LSU issue rate, not bandwidth, bounds this loop)
+                        for (int base = lo & ~7; base < b; base += 8) {
+                            const uint4 iq = *reinterpret_cast<const uint4*>(&rec->idx[base]);
+                            const int first = lo - base, last = b - base;  // valid q: first <= q < last
+                            const unsigned int w[4] = {iq.x, iq.y, iq.z, iq.w};
+                            float v[8];
+#pragma unroll
+                            for (int q = 0; q < 8; ++q) {
+                                const unsigned int ix = (q & 1) ? (w[q >> 1] >> 16) : (w[q >> 1] & 0xffffu);
+                                v[q] = (q >= first && q < last) ? row[ix] : 0.f;
+                            }
+                            t0 += (v[0] + v[1]) + (v[2] + v[3]);
+                            t1 += (v[4] + v[5]) + (v[6] + v[7]);
+                        }
+                        racc[c] += t0 + t1;
+                        lo = b;
+                    }
                 }
-                pos = seg_end;
-                atomicAdd(&acc[c * 32 + lane], t0 + t1);
             }
+#endif
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty[stage]);
             if (++stage == kStages) { stage = 0; phase ^= 1u; }
@@ -288,49 +317,89 @@ proto_finalize_kernel(const float* __restrict__ sums, const int32_t* __restrict_
     }
 }
 
-// one CTA per class; images in order; the reference's own fp32 operation sequence
+// one CTA per class; images in order; the reference's own fp32 operation sequence.  The prototype row lives
+// in registers for the whole walk (K <= 256 * kUpdR), the skip flags of a chunk of images are staged in shared
+// memory with one parallel load, and four images' vectors are in flight at once -- the update is a chain of
+// dependent fp32 operations per channel, so latency, not bandwidth, is what has to be hidden.
+constexpr int kUpdR = 8;      // channels per thread: K <= 2048
+constexpr int kUpdChunk = 256;
 __global__ void __launch_bounds__(256)
 proto_update_kernel(float* __restrict__ protos, float* __restrict__ num, const float* __restrict__ vectors,
                     const uint8_t* __restrict__ valid, const float* __restrict__ vector_sum, int64_t N, int C,
                     int64_t K, int mode, int start_mean, float m, float one_minus_m, float cap) {
-    const int c = blockIdx.x;
+    __shared__ uint8_t ok[kUpdChunk];
     __shared__ float red[8];
+    const int c = blockIdx.x, tid = threadIdx.x;
     float cnt = num[c];
-    for (int64_t n = 0; n < N; ++n) {
-        const int64_t nc = n * C + c;
-        if (valid != nullptr && !valid[nc]) continue;
-        if (vector_sum != nullptr) {
-            if (vector_sum[nc] == 0.f) continue;
-        } else {  // single-vector form: the `vector.sum() == 0` test is evaluated here
-            float s = 0.f;
-            for (int64_t k = threadIdx.x; k < K; k += 256) s += vectors[nc * K + k];
-            s = warp_sum(s);
-            __syncthreads();
-            if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
-            __syncthreads();
-            float tot = 0.f;
-            for (int w = 0; w < 8; ++w) tot += red[w];
-            if (tot == 0.f) continue;
-        }
+    const int ract = static_cast<int>((K + 255) / 256);  // live channel slots per thread (uniform)
+    float p[kUpdR];
+#pragma unroll
+    for (int r = 0; r < kUpdR; ++r) p[r] = (tid + r * 256 < K) ? protos[c * K + tid + r * 256] : 0.f;
+
+    auto apply = [&](const float (&v)[kUpdR]) {
         const bool mean = (mode == TSS_UPDATE_MEAN) || (start_mean && cnt < 100.f);
-        const float* v = vectors + nc * K;
         if (mean) {
             const float cnt1 = cnt + 1.f;
-            for (int64_t k = threadIdx.x; k < K; k += 256) {
-                const float p = protos[c * K + k];
-                protos[c * K + k] = __fdiv_rn(__fadd_rn(__fmul_rn(p, cnt), v[k]), cnt1);
-            }
+#pragma unroll
+            for (int r = 0; r < kUpdR; ++r)
+                if (r < ract) p[r] = __fdiv_rn(__fadd_rn(__fmul_rn(p[r], cnt), v[r]), cnt1);
             cnt = fminf(cnt1, cap);
         } else {
-            for (int64_t k = threadIdx.x; k < K; k += 256) {
-                const float p = protos[c * K + k];
-                protos[c * K + k] = __fadd_rn(__fmul_rn(p, one_minus_m), __fmul_rn(m, v[k]));
-            }
+#pragma unroll
+            for (int r = 0; r < kUpdR; ++r)
+                if (r < ract) p[r] = __fadd_rn(__fmul_rn(p[r], one_minus_m), __fmul_rn(m, v[r]));
             cnt = fminf(cnt + 1.f, cap);
         }
+    };
+    auto load = [&](int64_t n, float (&v)[kUpdR]) {
+        const float* src = vectors + (n * C + c) * K;
+#pragma unroll
+        for (int r = 0; r < kUpdR; ++r) v[r] = (tid + r * 256 < K) ? src[tid + r * 256] : 0.f;
+    };
+
+    for (int64_t n0 = 0; n0 < N; n0 += kUpdChunk) {
+        const int len = static_cast<int>(min(static_cast<int64_t>(kUpdChunk), N - n0));
+        __syncthreads();
+        if (vector_sum != nullptr) {
+            if (tid < len) {
+                const int64_t nc = (n0 + tid) * C + c;
+                ok[tid] = ((valid == nullptr || valid[nc]) && vector_sum[nc] != 0.f) ? 1 : 0;
+            }
+        } else {
+            // single-vector form: the `vector.sum() == 0` test is evaluated here
+            for (int i = 0; i < len; ++i) {
+                const int64_t nc = (n0 + i) * C + c;
+                float sacc = 0.f;
+                for (int64_t k = tid; k < K; k += 256) sacc += vectors[nc * K + k];
+                sacc = warp_sum(sacc);
+                __syncthreads();
+                if ((tid & 31) == 0) red[tid >> 5] = sacc;
+                __syncthreads();
+                if (tid == 0) {
+                    float tot = 0.f;
+                    for (int w = 0; w < 8; ++w) tot += red[w];
+                    ok[i] = ((valid == nullptr || valid[nc]) && tot != 0.f) ? 1 : 0;
+                }
+            }
+        }
+        __syncthreads();
+        for (int i = 0; i < len; i += 4) {
+            float v0[kUpdR], v1[kUpdR], v2[kUpdR], v3[kUpdR];
+            const bool k0 = ok[i], k1 = i + 1 < len && ok[i + 1], k2 = i + 2 < len && ok[i + 2], k3 = i + 3 < len && ok[i + 3];
+            if (k0) load(n0 + i, v0);
+            if (k1) load(n0 + i + 1, v1);
+            if (k2) load(n0 + i + 2, v2);
+            if (k3) load(n0 + i + 3, v3);
+            if (k0) apply(v0);
+            if (k1) apply(v1);
+            if (k2) apply(v2);
+            if (k3) apply(v3);
+        }
     }
-    __syncthreads();
-    if (threadIdx.x == 0) num[c] = cnt;
+#pragma unroll
+    for (int r = 0; r < kUpdR; ++r)
+        if (tid + r * 256 < K) protos[c * K + tid + r * 256] = p[r];
+    if (tid == 0) num[c] = cnt;
 }
 
 // closed-form weights of the same recurrence, for the sharded (all-reduce) form
@@ -476,6 +545,7 @@ extern "C" int tss_proto_update(float* protos, float* num, const float* vectors,
     TSS_REQUIRE(protos && num && vectors, TSS_E_ARG, "tss_proto_update: null pointer");
     TSS_REQUIRE(n_img >= 0 && channels > 0 && num_classes >= 1 && num_classes <= TSS_MAX_CLASSES, TSS_E_ARG, "tss_proto_update: bad extents");
     TSS_REQUIRE(mode == TSS_UPDATE_MEAN || mode == TSS_UPDATE_MOVING_AVERAGE, TSS_E_ARG, "tss_proto_update: bad mode %d", mode);
+    TSS_REQUIRE(channels <= 256 * kUpdR, TSS_E_ARG, "tss_proto_update: at most %d channels", 256 * kUpdR);
     if (n_img == 0) return TSS_OK;
     // python evaluates (1 - momentum) in double before the fp32 tensor multiply
     proto_update_kernel<<<num_classes, 256, 0, as_stream(stream)>>>(protos, num, vectors, valid, vector_sum, n_img, num_classes,
