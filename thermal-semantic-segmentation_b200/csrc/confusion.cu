@@ -80,7 +80,7 @@ __device__ __forceinline__ void count4(unsigned int* lane_base, unsigned int g4,
 }
 
 __global__ void __launch_bounds__(kPackedWarps * 32)
-confusion_u8_packed(const uint8_t* __restrict__ pred, const uint8_t* __restrict__ gt, int64_t n_vec, int C,
+confusion_u8_packed(const uint8_t* __restrict__ pred, const uint8_t* __restrict__ gt, int64_t n_vec, int C, int iters,
                     unsigned long long* __restrict__ hist, unsigned long long* __restrict__ bad) {
     // n_vec = number of 16-pixel vectors (both pointers 16-byte aligned; the tail goes to the atomic kernel)
     extern __shared__ unsigned int sh[];
@@ -100,12 +100,12 @@ confusion_u8_packed(const uint8_t* __restrict__ pred, const uint8_t* __restrict_
     const uint4* gv = reinterpret_cast<const uint4*>(gt);
     // chunk = 15 consecutive warp-wide rounds; chunks are dealt round-robin to all warps of the grid
     const int64_t warps_total = static_cast<int64_t>(gridDim.x) * kPackedWarps;
-    const int64_t chunk_vecs = static_cast<int64_t>(kPackedIters) * 32;
+    const int64_t chunk_vecs = static_cast<int64_t>(iters) * 32;  // iters <= kPackedIters: no counter can wrap
     for (int64_t chunk = static_cast<int64_t>(blockIdx.x) * kPackedWarps + warp;; chunk += warps_total) {
         const int64_t v0 = chunk * chunk_vecs;
         if (v0 >= n_vec) break;
-#pragma unroll 5
-        for (int it = 0; it < kPackedIters; ++it) {
+#pragma unroll 3
+        for (int it = 0; it < iters; ++it) {
             const int64_t v = v0 + static_cast<int64_t>(it) * 32 + lane;
             if (v < n_vec) {
                 const uint4 p = ldg_stream_u4(pv + v);
@@ -197,9 +197,15 @@ extern "C" int tss_confusion(const void* pred, const void* gt, int dtype, int64_
         int ctas_per_sm = static_cast<int>((220 * 1024) / (sh + 1024));
         if (ctas_per_sm > 8) ctas_per_sm = 8;
         if (ctas_per_sm < 1) ctas_per_sm = 1;
-        const int grid = grid_for(n_vec, kPackedWarps * 32 * kPackedIters, ctas_per_sm);
+        // chunk length: as long as possible (fewer flushes) while one wave of resident warps covers the input
+        const int64_t slots = static_cast<int64_t>(kNumSMs) * ctas_per_sm * kPackedWarps;
+        int64_t iters = (n_vec + 32 * slots - 1) / (32 * slots);
+        if (iters > kPackedIters) iters = kPackedIters;
+        if (iters < 1) iters = 1;
+        const int grid = grid_for(n_vec, kPackedWarps * 32 * static_cast<int>(iters), ctas_per_sm);
         confusion_u8_packed<<<grid, kPackedWarps * 32, sh, st>>>(static_cast<const uint8_t*>(pred),
-                                                                  static_cast<const uint8_t*>(gt), n_vec, C, h, b);
+                                                                  static_cast<const uint8_t*>(gt), n_vec, C,
+                                                                  static_cast<int>(iters), h, b);
         TSS_LAUNCH_CHECK("tss_confusion(packed)");
         done = n_vec * 16;
     }
