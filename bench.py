@@ -217,11 +217,10 @@ def run_b200(args):
 
     def stage_proto(i):
         logits, feat, _ = sets[i % N_SETS]
-        means = ops.class_means(feat, logits, C)
         if ws == 1:
-            ops.prototype_update(bank.protos, bank.num, means, bank.mode, bank.start_mean, bank.momentum)
+            ops.class_means(feat, logits, C, update=(bank.protos, bank.num, bank.mode, bank.start_mean, bank.momentum))
         else:
-            bank.update(means)
+            bank.update(ops.class_means(feat, logits, C))
 
     def stage_hist(i, pl):
         ops.confusion_matrix(pl.label.reshape(-1), sets[i % N_SETS][2].reshape(-1), C, meter.hist, meter.bad)
@@ -324,36 +323,24 @@ def run_b200(args):
 
 
 def run_e2e(args, dev, rank, ws, dist, dropin, ops, sharding):
+    """The same step through the public host-fed API (b200seg.pipeline.HostLabelPipeline): every step's
+    inputs come from pinned HOST memory (H2D inside the timed region), every step's thresholded labels and
+    fp16 confidences go back to pinned host memory (D2H inside the timed region)."""
+    from b200seg.pipeline import HostLabelPipeline
+
     c = CFG
     frames, C, size = c["frames"], c["C"], (c["H"], c["W"])
     host = []
     for s in range(2):
         lg, ft, gt = make_inputs("cpu", 4321 + 1000 * rank + s, frames)
         host.append((lg.pin_memory(), ft.pin_memory(), gt.pin_memory()))
-    d_logits, d_feat, d_gt = (torch.empty_like(t, device=dev) for t in host[0])
-    h_label = torch.empty((frames,) + size, dtype=torch.uint8).pin_memory()
-    h_conf = torch.empty((frames,) + size, dtype=torch.float16).pin_memory()
-    cf = dropin.Class_Features(dev, C, c["K"])
-    meter = dropin.ConfusionMeter(C, dev)
-    h2d = sum(t.numel() * t.element_size() for t in host[0])
-    d2h = h_label.numel() + 2 * h_conf.numel()
-
-    def step(i):
-        lg, ft, gt = host[i % 2]
-        d_logits.copy_(lg, non_blocking=True)
-        d_feat.copy_(ft, non_blocking=True)
-        d_gt.copy_(gt, non_blocking=True)
-        pl = dropin.pseudo_label_batch(d_logits, size=size, thr=c["thr"], keep=c["keep"], ignore_index=c["ignore"])
-        if ws == 1:
-            cf.update_from_batch(d_feat, d_logits)
-        else:
-            cf.class_means(d_feat, d_logits)  # sharded update is exercised by the device arm; means are the traffic
-        meter.add(pl.label, d_gt)
-        h_label.copy_(pl.label_thr, non_blocking=True)
-        h_conf.copy_(pl.conf16, non_blocking=True)
+    # ws > 1: the sharded prototype exchange is exercised by the device arm; here the class means are the traffic
+    pipe = HostLabelPipeline(dev, C, c["K"], size, thr=c["thr"], keep=c["keep"], ignore_index=c["ignore"],
+                             update_prototypes=(ws == 1))
 
     for i in range(3):
-        step(i)
+        pipe.submit(*host[i % 2])
+    pipe.join()
     torch.cuda.synchronize()
     if ws > 1:
         dist.barrier()
@@ -361,9 +348,10 @@ def run_e2e(args, dev, rank, ws, dist, dropin, ops, sharding):
     torch.cuda.synchronize()
     ev0.record()
     for i in range(args.steps):
-        step(i)
-    sharding.all_reduce_confusion(meter.hist, meter.bad)
-    hist = meter.result()            # D2H of the [C,C] matrix: the metric the user reads
+        pipe.submit(*host[i % 2])
+    pipe.join()
+    sharding.all_reduce_confusion(pipe.meter.hist, pipe.meter.bad)
+    hist = pipe.meter.result()       # D2H of the [C,C] matrix: the metric the user reads
     ev1.record()
     torch.cuda.synchronize()
     ms = torch.tensor([ev0.elapsed_time(ev1)], device=dev)
@@ -371,9 +359,10 @@ def run_e2e(args, dev, rank, ws, dist, dropin, ops, sharding):
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     ms = float(ms.item())
     return {"value": frames * c["H"] * c["W"] * ws * args.steps / (ms * 1e-3), "unit": UNIT,
-            "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h + hist.nbytes // max(args.steps, 1)),
+            "h2d_bytes_per_step": int(pipe.h2d_bytes), "d2h_bytes_per_step": int(pipe.d2h_bytes + hist.nbytes // max(args.steps, 1)),
             "ms_per_step": ms / args.steps,
-            "api": "b200seg.dropin.pseudo_label_batch + Class_Features.update_from_batch + ConfusionMeter.add"}
+            "api": "b200seg.pipeline.HostLabelPipeline.submit (dropin.pseudo_label_batch + Class_Features.update_from_batch "
+                   "+ ConfusionMeter.add; upload / kernels / download on three streams, two slots)"}
 
 
 def main():

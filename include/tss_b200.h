@@ -131,26 +131,37 @@ int tss_gather_nearest_u8(const uint8_t* src, uint8_t* dst, int64_t planes, int 
  *   optionally intersected with labels_val [N,P] fp32 (values >= C go to `overflow_channel`,
  *   process_label :146-151 / :204-209) and gated by conf >= conf_thresh (use_conf_gate != 0,
  *   self_training.py:180-181).  Writes seg_label [N,P] uint8 (class whose sum the pixel joins, 255 =
- *   none), count_all [N,C] int32 (ungated one-hot count: the "< 10" rule :135 / :196) and count_gated
- *   [N,C] int32 (the divisor :128,:140 / :189,:198), plus tile records for step 2 in `records`
- *   (tss_proto_records_bytes(N, P) bytes): per tile of TSS_PROTO_TILE pixels the pixel offsets sorted
- *   by class and the class segment boundaries.
+ *   none) and, in `records` (tss_proto_records_bytes(N, P) bytes, 16-byte aligned), per tile of
+ *   TSS_PROTO_TILE pixels: the pixel offsets sorted by class, the class segment boundaries (= the gated
+ *   per-class counts, the divisor :128,:140 / :189,:198) and the ungated one-hot counts (the "< 10" rule
+ *   :135 / :196).  No atomics, no zero-initialised buffers.  sums_to_zero (may be NULL): sums_elems floats
+ *   zeroed by the same launch, so that tss_proto_accumulate(zero_sums = 0) can follow without a memset.
  * Step 2, tss_proto_accumulate: feat [N,K,P] fp32 (K % 32 == 0) streamed once through shared memory
- *   (bulk async copies + mbarrier ring); sums [N,C,K] fp32 are zeroed by the call, then accumulated.
- * Step 3, tss_proto_finalize: vectors [N,C,K] = sums / count_gated; valid [N,C] uint8 =
- *   count_gated > 0 && count_all >= 10 (the two `continue`s); vector_sum [N,C] fp32 (for the
- *   `vector.sum() == 0` skip of update_objective_SingleVector :154 / :212). */
+ *   (bulk async copies + mbarrier ring); sums [N,C,K] fp32 are zeroed first when zero_sums != 0, then
+ *   accumulated.
+ * Step 3, tss_proto_finalize: count_all / count_gated [N,C] int32 (OUT, summed over the tile records);
+ *   vectors [N,C,K] = sums / count_gated; valid [N,C] uint8 = count_gated > 0 && count_all >= min_pixels
+ *   (the two `continue`s); vector_sum [N,C] fp32 (for the `vector.sum() == 0` skip of
+ *   update_objective_SingleVector :154 / :212).
+ * Step 3+A6 in one launch, tss_proto_finalize_update: the same outputs, then the sequential prototype
+ *   update of tss_proto_update below with them (cal_prototype.py:72-75: calculate_mean_vector followed by
+ *   the update loop). */
 #define TSS_PROTO_TILE 512
 size_t tss_proto_records_bytes(int64_t n_img, int64_t plane);
 int tss_proto_labels(const float* logits, const float* labels_val, int64_t n_img, int num_classes,
                      int64_t plane, int overflow_channel, int use_conf_gate, float conf_thresh,
-                     uint8_t* seg_label, int32_t* count_all, int32_t* count_gated, void* records,
+                     uint8_t* seg_label, void* records, float* sums_to_zero, int64_t sums_elems,
                      void* stream);
 int tss_proto_accumulate(const float* feat, const void* records, int64_t n_img, int64_t channels,
-                         int64_t plane, int num_classes, float* sums, void* stream);
-int tss_proto_finalize(const float* sums, const int32_t* count_all, const int32_t* count_gated,
-                       int64_t n_img, int num_classes, int64_t channels, int min_pixels, float* vectors,
-                       uint8_t* valid, float* vector_sum, void* stream);
+                         int64_t plane, int num_classes, float* sums, int zero_sums, void* stream);
+int tss_proto_finalize(const float* sums, const void* records, int64_t n_img, int num_classes,
+                       int64_t channels, int64_t plane, int min_pixels, int32_t* count_all,
+                       int32_t* count_gated, float* vectors, uint8_t* valid, float* vector_sum, void* stream);
+int tss_proto_finalize_update(const float* sums, const void* records, int64_t n_img, int num_classes,
+                              int64_t channels, int64_t plane, int min_pixels, int32_t* count_all,
+                              int32_t* count_gated, float* vectors, uint8_t* valid, float* vector_sum,
+                              float* protos, float* num, int mode, int start_mean, double momentum,
+                              double cap, void* stream);
 
 /* A6   sequential prototype update -- update_objective_SingleVector (cal_prototype.py:153-169,
  * self_training.py:211-227) applied to the vectors of one batch in the reference's list order

@@ -34,7 +34,7 @@ def test_library_exports_every_declared_symbol():
     assert handle.tss_version() == 100
     handle.tss_proto_records_bytes.restype = ctypes.c_size_t
     handle.tss_proto_records_bytes.argtypes = [ctypes.c_int64, ctypes.c_int64]
-    assert handle.tss_proto_records_bytes(2, 1000) == 2 * 2 * (512 * 2 + 128)
+    assert handle.tss_proto_records_bytes(2, 1000) == 2 * 2 * (512 * 2 + 128 + 64)
     assert handle.tss_proto_records_bytes(0, 1000) == 0
 
 
@@ -47,7 +47,7 @@ def test_argument_rejection_needs_no_gpu():
     p = ctypes.cast(buf, ctypes.c_void_p)
     assert L.tss_confusion(p, p, 0, 10, 99, p, None, None) == 2                   # TSS_E_CLASSES
     assert L.tss_confusion(p, p, 7, 10, 13, p, None, None) == 1                   # bad dtype
-    assert L.tss_proto_accumulate(p, p, 1, 33, 10, 13, p, None) == 1              # channels % 32
+    assert L.tss_proto_accumulate(p, p, 1, 33, 10, 13, p, 1, None) == 1              # channels % 32
     assert L.tss_confusion(p, p, 0, 0, 13, p, None, None) == 0                    # empty input is a no-op
 
 

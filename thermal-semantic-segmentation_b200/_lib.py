@@ -30,9 +30,11 @@ _SIGNATURES = {
     "tss_threshold_labels": (c_int, [c_vp, c_vp, c_i64, c_int, c_vp, c_vp, c_int, c_vp, c_vp]),
     "tss_gather_nearest_u8": (c_int, [c_vp, c_vp, c_i64, c_int, c_int, c_int, c_int, c_vp, c_vp, c_vp]),
     "tss_proto_records_bytes": (c_sz, [c_i64, c_i64]),
-    "tss_proto_labels": (c_int, [c_vp, c_vp, c_i64, c_int, c_i64, c_int, c_int, c_f32, c_vp, c_vp, c_vp, c_vp, c_vp]),
-    "tss_proto_accumulate": (c_int, [c_vp, c_vp, c_i64, c_i64, c_i64, c_int, c_vp, c_vp]),
-    "tss_proto_finalize": (c_int, [c_vp, c_vp, c_vp, c_i64, c_int, c_i64, c_int, c_vp, c_vp, c_vp, c_vp]),
+    "tss_proto_labels": (c_int, [c_vp, c_vp, c_i64, c_int, c_i64, c_int, c_int, c_f32, c_vp, c_vp, c_vp, c_i64, c_vp]),
+    "tss_proto_accumulate": (c_int, [c_vp, c_vp, c_i64, c_i64, c_i64, c_int, c_vp, c_int, c_vp]),
+    "tss_proto_finalize": (c_int, [c_vp, c_vp, c_i64, c_int, c_i64, c_i64, c_int, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
+    "tss_proto_finalize_update": (c_int, [c_vp, c_vp, c_i64, c_int, c_i64, c_i64, c_int, c_vp, c_vp, c_vp, c_vp, c_vp,
+                                          c_vp, c_vp, c_int, c_int, c_f64, c_f64, c_vp]),
     "tss_proto_update": (c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_int, c_i64, c_int, c_int, c_f64, c_f64, c_vp]),
     "tss_proto_update_partial": (c_int, [c_vp, c_vp, c_vp, c_i64, c_int, c_i64, c_int, c_int, c_f64, c_f64, c_vp,
                                          c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),

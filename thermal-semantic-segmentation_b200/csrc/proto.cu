@@ -24,23 +24,25 @@ constexpr int kKT = 32;                    // channels per tile: one per lane
 constexpr int kConsumers = 16;             // consumer warps (each owns kPT/kConsumers sorted positions of a tile)
 constexpr int kAccThreads = (kConsumers + 1) * 32;
 constexpr int kRowStride = kPT + 36;       // floats; room for head misalignment (3) + 16 B round-up (3) + skew (28)
-constexpr int kRecBytes = kPT * 2 + 128;   // uint16 idx[kPT] + uint16 off[64]
+constexpr int kRecBytes = kPT * 2 + 128 + 64;   // uint16 idx[kPT] + uint16 off[64] + uint16 call[32]
 constexpr int kStages = 3;
 
 static_assert(kRowStride % 4 == 0, "rows must start 16-byte aligned");
 static_assert(kRecBytes % 16 == 0, "records are bulk-copied");
 
 struct TileRecord {
-    uint16_t idx[kPT];
-    uint16_t off[64];
+    uint16_t idx[kPT];   // pixel offsets of the tile sorted by class (bucket C = pixels that join no sum)
+    uint16_t off[64];    // off[c] = first sorted position of class c; off[c+1]-off[c] = gated count in the tile
+    uint16_t call[32];   // ungated one-hot count per class in the tile (the "< 10 pixels" rule)
 };
+static_assert(sizeof(TileRecord) == kRecBytes, "record layout");
 
 // ------------------------------------------------------------------------------------------------
 template <int CT>
 __global__ void __launch_bounds__(256, 5)
 proto_label_kernel(const float* __restrict__ logits, const float* __restrict__ labels_val, int C, int64_t P,
                    int overflow, int use_gate, float thresh, uint8_t* __restrict__ seg_label,
-                   int32_t* __restrict__ cnt_all, int32_t* __restrict__ cnt_gated, TileRecord* __restrict__ records) {
+                   TileRecord* __restrict__ records, float* __restrict__ zero_buf, int64_t zero_elems) {
     __shared__ int wcnt[16][TSS_MAX_CLASSES + 1];
     __shared__ int call[TSS_MAX_CLASSES], cgate[TSS_MAX_CLASSES];
     __shared__ int boff[TSS_MAX_CLASSES + 2];
@@ -48,6 +50,8 @@ proto_label_kernel(const float* __restrict__ logits, const float* __restrict__ l
     const int64_t tile = blockIdx.x, n = blockIdx.y;
     const int64_t tiles = gridDim.x;
     const int64_t p0 = tile * kPT;
+    // zero the segmented-sum buffer the accumulate kernel adds into (saves a memset node on the stream)
+    for (int64_t i = (n * tiles + tile) * 256 + tid; i < zero_elems; i += tiles * gridDim.y * 256) zero_buf[i] = 0.f;
     for (int i = tid; i < 16 * (TSS_MAX_CLASSES + 1); i += 256) (&wcnt[0][0])[i] = 0;
     if (tid < TSS_MAX_CLASSES) { call[tid] = 0; cgate[tid] = 0; }
     __syncthreads();
@@ -126,11 +130,9 @@ proto_label_kernel(const float* __restrict__ logits, const float* __restrict__ l
 #pragma unroll
     for (int r = 0; r < 2; ++r) rec->idx[wcnt[r * 8 + warp][bucket[r]] + rank[r]] = static_cast<uint16_t>(r * 256 + tid);
     if (tid < 64) rec->off[tid] = static_cast<uint16_t>(tid <= C + 1 ? boff[tid] : kPT);
-    if (tid < C) {
-        const int g = boff[tid + 1] - boff[tid];  // gated count of this class in the tile
-        const int a = (use_gate || labels_val != nullptr) ? call[tid] : g;
-        if (a) atomicAdd(&cnt_all[n * C + tid], a);
-        if (g) atomicAdd(&cnt_gated[n * C + tid], g);
+    if (tid < 32) {
+        const int g = tid < C ? boff[tid + 1] - boff[tid] : 0;  // gated count of this class in the tile
+        rec->call[tid] = static_cast<uint16_t>(tid < C ? ((use_gate || labels_val != nullptr) ? call[tid] : g) : 0);
     }
 }
 
@@ -146,6 +148,12 @@ struct AccSmem {
 
 __device__ __forceinline__ void consumer_bar() {  // named barrier 1: the consumer warps only
     asm volatile("bar.sync 1, %0;" ::"n"(kConsumers * 32) : "memory");
+}
+
+__device__ __forceinline__ float lds_f32(uint32_t addr) {  // unconditional shared load (never sunk into a branch)
+    float v;
+    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+    return v;
 }
 
 __device__ __forceinline__ int row_skew_words(int lane) {
@@ -254,31 +262,42 @@ proto_accum_kernel(const float* __restrict__ feat, const TileRecord* __restrict_
             const TileRecord* rec = reinterpret_cast<const TileRecord*>(recs + stage * kRecBytes);
             mbar_wait(&full[stage], phase);
 #ifndef TSS_PROTO_NOCONSUME
-            int lo = s0;
+            // classes that own at least one of this warp's sorted positions: lane c tests class c, one ballot
+            unsigned int present;
+            {
+                const int oa = rec->off[lane], ob = rec->off[lane + 1];  // off[] has 64 entries, non-decreasing
+                present = __ballot_sync(0xffffffffu, lane < C && max(oa, s0) < min(ob, s1));
+            }
+            const uint32_t row_addr = smem_u32(row);
 #pragma unroll
             for (int c = 0; c < CT; ++c) {
-                if (c < C) {
-                    const int b = min(s1, static_cast<int>(rec->off[c + 1]));  // off[] is non-decreasing
-                    if (lo < b) {
-                        float t0 = 0.f, t1 = 0.f;
-                        // aligned groups of eight sorted positions: ONE 128-bit shared load brings the eight
-                        // pixel indices (the LSU issue rate, not bandwidth, bounds this loop)
-                        for (int base = lo & ~7; base < b; base += 8) {
-                            const uint4 iq = *reinterpret_cast<const uint4*>(&rec->idx[base]);
-                            const int first = lo - base, last = b - base;  // valid q: first <= q < last
-                            const unsigned int w[4] = {iq.x, iq.y, iq.z, iq.w};
-                            float v[8];
+                if ((present >> c) & 1u) {   // warp-uniform
+                    const int lo = max(s0, static_cast<int>(rec->off[c]));
+                    const int b = min(s1, static_cast<int>(rec->off[c + 1]));
+                    float t0 = 0.f, t1 = 0.f;
+                    // aligned groups of eight sorted positions: ONE 128-bit shared load brings the eight pixel
+                    // indices; the eight feature loads are unconditional (every index of a record is a valid
+                    // offset into the staged row), the partial groups at the two ends of a segment select zeros
+                    for (int base = lo & ~7; base < b; base += 8) {
+                        const uint4 iq = *reinterpret_cast<const uint4*>(&rec->idx[base]);
+                        float v[8];
+                        v[0] = lds_f32(row_addr + ((iq.x & 0xffffu) << 2));
+                        v[1] = lds_f32(row_addr + ((iq.x >> 16) << 2));
+                        v[2] = lds_f32(row_addr + ((iq.y & 0xffffu) << 2));
+                        v[3] = lds_f32(row_addr + ((iq.y >> 16) << 2));
+                        v[4] = lds_f32(row_addr + ((iq.z & 0xffffu) << 2));
+                        v[5] = lds_f32(row_addr + ((iq.z >> 16) << 2));
+                        v[6] = lds_f32(row_addr + ((iq.w & 0xffffu) << 2));
+                        v[7] = lds_f32(row_addr + ((iq.w >> 16) << 2));
+                        const int first = lo - base, last = b - base;  // valid q: first <= q < last
+                        if (first > 0 || last < 8) {
 #pragma unroll
-                            for (int q = 0; q < 8; ++q) {
-                                const unsigned int ix = (q & 1) ? (w[q >> 1] >> 16) : (w[q >> 1] & 0xffffu);
-                                v[q] = (q >= first && q < last) ? row[ix] : 0.f;
-                            }
-                            t0 += (v[0] + v[1]) + (v[2] + v[3]);
-                            t1 += (v[4] + v[5]) + (v[6] + v[7]);
+                            for (int q = 0; q < 8; ++q) v[q] = (q >= first && q < last) ? v[q] : 0.f;
                         }
-                        racc[c] += t0 + t1;
-                        lo = b;
+                        t0 += (v[0] + v[1]) + (v[2] + v[3]);
+                        t1 += (v[4] + v[5]) + (v[6] + v[7]);
                     }
+                    racc[c] += t0 + t1;
                 }
             }
 #endif
@@ -291,13 +310,34 @@ proto_accum_kernel(const float* __restrict__ feat, const TileRecord* __restrict_
 }
 
 // ------------------------------------------------------------------------------------------------
+// per-(image, class) pixel counts = sums over the image's tile records (no atomics, no zero-initialised buffers)
+__device__ __forceinline__ void tile_counts(const TileRecord* __restrict__ rec, int64_t tiles, int c, int lane,
+                                            int& gated, int& all) {
+    int g = 0, a = 0;
+    for (int64_t t = lane; t < tiles; t += 32) {
+        g += static_cast<int>(rec[t].off[c + 1]) - static_cast<int>(rec[t].off[c]);
+        a += rec[t].call[c];
+    }
+    gated = __reduce_add_sync(0xffffffffu, g);
+    all = __reduce_add_sync(0xffffffffu, a);
+}
+
 __global__ void __launch_bounds__(256)
-proto_finalize_kernel(const float* __restrict__ sums, const int32_t* __restrict__ cnt_all,
-                      const int32_t* __restrict__ cnt_gated, int C, int64_t K, int min_pixels,
+proto_finalize_kernel(const float* __restrict__ sums, const TileRecord* __restrict__ records, int64_t tiles, int C,
+                      int64_t K, int min_pixels, int32_t* __restrict__ cnt_all, int32_t* __restrict__ cnt_gated,
                       float* __restrict__ vectors, uint8_t* __restrict__ valid, float* __restrict__ vector_sum) {
     __shared__ float part[8];
+    __shared__ int cnt[2];
     const int64_t nc = blockIdx.x;  // n*C + c
-    const int cg = cnt_gated[nc], ca = cnt_all[nc];
+    const int64_t n = nc / C;
+    const int c = static_cast<int>(nc - n * C);
+    if (threadIdx.x < 32) {
+        int g, a;
+        tile_counts(records + n * tiles, tiles, c, threadIdx.x, g, a);
+        if (threadIdx.x == 0) { cnt[0] = g; cnt[1] = a; }
+    }
+    __syncthreads();
+    const int cg = cnt[0], ca = cnt[1];
     const bool ok = cg > 0 && ca >= min_pixels;
     const float denom = static_cast<float>(cg);
     float s = 0.f;
@@ -314,6 +354,8 @@ proto_finalize_kernel(const float* __restrict__ sums, const int32_t* __restrict_
         for (int w = 0; w < 8; ++w) tot += part[w];
         vector_sum[nc] = tot;
         valid[nc] = ok ? 1 : 0;
+        cnt_all[nc] = ca;
+        cnt_gated[nc] = cg;
     }
 }
 
@@ -323,10 +365,18 @@ proto_finalize_kernel(const float* __restrict__ sums, const int32_t* __restrict_
 // dependent fp32 operations per channel, so latency, not bandwidth, is what has to be hidden.
 constexpr int kUpdR = 8;      // channels per thread: K <= 2048
 constexpr int kUpdChunk = 256;
+struct FinalizeArgs {  // non-null sums: the kernel first turns sums into vectors (proto_finalize fused in)
+    const float* sums;
+    const TileRecord* records;
+    int64_t tiles;
+    int min_pixels;
+    int32_t* cnt_all;
+    int32_t* cnt_gated;
+};
 __global__ void __launch_bounds__(256)
-proto_update_kernel(float* __restrict__ protos, float* __restrict__ num, const float* __restrict__ vectors,
-                    const uint8_t* __restrict__ valid, const float* __restrict__ vector_sum, int64_t N, int C,
-                    int64_t K, int mode, int start_mean, float m, float one_minus_m, float cap) {
+proto_update_kernel(float* __restrict__ protos, float* __restrict__ num, float* vectors, uint8_t* valid,
+                    float* vector_sum, int64_t N, int C, int64_t K, int mode, int start_mean, float m,
+                    float one_minus_m, float cap, const FinalizeArgs fin) {
     __shared__ uint8_t ok[kUpdChunk];
     __shared__ float red[8];
     const int c = blockIdx.x, tid = threadIdx.x;
@@ -360,7 +410,32 @@ proto_update_kernel(float* __restrict__ protos, float* __restrict__ num, const f
     for (int64_t n0 = 0; n0 < N; n0 += kUpdChunk) {
         const int len = static_cast<int>(min(static_cast<int64_t>(kUpdChunk), N - n0));
         __syncthreads();
-        if (vector_sum != nullptr) {
+        if (fin.sums != nullptr) {
+            // fused finalize: one warp per image of the chunk -- counts from the tile records, vector = sum / count
+            // (written out: the same tensors tss_proto_finalize produces), skip flags straight into shared memory
+            const int warp = tid >> 5, lane = tid & 31;
+            for (int i = warp; i < len; i += 8) {
+                const int64_t n = n0 + i, nc = n * C + c;
+                int g, a;
+                tile_counts(fin.records + n * fin.tiles, fin.tiles, c, lane, g, a);
+                const bool good = g > 0 && a >= fin.min_pixels;
+                const float denom = static_cast<float>(g);
+                float sacc = 0.f;
+                for (int64_t k = lane; k < K; k += 32) {
+                    const float v = good ? __fdiv_rn(fin.sums[nc * K + k], denom) : 0.f;
+                    vectors[nc * K + k] = v;
+                    sacc += v;
+                }
+                sacc = warp_sum(sacc);
+                if (lane == 0) {
+                    vector_sum[nc] = sacc;
+                    valid[nc] = good ? 1 : 0;
+                    fin.cnt_all[nc] = a;
+                    fin.cnt_gated[nc] = g;
+                    ok[i] = (good && sacc != 0.f) ? 1 : 0;
+                }
+            }
+        } else if (vector_sum != nullptr) {
             if (tid < len) {
                 const int64_t nc = (n0 + tid) * C + c;
                 ok[tid] = ((valid == nullptr || valid[nc]) && vector_sum[nc] != 0.f) ? 1 : 0;
@@ -467,27 +542,25 @@ extern "C" size_t tss_proto_records_bytes(int64_t n_img, int64_t plane) {
 
 extern "C" int tss_proto_labels(const float* logits, const float* labels_val, int64_t n_img, int num_classes,
                                 int64_t plane, int overflow_channel, int use_conf_gate, float conf_thresh,
-                                uint8_t* seg_label, int32_t* count_all, int32_t* count_gated, void* records,
+                                uint8_t* seg_label, void* records, float* sums_to_zero, int64_t sums_elems,
                                 void* stream) {
     using namespace tss;
-    TSS_REQUIRE(logits && seg_label && count_all && count_gated && records, TSS_E_ARG, "tss_proto_labels: null pointer");
+    TSS_REQUIRE(logits && seg_label && records, TSS_E_ARG, "tss_proto_labels: null pointer");
     TSS_REQUIRE(n_img >= 0 && plane > 0 && n_img <= 65535, TSS_E_ARG, "tss_proto_labels: bad extents");
     TSS_REQUIRE(num_classes >= 1 && num_classes <= TSS_MAX_CLASSES, TSS_E_CLASSES, "tss_proto_labels: num_classes %d", num_classes);
     TSS_REQUIRE((reinterpret_cast<uintptr_t>(records) & 15) == 0, TSS_E_ALIGN, "tss_proto_labels: records must be 16-byte aligned");
+    TSS_REQUIRE(sums_elems >= 0 && (sums_elems == 0 || sums_to_zero != nullptr), TSS_E_ARG, "tss_proto_labels: sums_elems without buffer");
     if (n_img == 0) return TSS_OK;
     cudaStream_t st = as_stream(stream);
-    cudaError_t e = cudaMemsetAsync(count_all, 0, sizeof(int32_t) * n_img * num_classes, st);
-    if (e == cudaSuccess) e = cudaMemsetAsync(count_gated, 0, sizeof(int32_t) * n_img * num_classes, st);
-    if (e != cudaSuccess) return cuda_status(e, "tss_proto_labels: memset");
     const int64_t tiles = (plane + kPT - 1) / kPT;
     dim3 grid(static_cast<unsigned>(tiles), static_cast<unsigned>(n_img));
     auto* rec = static_cast<TileRecord*>(records);
     if (num_classes <= 13)
-        proto_label_kernel<13><<<grid, 256, 0, st>>>(logits, labels_val, num_classes, plane, overflow_channel, use_conf_gate, conf_thresh, seg_label, count_all, count_gated, rec);
+        proto_label_kernel<13><<<grid, 256, 0, st>>>(logits, labels_val, num_classes, plane, overflow_channel, use_conf_gate, conf_thresh, seg_label, rec, sums_to_zero, sums_elems);
     else if (num_classes <= 19)
-        proto_label_kernel<19><<<grid, 256, 0, st>>>(logits, labels_val, num_classes, plane, overflow_channel, use_conf_gate, conf_thresh, seg_label, count_all, count_gated, rec);
+        proto_label_kernel<19><<<grid, 256, 0, st>>>(logits, labels_val, num_classes, plane, overflow_channel, use_conf_gate, conf_thresh, seg_label, rec, sums_to_zero, sums_elems);
     else
-        proto_label_kernel<TSS_MAX_CLASSES><<<grid, 256, 0, st>>>(logits, labels_val, num_classes, plane, overflow_channel, use_conf_gate, conf_thresh, seg_label, count_all, count_gated, rec);
+        proto_label_kernel<TSS_MAX_CLASSES><<<grid, 256, 0, st>>>(logits, labels_val, num_classes, plane, overflow_channel, use_conf_gate, conf_thresh, seg_label, rec, sums_to_zero, sums_elems);
     TSS_LAUNCH_CHECK("tss_proto_labels");
     return TSS_OK;
 }
@@ -507,7 +580,7 @@ static int launch_accum(const float* feat, const TileRecord* rec, int64_t N, int
 }  // namespace tss
 
 extern "C" int tss_proto_accumulate(const float* feat, const void* records, int64_t n_img, int64_t channels,
-                                    int64_t plane, int num_classes, float* sums, void* stream) {
+                                    int64_t plane, int num_classes, float* sums, int zero_sums, void* stream) {
     using namespace tss;
     TSS_REQUIRE(feat && records && sums, TSS_E_ARG, "tss_proto_accumulate: null pointer");
     TSS_REQUIRE(n_img >= 0 && plane > 0 && channels > 0, TSS_E_ARG, "tss_proto_accumulate: bad extents");
@@ -517,41 +590,73 @@ extern "C" int tss_proto_accumulate(const float* feat, const void* records, int6
                 "tss_proto_accumulate: feat and records must be 16-byte aligned");
     if (n_img == 0) return TSS_OK;
     cudaStream_t st = as_stream(stream);
-    cudaError_t e = cudaMemsetAsync(sums, 0, sizeof(float) * n_img * num_classes * channels, st);
-    if (e != cudaSuccess) return cuda_status(e, "tss_proto_accumulate: memset");
+    if (zero_sums) {
+        cudaError_t e = cudaMemsetAsync(sums, 0, sizeof(float) * n_img * num_classes * channels, st);
+        if (e != cudaSuccess) return cuda_status(e, "tss_proto_accumulate: memset");
+    }
     auto* rec = static_cast<const TileRecord*>(records);
     if (num_classes <= 13) return launch_accum<13>(feat, rec, n_img, channels, plane, num_classes, sums, st);
     if (num_classes <= 19) return launch_accum<19>(feat, rec, n_img, channels, plane, num_classes, sums, st);
     return launch_accum<TSS_MAX_CLASSES>(feat, rec, n_img, channels, plane, num_classes, sums, st);
 }
 
-extern "C" int tss_proto_finalize(const float* sums, const int32_t* count_all, const int32_t* count_gated,
-                                  int64_t n_img, int num_classes, int64_t channels, int min_pixels, float* vectors,
-                                  uint8_t* valid, float* vector_sum, void* stream) {
+extern "C" int tss_proto_finalize(const float* sums, const void* records, int64_t n_img, int num_classes,
+                                  int64_t channels, int64_t plane, int min_pixels, int32_t* count_all,
+                                  int32_t* count_gated, float* vectors, uint8_t* valid, float* vector_sum, void* stream) {
     using namespace tss;
-    TSS_REQUIRE(sums && count_all && count_gated && vectors && valid && vector_sum, TSS_E_ARG, "tss_proto_finalize: null pointer");
-    TSS_REQUIRE(n_img >= 0 && channels > 0 && num_classes >= 1 && num_classes <= TSS_MAX_CLASSES, TSS_E_ARG, "tss_proto_finalize: bad extents");
+    TSS_REQUIRE(sums && records && count_all && count_gated && vectors && valid && vector_sum, TSS_E_ARG, "tss_proto_finalize: null pointer");
+    TSS_REQUIRE(n_img >= 0 && channels > 0 && plane > 0 && num_classes >= 1 && num_classes <= TSS_MAX_CLASSES, TSS_E_ARG, "tss_proto_finalize: bad extents");
     if (n_img == 0) return TSS_OK;
     proto_finalize_kernel<<<static_cast<unsigned>(n_img * num_classes), 256, 0, as_stream(stream)>>>(
-        sums, count_all, count_gated, num_classes, channels, min_pixels, vectors, valid, vector_sum);
+        sums, static_cast<const TileRecord*>(records), (plane + kPT - 1) / kPT, num_classes, channels, min_pixels, count_all,
+        count_gated, vectors, valid, vector_sum);
     TSS_LAUNCH_CHECK("tss_proto_finalize");
     return TSS_OK;
 }
+
+namespace tss {
+static int check_update_args(const char* who, const void* protos, const void* num, const void* vectors, int64_t n_img,
+                             int num_classes, int64_t channels, int mode) {
+    TSS_REQUIRE(protos && num && vectors, TSS_E_ARG, "%s: null pointer", who);
+    TSS_REQUIRE(n_img >= 0 && channels > 0 && num_classes >= 1 && num_classes <= TSS_MAX_CLASSES, TSS_E_ARG, "%s: bad extents", who);
+    TSS_REQUIRE(mode == TSS_UPDATE_MEAN || mode == TSS_UPDATE_MOVING_AVERAGE, TSS_E_ARG, "%s: bad mode %d", who, mode);
+    TSS_REQUIRE(channels <= 256 * kUpdR, TSS_E_ARG, "%s: at most %d channels", who, 256 * kUpdR);
+    return TSS_OK;
+}
+}  // namespace tss
 
 extern "C" int tss_proto_update(float* protos, float* num, const float* vectors, const uint8_t* valid,
                                 const float* vector_sum, int64_t n_img, int num_classes, int64_t channels, int mode,
                                 int start_mean, double momentum, double cap, void* stream) {
     using namespace tss;
-    TSS_REQUIRE(protos && num && vectors, TSS_E_ARG, "tss_proto_update: null pointer");
-    TSS_REQUIRE(n_img >= 0 && channels > 0 && num_classes >= 1 && num_classes <= TSS_MAX_CLASSES, TSS_E_ARG, "tss_proto_update: bad extents");
-    TSS_REQUIRE(mode == TSS_UPDATE_MEAN || mode == TSS_UPDATE_MOVING_AVERAGE, TSS_E_ARG, "tss_proto_update: bad mode %d", mode);
-    TSS_REQUIRE(channels <= 256 * kUpdR, TSS_E_ARG, "tss_proto_update: at most %d channels", 256 * kUpdR);
+    const int rc = check_update_args("tss_proto_update", protos, num, vectors, n_img, num_classes, channels, mode);
+    if (rc != TSS_OK) return rc;
     if (n_img == 0) return TSS_OK;
     // python evaluates (1 - momentum) in double before the fp32 tensor multiply
-    proto_update_kernel<<<num_classes, 256, 0, as_stream(stream)>>>(protos, num, vectors, valid, vector_sum, n_img, num_classes,
-                                                                    channels, mode, start_mean, static_cast<float>(momentum),
-                                                                    static_cast<float>(1.0 - momentum), static_cast<float>(cap));
+    proto_update_kernel<<<num_classes, 256, 0, as_stream(stream)>>>(
+        protos, num, const_cast<float*>(vectors), const_cast<uint8_t*>(valid), const_cast<float*>(vector_sum), n_img,
+        num_classes, channels, mode, start_mean, static_cast<float>(momentum), static_cast<float>(1.0 - momentum),
+        static_cast<float>(cap), FinalizeArgs{nullptr, nullptr, 0, 0, nullptr, nullptr});
     TSS_LAUNCH_CHECK("tss_proto_update");
+    return TSS_OK;
+}
+
+extern "C" int tss_proto_finalize_update(const float* sums, const void* records, int64_t n_img, int num_classes,
+                                         int64_t channels, int64_t plane, int min_pixels, int32_t* count_all,
+                                         int32_t* count_gated, float* vectors, uint8_t* valid, float* vector_sum,
+                                         float* protos, float* num, int mode, int start_mean, double momentum,
+                                         double cap, void* stream) {
+    using namespace tss;
+    TSS_REQUIRE(sums && records && count_all && count_gated && valid && vector_sum && plane > 0, TSS_E_ARG,
+                "tss_proto_finalize_update: null pointer");
+    const int rc = check_update_args("tss_proto_finalize_update", protos, num, vectors, n_img, num_classes, channels, mode);
+    if (rc != TSS_OK) return rc;
+    if (n_img == 0) return TSS_OK;
+    proto_update_kernel<<<num_classes, 256, 0, as_stream(stream)>>>(
+        protos, num, vectors, valid, vector_sum, n_img, num_classes, channels, mode, start_mean, static_cast<float>(momentum),
+        static_cast<float>(1.0 - momentum), static_cast<float>(cap),
+        FinalizeArgs{sums, static_cast<const TileRecord*>(records), (plane + kPT - 1) / kPT, min_pixels, count_all, count_gated});
+    TSS_LAUNCH_CHECK("tss_proto_finalize_update");
     return TSS_OK;
 }
 

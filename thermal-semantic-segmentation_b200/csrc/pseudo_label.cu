@@ -242,6 +242,12 @@ __device__ __forceinline__ void up_load_row_coop(f32x2 (&dst)[C], const float* p
     }
 }
 
+__device__ __forceinline__ float set_neu(float a, float b) {  // (a != b or unordered) ? 1.0f : 0.0f  (FSET.BF)
+    float d;
+    asm("set.neu.f32.f32 %0, %1, %2;" : "=f"(d) : "f"(a), "f"(b));
+    return d;
+}
+
 __device__ __forceinline__ float rcp_refined(float s) {
     // s in [1, C]: MUFU.RCP (<= 1 ulp) + one Newton step; no special-case path
     float r;
@@ -360,21 +366,19 @@ pl_up_kernel(const PLArgs a, int64_t total_rows, int rows_per_seg, int col_block
         float ma = va[0], mb = vb[0];
 #pragma unroll
         for (int c = 1; c < C; ++c) { ma = fmaxf(ma, va[c]); mb = fmaxf(mb, vb[c]); }
-        // lowest class equal to the maximum (torch.max tie rule); two half-length select chains per pixel
-        constexpr int HALF = C / 2;
-        int ia = -1, ib = -1, ja = C - 1, jb = C - 1;
+        // lowest class equal to the maximum (torch.max tie rule) = the number of leading classes that differ
+        // from it: with ne_c = (v_c != max) as 1.0 / 0.0, idx = ne_0 (1 + ne_1 (1 + ne_2 (...))) -- one FSET per
+        // class and pixel plus ONE packed FFMA per class for the pixel pair, instead of compare + select chains
+        // on the (half-rate) ALU pipe.  Exact: every partial value is an integer <= C.
+        f32x2 hidx = pack2(0.f, 0.f);
 #pragma unroll
-        for (int c = HALF - 1; c >= 0; --c) {
-            ia = (va[c] == ma) ? c : ia;
-            ib = (vb[c] == mb) ? c : ib;
+        for (int c = C - 2; c >= 0; --c) {
+            const f32x2 ne = pack2(set_neu(va[c], ma), set_neu(vb[c], mb));
+            hidx = fma2(ne, hidx, ne);
         }
-#pragma unroll
-        for (int c = C - 2; c >= HALF; --c) {
-            ja = (va[c] == ma) ? c : ja;
-            jb = (vb[c] == mb) ? c : jb;
-        }
-        ia = ia >= 0 ? ia : ja;
-        ib = ib >= 0 ? ib : jb;
+        float fia, fib;
+        unpack2(add2(hidx, pack2(8388608.f, 8388608.f)), fia, fib);  // integer in the low mantissa bits
+        const int ia = __float_as_int(fia) & 0xff, ib = __float_as_int(fib) & 0xff;
         float sa = ma, sb = mb;  // UP_ARGMAX: the "confidence" is the max logit
         if (MODE == TSS_PL_UP_SOFTMAX) {
             const f32x2 l2e = pack2(kLog2e, kLog2e);

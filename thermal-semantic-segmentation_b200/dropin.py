@@ -48,10 +48,10 @@ class Class_Features:
 
     def update_from_batch(self, feat_cls, outputs, labels_val=None, name: str = "mean", start_mean: bool = True):
         """calculate_mean_vector + the update loop of cal_prototype.py:72-75 for one batch, on device."""
-        means = self.class_means(feat_cls, outputs, labels_val)
-        ops.prototype_update(self.objective_vectors, self.objective_vectors_num, means, _mode(name), start_mean,
-                             self.proto_momentum)
-        return means
+        return ops.class_means(feat_cls, outputs, self.class_numbers, labels_val=labels_val,
+                               overflow_channel=self.class_numbers,
+                               update=(self.objective_vectors, self.objective_vectors_num, _mode(name), start_mean,
+                                       self.proto_momentum))
 
     # -- reference signatures
     def calculate_mean_vector(self, feat_cls, outputs, labels_val=None):
@@ -368,9 +368,9 @@ class SelfTrain:
 
     def update_prototypes(self, feat_cls, outputs, name="moving_average", start_mean=False):
         """self_training.py:123-126 for one batch on device: segmented means + the sequential update."""
-        means = self.class_means(feat_cls, outputs)
-        ops.prototype_update(self._protos(), self._num(), means, _mode(name), start_mean, self.args.proto_momentum)
-        return means
+        return ops.class_means(feat_cls, outputs, self.num_classes, overflow_channel=self.args.ignore_index,
+                               use_conf_gate=True, conf_thresh=-1,
+                               update=(self._protos(), self._num(), _mode(name), start_mean, self.args.proto_momentum))
 
     # -- the step
     def step(self, source_image, source_label, target_image, target_image_full, target_lp_soft, target_lp_hard,

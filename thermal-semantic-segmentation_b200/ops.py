@@ -218,9 +218,20 @@ class ClassMeans:
     sums: torch.Tensor         # [N,C,K] fp32 raw segmented sums
 
 
+def _check_bank(protos: torch.Tensor, num: torch.Tensor, c: int, k: int) -> None:
+    for t, nm in ((protos, "protos"), (num, "num")):
+        if not (t.is_cuda and t.dtype == torch.float32 and t.is_contiguous()):
+            raise TssError("%s must be a contiguous fp32 CUDA tensor (updated in place)" % nm)
+    if protos.shape != (c, k) or num.numel() != c:
+        raise ValueError("protos %s / num %s do not match [%d,%d]" % (tuple(protos.shape), tuple(num.shape), c, k))
+
+
 def class_means(feat: torch.Tensor, logits: torch.Tensor, num_classes: int, labels_val: Optional[torch.Tensor] = None,
                 overflow_channel: Optional[int] = None, conf_thresh: Optional[float] = None,
-                use_conf_gate: bool = False, min_pixels: int = 10) -> ClassMeans:
+                use_conf_gate: bool = False, min_pixels: int = 10, update=None) -> ClassMeans:
+    """A5 (three launches: labels -> segmented sums -> means).  ``update=(protos, num, mode, start_mean,
+    momentum[, cap])``: the sequential prototype update A6 runs inside the third launch
+    (tss_proto_finalize_update), as cal_prototype.py:72-75 / self_training.py:124-126 chain the two."""
     f = _dev(feat, torch.float32, "feat")
     x = _dev(logits, torch.float32, "logits")
     n, k = f.shape[0], f.shape[1]
@@ -236,20 +247,28 @@ def class_means(feat: torch.Tensor, logits: torch.Tensor, num_classes: int, labe
     L = lib()
     rec = torch.empty(max(int(L.tss_proto_records_bytes(n, plane)), 16), dtype=torch.uint8, device=dev)
     seg = torch.empty((n, plane), dtype=torch.uint8, device=dev)
-    ca = torch.empty((n, num_classes), dtype=torch.int32, device=dev)
-    cg = torch.empty((n, num_classes), dtype=torch.int32, device=dev)
+    sums = torch.empty((n, num_classes, k), dtype=torch.float32, device=dev)
     st = _stream()
     check(L.tss_proto_labels(_ptr(x), _ptr(lv), n, num_classes, plane,
                              num_classes if overflow_channel is None else int(overflow_channel),
                              1 if use_conf_gate else 0, float(-1.0 if conf_thresh is None else conf_thresh),
-                             _ptr(seg), _ptr(ca), _ptr(cg), _ptr(rec), st), "tss_proto_labels")
-    sums = torch.empty((n, num_classes, k), dtype=torch.float32, device=dev)
-    check(L.tss_proto_accumulate(_ptr(f), _ptr(rec), n, k, plane, num_classes, _ptr(sums), st), "tss_proto_accumulate")
+                             _ptr(seg), _ptr(rec), _ptr(sums), sums.numel(), st), "tss_proto_labels")
+    check(L.tss_proto_accumulate(_ptr(f), _ptr(rec), n, k, plane, num_classes, _ptr(sums), 0, st), "tss_proto_accumulate")
+    ca = torch.empty((n, num_classes), dtype=torch.int32, device=dev)
+    cg = torch.empty((n, num_classes), dtype=torch.int32, device=dev)
     vec = torch.empty_like(sums)
     valid = torch.empty((n, num_classes), dtype=torch.uint8, device=dev)
     vsum = torch.empty((n, num_classes), dtype=torch.float32, device=dev)
-    check(L.tss_proto_finalize(_ptr(sums), _ptr(ca), _ptr(cg), n, num_classes, k, int(min_pixels), _ptr(vec), _ptr(valid),
-                               _ptr(vsum), st), "tss_proto_finalize")
+    if update is None:
+        check(L.tss_proto_finalize(_ptr(sums), _ptr(rec), n, num_classes, k, plane, int(min_pixels), _ptr(ca), _ptr(cg),
+                                   _ptr(vec), _ptr(valid), _ptr(vsum), st), "tss_proto_finalize")
+    else:
+        protos, num, mode, start_mean, momentum = update[:5]
+        cap = float(update[5]) if len(update) > 5 else 3000.0
+        _check_bank(protos, num, num_classes, k)
+        check(L.tss_proto_finalize_update(_ptr(sums), _ptr(rec), n, num_classes, k, plane, int(min_pixels), _ptr(ca),
+                                          _ptr(cg), _ptr(vec), _ptr(valid), _ptr(vsum), _ptr(protos), _ptr(num), int(mode),
+                                          1 if start_mean else 0, float(momentum), cap, st), "tss_proto_finalize_update")
     return ClassMeans(vec, valid, vsum, ca, cg, seg, sums)
 
 

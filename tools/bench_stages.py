@@ -1,0 +1,183 @@
+"""Per-kernel throughput of every stage of the label path at the BASELINE.json shapes.
+
+usage: python tools/bench_stages.py [--reps R] [--only NAME[,NAME]] > stages.jsonl
+
+One JSON line per stage: device time (CUDA events around the stage's launches, median of R after 3 warm-ups),
+algorithmic bytes (each input read once, each output written once), achieved GB/s and the fraction of the
+measured HBM peak.  Inputs rotate over enough resident copies that consecutive iterations never re-read the
+same bytes out of the 126 MB L2 (or the input itself is larger than L2).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import torch  # noqa: E402
+
+import bench  # noqa: E402
+from b200seg import ops  # noqa: E402
+
+L2 = 126e6
+dev = torch.device("cuda:0")
+PEAK, PEAK_SRC = bench.measured_peak_gbs()
+
+
+def copies_for(nbytes: float) -> int:
+    return max(2, int(2.5 * L2 // max(nbytes, 1)) + 1) if nbytes < 2.5 * L2 else 2
+
+
+def timed(fn, sets, reps):
+    for i in range(3):
+        fn(*sets[i % len(sets)])
+    torch.cuda.synchronize()
+    out = []
+    for i in range(reps):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        fn(*sets[i % len(sets)])
+        e1.record()
+        torch.cuda.synchronize()
+        out.append(e0.elapsed_time(e1) * 1e3)
+    out.sort()
+    return out[len(out) // 2], out[0]
+
+
+def report(name, shape, us_med, us_min, alg_bytes, unit_px, launches, note=""):
+    gbs = alg_bytes / (us_med * 1e-6) / 1e9
+    print(json.dumps({"stage": name, "shape": shape, "us_median": round(us_med, 2), "us_min": round(us_min, 2),
+                      "algorithmic_MB": round(alg_bytes / 1e6, 2), "GBps": round(gbs, 1), "frac_of_measured_hbm": round(gbs / PEAK, 4),
+                      "peak_GBps": PEAK, "Gpx_per_s": round(unit_px / (us_med * 1e-6) / 1e9, 3), "launches": launches,
+                      "note": note}), flush=True)
+
+
+def g(seed):
+    return torch.Generator(device=dev).manual_seed(seed)
+
+
+def stage_pl_low(reps, N, C, h, w, H, W, tag):
+    nb = 4 * N * C * h * w
+    sets = [(3.0 * torch.randn(N, C, h, w, generator=g(s), device=dev),) for s in range(copies_for(nb + 4 * N * H * W))]
+    thr, keep = 0.3, ((5, 11) if C == 13 else None)
+    fn = lambda x: ops.pseudo_label(x, size=(H, W), thr=thr, keep=keep, ignore_index=C - 1 if C == 13 else 255)
+    med, mn = timed(fn, sets, reps)
+    report("pl_low_" + tag, [N, C, h, w, H, W], med, mn, nb + N * H * W * 4, N * H * W, 1,
+           "XU/issue-bound (C ex2 per px), not HBM: see DESIGN.md section 4")
+
+
+def stage_pl_full(reps, N, C, H, W, tag):
+    nb = 4 * N * C * H * W
+    sets = [(3.0 * torch.randn(N, C, H, W, generator=g(s), device=dev),) for s in range(copies_for(nb))]
+    fn = lambda x: ops.pseudo_label(x, size=None, thr=0.3, keep=None, ignore_index=255)
+    med, mn = timed(fn, sets, reps)
+    report("pl_full_" + tag, [N, C, H, W], med, mn, nb + N * H * W * 4, N * H * W, 1, "HBM-bound: (4C+4) B/px")
+
+
+def stage_proto(reps, N, C, K, h, w, tag):
+    nb = 4 * N * (K + C) * h * w
+    sets = []
+    for s in range(copies_for(nb)):
+        sets.append((torch.randn(N, K, h, w, generator=g(s), device=dev), 3.0 * torch.randn(N, C, h, w, generator=g(100 + s), device=dev)))
+    protos = torch.zeros(C, K, device=dev)
+    num = torch.zeros(C, device=dev)
+
+    def fn(feat, logits):
+        ops.class_means(feat, logits, C, update=(protos, num, ops.UPDATE_MEAN, True, 0.9999))
+    med, mn = timed(fn, sets, reps)
+    report("proto_" + tag, [N, C, K, h, w], med, mn, nb + 4 * N * C * (K + 1), N * h * w, 5,
+           "labels + accumulate + finalize + sequential update")
+
+
+def stage_dist(reps, N, C, K, h, w, tag, rectify):
+    nb = 4 * N * K * h * w
+    sets = []
+    for s in range(copies_for(nb)):
+        feat = torch.randn(N, K, h, w, generator=g(s), device=dev)
+        soft = torch.softmax(3.0 * torch.randn(N, C, h, w, generator=g(200 + s), device=dev), 1)
+        hard = torch.full((N, 1, h, w), 255, dtype=torch.uint8, device=dev)
+        sets.append((feat, soft, hard))
+    protos = torch.randn(C, K, generator=g(7), device=dev)
+    if rectify:
+        fn = lambda f, s, hd: ops.prototype_distance(f, protos, 0.5, want_dist=False, want_weight=True, soft=s, hard=hd,
+                                                     train_thred=0.0, ignore_index=255)
+        alg = nb + N * h * w * (4 * C + 4 * C + 1 + 8)
+    else:
+        fn = lambda f, s, hd: ops.prototype_distance(f, protos, 0.5, want_dist=True, want_weight=False)
+        alg = nb + N * h * w * 4 * C
+    med, mn = timed(fn, sets, reps)
+    report(("dist_rectify_" if rectify else "dist_") + tag, [N, C, K, h, w], med, mn, alg, N * h * w, 1,
+           "feat read once; weights+rectified label fused" if rectify else "distance only")
+
+
+def stage_loss(reps, N, C, H, W, tag):
+    nb = 4 * N * C * H * W
+    sets = []
+    for s in range(copies_for(nb)):
+        x = torch.randn(N, C, H, W, generator=g(s), device=dev)
+        y = torch.randint(0, C, (N, H, W), generator=g(300 + s), device=dev, dtype=torch.int64)
+        sets.append((x, y))
+
+    def fwd(x, y):
+        return ops.ce_rce(x, y, 255, 0.1, 1.0)
+    med, mn = timed(fwd, sets, reps)
+    report("ce_rce_fwd_" + tag, [N, C, H, W], med, mn, nb + 8 * N * H * W, N * H * W, 2, "int64 targets as the reference")
+
+    def fwdbwd(x, y):
+        xr = x.requires_grad_(True)
+        out = ops.ce_rce(xr, y, 255, 0.1, 1.0)
+        (out[0] if isinstance(out, (tuple, list)) else out).backward()
+        xr.grad = None
+    med, mn = timed(fwdbwd, sets, reps)
+    report("ce_rce_fwd_bwd_" + tag, [N, C, H, W], med, mn, 3 * nb + 16 * N * H * W, N * H * W, 4,
+           "forward + backward (logits read twice, grad written once) incl. autograd overhead")
+
+
+def stage_hist(reps, n_maps, H, W, C, dtype, tag):
+    n = n_maps * H * W
+    es = torch.empty(0, dtype=dtype).element_size()
+    sets = []
+    for s in range(copies_for(2 * n * es)):
+        gt = torch.randint(0, C + 1, (n,), generator=g(s), device=dev, dtype=torch.int16).to(dtype)
+        gt[gt == C] = 255 if dtype == torch.uint8 else 255
+        same = torch.rand(n, generator=g(400 + s), device=dev) < 0.7
+        pred = torch.where(same & (gt < C), gt, torch.randint(0, C, (n,), generator=g(500 + s), device=dev, dtype=torch.int16).to(dtype))
+        sets.append((pred, gt))
+    hist = torch.zeros(C, C, dtype=torch.int64, device=dev)
+    bad = torch.zeros(1, dtype=torch.int64, device=dev)
+    fn = lambda p, t: ops.confusion_matrix(p, t, C, hist, bad)
+    med, mn = timed(fn, sets, reps)
+    report("hist_" + tag, [n_maps, H, W, C, str(dtype)], med, mn, 2 * n * es, n, 1, "%d B/px" % (2 * es))
+
+
+STAGES = {
+    "pl_low_cfg2": lambda r: stage_pl_low(r, 16, 13, 81, 241, 640, 1920, "cfg2"),
+    "pl_low_city": lambda r: stage_pl_low(r, 4, 19, 129, 257, 1024, 2048, "cityscapes19"),
+    "pl_full_cfg2": lambda r: stage_pl_full(r, 16, 13, 640, 1920, "cfg2"),
+    "pl_full_city": lambda r: stage_pl_full(r, 4, 19, 1024, 2048, "cityscapes19"),
+    "proto_cfg2": lambda r: stage_proto(r, 16, 13, 256, 81, 241, "cfg2_k256"),
+    "proto_cfg3": lambda r: stage_proto(r, 2, 19, 2048, 129, 257, "cfg3_k2048"),
+    "dist_cfg3": lambda r: stage_dist(r, 2, 19, 2048, 129, 257, "cfg3_k2048", False),
+    "dist_rectify_cfg3": lambda r: stage_dist(r, 2, 19, 2048, 129, 257, "cfg3_k2048", True),
+    "dist_rectify_k256": lambda r: stage_dist(r, 16, 13, 256, 81, 241, "cfg2_k256", True),
+    "loss_cfg2": lambda r: stage_loss(r, 4, 13, 640, 1920, "4x13x640x1920"),
+    "hist_u8": lambda r: stage_hist(r, 2000, 256, 512, 19, torch.uint8, "cfg5_u8_2000maps"),
+    "hist_i64": lambda r: stage_hist(r, 500, 256, 512, 19, torch.int64, "cfg5_i64_500maps"),
+}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--reps", type=int, default=20)
+    ap.add_argument("--only", default="")
+    a = ap.parse_args()
+    names = [n for n in a.only.split(",") if n] or list(STAGES)
+    for n in names:
+        STAGES[n](a.reps)
+        torch.cuda.empty_cache()
+
+
+if __name__ == "__main__":
+    main()

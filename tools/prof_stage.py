@@ -39,8 +39,7 @@ for i in range(reps):
                                              ignore_index=c["ignore"]))
     if stage in ("proto", "all"):
         def f():
-            m = ops.class_means(feat, logits, c["C"])
-            ops.prototype_update(protos, num, m, ops.UPDATE_MEAN, True, 0.9999)
+            ops.class_means(feat, logits, c["C"], update=(protos, num, ops.UPDATE_MEAN, True, 0.9999))
         timed("proto", f)
     if stage in ("hist", "all"):
         timed("hist", lambda: ops.confusion_matrix(pl0.label.reshape(-1), gt.reshape(-1), c["C"], hist, bad))
