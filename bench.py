@@ -194,6 +194,7 @@ def run_b200(args):
     import torch.distributed as dist
 
     from b200seg import dropin, ops, sharding
+    from b200seg.graphs import GraphedCall
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device -- the B200 path has no CPU fallback (use --impl reference "
@@ -218,17 +219,28 @@ def run_b200(args):
     def stage_proto(i):
         logits, feat, _ = sets[i % N_SETS]
         if ws == 1:
-            ops.class_means(feat, logits, C, update=(bank.protos, bank.num, bank.mode, bank.start_mean, bank.momentum))
-        else:
-            bank.update(ops.class_means(feat, logits, C))
+            return ops.class_means(feat, logits, C, update=(bank.protos, bank.num, bank.mode, bank.start_mean, bank.momentum))
+        return ops.class_means(feat, logits, C)     # the exchange (bank.update) follows outside the graph
 
     def stage_hist(i, pl):
         ops.confusion_matrix(pl.label.reshape(-1), sets[i % N_SETS][2].reshape(-1), C, meter.hist, meter.bad)
 
-    def step(i):
+    def local_step(i):
         pl = stage_pl(i)
-        stage_proto(i)
+        means = stage_proto(i)
         stage_hist(i, pl)
+        return pl, means
+
+    # One CUDA graph per resident input set: the step's launch sequence is fixed, so the host issues ONE
+    # replay per step (b200seg.graphs).  At N > 1 the prototype exchange (two small kernels + all_gather +
+    # all_reduce) runs eagerly after the replay.
+    step_graphs = [GraphedCall(lambda i=i: local_step(i)) for i in range(N_SETS)]
+    launches_per_step = step_graphs[0].launches + (2 if ws > 1 else 0)
+
+    def step(i):
+        pl, means = step_graphs[i % N_SETS].replay()
+        if ws > 1:
+            bank.update(means)
         return pl
 
     def fence():
@@ -248,7 +260,6 @@ def run_b200(args):
         time.sleep(0.35)
     meter.hist.zero_()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    launches0 = ops.launch_count()
     fence()
     t_wall0 = time.perf_counter()
     ev0.record()
@@ -258,24 +269,28 @@ def run_b200(args):
     ev1.record()
     fence()
     t_wall1 = time.perf_counter()
-    launches = ops.launch_count() - launches0
+    launches = launches_per_step * args.steps
     ms = torch.tensor([ev0.elapsed_time(ev1)], device=dev)
     if ws > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     ms = float(ms.item())
     miou = dropin.metrics_from_hist(meter.result(), C)[2]
 
-    # ---- per-stage device time (same rotation, CUDA events around every stage) -> roofline
+    # ---- per-stage device time: one graph per (stage, input set), CUDA events around every replay -> roofline
+    pl_graphs = [GraphedCall(lambda i=i: stage_pl(i)) for i in range(N_SETS)]
+    proto_graphs = [GraphedCall(lambda i=i: stage_proto(i)) for i in range(N_SETS)]
+    hist_graphs = [GraphedCall(lambda i=i: stage_hist(i, pl_graphs[i].out)) for i in range(N_SETS)]
     stage_ms = {"pseudo_label": 0.0, "prototype": 0.0, "confusion": 0.0}
     evs = []
+    fence()
     for i in range(args.steps):
         e = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
         e[0].record()
-        pl = stage_pl(i)
+        pl_graphs[i % N_SETS].replay()
         e[1].record()
-        stage_proto(i)
+        proto_graphs[i % N_SETS].replay()
         e[2].record()
-        stage_hist(i, pl)
+        hist_graphs[i % N_SETS].replay()
         e[3].record()
         evs.append(e)
     fence()
@@ -284,6 +299,7 @@ def run_b200(args):
             stage_ms[k] += e[j].elapsed_time(e[j + 1]) / args.steps
     if sampler:
         clocks = sampler.finish(t_wall0, time.perf_counter())
+    del pl_graphs, proto_graphs, hist_graphs
 
     # ---- end to end through the drop-in API: pinned host buffers, H2D + D2H inside the timed region
     e2e = run_e2e(args, dev, rank, ws, dist, dropin, ops, sharding)
@@ -304,6 +320,7 @@ def run_b200(args):
         "config": {"workload": workload_name(), "frames_per_gpu_per_step": frames, "logits": [frames, C, c["h"], c["w"]],
                    "feat": [frames, c["K"], c["h"], c["w"]], "labels": [frames, c["H"], c["W"]],
                    "l2": "inputs rotate over %d resident sets (780 MB working set > 126 MB L2)" % N_SETS,
+                   "launch": "one CUDA-graph replay per step (b200seg.graphs.GraphedCall), %d kernels per replay" % launches_per_step,
                    "parallelism": "image-sharded x%d; collectives: prototype partial [13,258] fp32 per step, "
                                   "confusion [13,13] int64 once" % ws,
                    "miou": float(miou)},

@@ -14,24 +14,44 @@ template <int CT>
 struct PixelSoftmax {
     float p[CT];   // exp(x - max), later normalised on demand
     float m, s;
-    __device__ __forceinline__ void load(const float* x, int C, int64_t plane) {
+    float xy;      // raw logit of class y (picked from registers: the streaming loads bypass L1)
+    __device__ __forceinline__ void load(const float* x, int C, int64_t plane, int y = -1) {
+        // unconditional loads (class index clamped): all C loads of the pixel are in flight together
+#pragma unroll
+        for (int c = 0; c < CT; ++c) p[c] = ldg_stream_f(x + static_cast<int64_t>(min(c, C - 1)) * plane);
         m = -INFINITY;
+        xy = 0.f;
 #pragma unroll
         for (int c = 0; c < CT; ++c)
             if (c < C) {
-                p[c] = ldg_stream_f(x + c * plane);
                 m = fmaxf(m, p[c]);
+                xy = (c == y) ? p[c] : xy;
             }
+        // exp(x - m) = 2^((x - m) * log2 e): one FFMA + one MUFU.EX2 per class (2 ulp; the loss bar is 1e-5 relative)
+        const float mb = m * kLog2e;
         s = 0.f;
 #pragma unroll
         for (int c = 0; c < CT; ++c)
             if (c < C) {
-                p[c] = expf(p[c] - m);
+                p[c] = ex2_approx(fmaf(p[c], kLog2e, -mb));
                 s += p[c];
             }
     }
-    // log-softmax of class y given the raw logit xy
-    __device__ __forceinline__ float logp(float xy) const { return (xy - m) - logf(s); }
+    __device__ __forceinline__ float log_s() const { return __logf(s); }
+    __device__ __forceinline__ float inv_s() const { return __frcp_rn(s); }
+};
+
+// (image, pixel) walk of a 1-D grid-stride loop without a 64-bit division per element
+struct PixelWalk {
+    int64_t n, p, P, sn, sp;
+    __device__ __forceinline__ PixelWalk(int64_t first, int64_t stride, int64_t plane) : P(plane) {
+        n = first / plane; p = first - n * plane;
+        sn = stride / plane; sp = stride - sn * plane;
+    }
+    __device__ __forceinline__ void next() {
+        n += sn; p += sp;
+        if (p >= P) { p -= P; ++n; }
+    }
 };
 
 template <typename T>
@@ -82,23 +102,24 @@ ce_rce_fwd_kernel(const float* __restrict__ logits, const void* __restrict__ tar
     double acc[4] = {0, 0, 0, 0};
     const int64_t total = N * P;
     const float A = rce_log_floor();
-    for (int64_t i = blockIdx.x * static_cast<int64_t>(kLossThreads) + threadIdx.x; i < total;
-         i += static_cast<int64_t>(gridDim.x) * kLossThreads) {
+    const int64_t first = blockIdx.x * static_cast<int64_t>(kLossThreads) + threadIdx.x;
+    const int64_t stride = static_cast<int64_t>(gridDim.x) * kLossThreads;
+    PixelWalk w(first, stride, P);
+    for (int64_t i = first; i < total; i += stride, w.next()) {
         const long long y = target_at<T>(target, i);
         if (y == ignore) continue;
         if (y < 0 || y >= C) { acc[3] += 1.0; continue; }
-        const int64_t n = i / P, p = i - n * P;
-        const float* x = logits + n * C * P + p;
         PixelSoftmax<CT> sm;
-        sm.load(x, C, P);
-        // -log_softmax[y] = log(s) - (x_y - m); x_y re-read (L1 hit) because p[] already holds the exponentials
-        acc[0] += static_cast<double>(logf(sm.s) - (__ldg(x + y * P) - sm.m));
+        sm.load(logits + w.n * C * P + w.p, C, P, static_cast<int>(y));
+        // -log_softmax[y] = log(s) - (x_y - m)
+        acc[0] += static_cast<double>(sm.log_s() - (sm.xy - sm.m));
         acc[2] += 1.0;
         if (with_rce) {
+            const float inv = sm.inv_s();
             float r = 0.f;
 #pragma unroll
             for (int c = 0; c < CT; ++c)
-                if (c < C && c != static_cast<int>(y)) r += fminf(fmaxf(__fdiv_rn(sm.p[c], sm.s), 1e-7f), 1.0f);
+                if (c < C && c != static_cast<int>(y)) r += fminf(fmaxf(sm.p[c] * inv, 1e-7f), 1.0f);
             acc[1] += static_cast<double>(A * r);
         }
     }
@@ -112,11 +133,12 @@ ce_rce_bwd_kernel(const float* __restrict__ logits, const void* __restrict__ tar
     const float ce_scale = scales[0], rce_scale = scales[1];
     const float A = rce_log_floor();
     const int64_t total = N * P;
-    for (int64_t i = blockIdx.x * static_cast<int64_t>(kLossThreads) + threadIdx.x; i < total;
-         i += static_cast<int64_t>(gridDim.x) * kLossThreads) {
+    const int64_t first = blockIdx.x * static_cast<int64_t>(kLossThreads) + threadIdx.x;
+    const int64_t stride = static_cast<int64_t>(gridDim.x) * kLossThreads;
+    PixelWalk w(first, stride, P);
+    for (int64_t i = first; i < total; i += stride, w.next()) {
         const long long y = target_at<T>(target, i);
-        const int64_t n = i / P, p = i - n * P;
-        float* g = grad + n * C * P + p;
+        float* g = grad + w.n * C * P + w.p;
         if (y == ignore || y < 0 || y >= C) {
 #pragma unroll
             for (int c = 0; c < CT; ++c)
@@ -124,12 +146,13 @@ ce_rce_bwd_kernel(const float* __restrict__ logits, const void* __restrict__ tar
             continue;
         }
         PixelSoftmax<CT> sm;
-        sm.load(logits + n * C * P + p, C, P);
+        sm.load(logits + w.n * C * P + w.p, C, P);
+        const float inv = sm.inv_s();
         float S = 0.f;  // sum over j != y of [1e-7 <= p_j <= 1] p_j  (clamp passes gradient inside its range)
 #pragma unroll
         for (int c = 0; c < CT; ++c)
             if (c < C) {
-                sm.p[c] = __fdiv_rn(sm.p[c], sm.s);
+                sm.p[c] = sm.p[c] * inv;
                 if (c != static_cast<int>(y) && sm.p[c] >= 1e-7f && sm.p[c] <= 1.0f) S += sm.p[c];
             }
         const float rs = rce_scale * A;
@@ -158,15 +181,16 @@ focal_fwd_kernel(const float* __restrict__ logits, const void* __restrict__ targ
                  float gamma, const float* __restrict__ alpha, double* __restrict__ part) {
     double acc[4] = {0, 0, 0, 0};
     const int64_t total = N * P;
-    for (int64_t i = blockIdx.x * static_cast<int64_t>(kLossThreads) + threadIdx.x; i < total;
-         i += static_cast<int64_t>(gridDim.x) * kLossThreads) {
+    const int64_t first = blockIdx.x * static_cast<int64_t>(kLossThreads) + threadIdx.x;
+    const int64_t stride = static_cast<int64_t>(gridDim.x) * kLossThreads;
+    PixelWalk w(first, stride, P);
+    for (int64_t i = first; i < total; i += stride, w.next()) {
         const long long y = target_at<T>(target, i);
         if (y < 0 || y >= C) { acc[3] += 1.0; continue; }
-        const int64_t n = i / P, p = i - n * P;
         PixelSoftmax<CT> sm;
-        sm.load(logits + n * C * P + p, C, P);
-        float logpt = (__ldg(logits + n * C * P + p + y * P) - sm.m) - logf(sm.s);
-        const float pt = expf(logpt);
+        sm.load(logits + w.n * C * P + w.p, C, P, static_cast<int>(y));
+        float logpt = (sm.xy - sm.m) - sm.log_s();
+        const float pt = __expf(logpt);
         if (alpha) logpt *= alpha[y];
         acc[0] += static_cast<double>(-1.0f * focal_weight(pt, gamma) * logpt);
         acc[1] += 1.0;
@@ -180,11 +204,12 @@ focal_bwd_kernel(const float* __restrict__ logits, const void* __restrict__ targ
                  float gamma, const float* __restrict__ alpha, const float* __restrict__ scale, float* __restrict__ grad) {
     const float sc = scale[0];
     const int64_t total = N * P;
-    for (int64_t i = blockIdx.x * static_cast<int64_t>(kLossThreads) + threadIdx.x; i < total;
-         i += static_cast<int64_t>(gridDim.x) * kLossThreads) {
+    const int64_t first = blockIdx.x * static_cast<int64_t>(kLossThreads) + threadIdx.x;
+    const int64_t stride = static_cast<int64_t>(gridDim.x) * kLossThreads;
+    PixelWalk w(first, stride, P);
+    for (int64_t i = first; i < total; i += stride, w.next()) {
         const long long y = target_at<T>(target, i);
-        const int64_t n = i / P, p = i - n * P;
-        float* g = grad + n * C * P + p;
+        float* g = grad + w.n * C * P + w.p;
         if (y < 0 || y >= C) {
 #pragma unroll
             for (int c = 0; c < CT; ++c)
@@ -192,13 +217,14 @@ focal_bwd_kernel(const float* __restrict__ logits, const void* __restrict__ targ
             continue;
         }
         PixelSoftmax<CT> sm;
-        sm.load(logits + n * C * P + p, C, P);
-        const float pt = expf((__ldg(logits + n * C * P + p + y * P) - sm.m) - logf(sm.s));
+        sm.load(logits + w.n * C * P + w.p, C, P, static_cast<int>(y));
+        const float pt = __expf((sm.xy - sm.m) - sm.log_s());
         // pt is detached in the reference (logpt.data.exp()): d loss / d x_c = -w * alpha_y * (delta_cy - p_c)
         const float coef = -sc * focal_weight(pt, gamma) * (alpha ? alpha[y] : 1.0f);
+        const float inv = sm.inv_s();
 #pragma unroll
         for (int c = 0; c < CT; ++c)
-            if (c < C) g[c * P] = coef * ((c == static_cast<int>(y) ? 1.f : 0.f) - __fdiv_rn(sm.p[c], sm.s));
+            if (c < C) g[c * P] = coef * ((c == static_cast<int>(y) ? 1.f : 0.f) - sm.p[c] * inv);
     }
 }
 

@@ -64,14 +64,16 @@ proto_label_kernel(const float* __restrict__ logits, const float* __restrict__ l
         if (p < P) {
             const float* x = logits + n * C * P + p;
             float v[CT];
-            float m = 0.f;
+#pragma unroll
+            for (int c = 0; c < CT; ++c) v[c] = ldg_stream_f(x + static_cast<int64_t>(min(c, C - 1)) * P);  // all in flight
+            float m = v[0];
             int t = 0;
 #pragma unroll
-            for (int c = 0; c < CT; ++c)
-                if (c < C) {
-                    v[c] = ldg_stream_f(x + c * P);
-                    if (c == 0 || v[c] > m) { m = v[c]; t = c; }
-                }
+            for (int c = 1; c < CT; ++c) {
+                const bool gt = c < C && v[c] > m;   // strict: ties keep the lowest class (torch argmax)
+                m = gt ? v[c] : m;
+                t = gt ? c : t;
+            }
             bool hot = true;
             if (labels_val != nullptr) {
                 const float lv = labels_val[n * P + p];
@@ -262,23 +264,24 @@ proto_accum_kernel(const float* __restrict__ feat, const TileRecord* __restrict_
             const TileRecord* rec = reinterpret_cast<const TileRecord*>(recs + stage * kRecBytes);
             mbar_wait(&full[stage], phase);
 #ifndef TSS_PROTO_NOCONSUME
-            // classes that own at least one of this warp's sorted positions: lane c tests class c, one ballot
-            unsigned int present;
-            {
-                const int oa = rec->off[lane], ob = rec->off[lane + 1];  // off[] has 64 entries, non-decreasing
-                present = __ballot_sync(0xffffffffu, lane < C && max(oa, s0) < min(ob, s1));
-            }
+            // Walk this warp's sorted positions [s0, s1) segment by segment.  Lane c holds class c's range
+            // [off[c], off[c+1]) of the tile; ONE ballot finds the class that owns the current position.  The
+            // loop body exists once in the instruction stream (an unrolled per-class copy thrashes the
+            // instruction cache at 19 classes); only the final "add the segment sum to class c's register
+            // accumulator" is an unrolled chain of predicated adds.
+            const int oa = rec->off[lane], ob = rec->off[lane + 1];  // off[] has 64 entries, non-decreasing
             const uint32_t row_addr = smem_u32(row);
-#pragma unroll
-            for (int c = 0; c < CT; ++c) {
-                if ((present >> c) & 1u) {   // warp-uniform
-                    const int lo = max(s0, static_cast<int>(rec->off[c]));
-                    const int b = min(s1, static_cast<int>(rec->off[c + 1]));
+            int pos = s0;
+            while (pos < s1) {  // warp-uniform
+                const unsigned int owner = __ballot_sync(0xffffffffu, oa <= pos && pos < ob);
+                const int c = __ffs(owner) - 1;
+                const int b = min(s1, __shfl_sync(0xffffffffu, ob, c));
+                if (c < C) {  // bucket C = pixels that join no sum
                     float t0 = 0.f, t1 = 0.f;
                     // aligned groups of eight sorted positions: ONE 128-bit shared load brings the eight pixel
                     // indices; the eight feature loads are unconditional (every index of a record is a valid
                     // offset into the staged row), the partial groups at the two ends of a segment select zeros
-                    for (int base = lo & ~7; base < b; base += 8) {
+                    for (int base = pos & ~7; base < b; base += 8) {
                         const uint4 iq = *reinterpret_cast<const uint4*>(&rec->idx[base]);
                         float v[8];
                         v[0] = lds_f32(row_addr + ((iq.x & 0xffffu) << 2));
@@ -289,7 +292,7 @@ proto_accum_kernel(const float* __restrict__ feat, const TileRecord* __restrict_
                         v[5] = lds_f32(row_addr + ((iq.z >> 16) << 2));
                         v[6] = lds_f32(row_addr + ((iq.w & 0xffffu) << 2));
                         v[7] = lds_f32(row_addr + ((iq.w >> 16) << 2));
-                        const int first = lo - base, last = b - base;  // valid q: first <= q < last
+                        const int first = pos - base, last = b - base;  // valid q: first <= q < last
                         if (first > 0 || last < 8) {
 #pragma unroll
                             for (int q = 0; q < 8; ++q) v[q] = (q >= first && q < last) ? v[q] : 0.f;
@@ -297,8 +300,11 @@ proto_accum_kernel(const float* __restrict__ feat, const TileRecord* __restrict_
                         t0 += (v[0] + v[1]) + (v[2] + v[3]);
                         t1 += (v[4] + v[5]) + (v[6] + v[7]);
                     }
-                    racc[c] += t0 + t1;
+                    const float t = t0 + t1;
+#pragma unroll
+                    for (int cc = 0; cc < CT; ++cc) racc[cc] += (cc == c) ? t : 0.f;
                 }
+                pos = b;
             }
 #endif
             __syncwarp();
@@ -360,12 +366,14 @@ proto_finalize_kernel(const float* __restrict__ sums, const TileRecord* __restri
 }
 
 // one CTA per class; images in order; the reference's own fp32 operation sequence.  The prototype row lives
-// in registers for the whole walk (K <= 256 * kUpdR), the skip flags of a chunk of images are staged in shared
-// memory with one parallel load, and four images' vectors are in flight at once -- the update is a chain of
-// dependent fp32 operations per channel, so latency, not bandwidth, is what has to be hidden.
-constexpr int kUpdR = 8;      // channels per thread: K <= 2048
-constexpr int kUpdChunk = 256;
-struct FinalizeArgs {  // non-null sums: the kernel first turns sums into vectors (proto_finalize fused in)
+// in registers for the whole walk (R channels per thread, K <= 256 R).  Images are taken S = 16/R at a time:
+// all S*R loads of a group are issued together (the update itself is a chain of dependent fp32 operations per
+// channel, so latency, not bandwidth, is what has to be hidden), then the group is applied in order from
+// registers.  With fin.sums != NULL the kernel first turns segmented sums into mean vectors (proto_finalize
+// fused in: counts from the tile records, vector = sum / count, the validity rules), writing the same
+// tensors tss_proto_finalize produces.
+constexpr int kUpdR = 8;      // max channels per thread: K <= 2048
+struct FinalizeArgs {
     const float* sums;
     const TileRecord* records;
     int64_t tiles;
@@ -373,108 +381,118 @@ struct FinalizeArgs {  // non-null sums: the kernel first turns sums into vector
     int32_t* cnt_all;
     int32_t* cnt_gated;
 };
+template <int R>
 __global__ void __launch_bounds__(256)
 proto_update_kernel(float* __restrict__ protos, float* __restrict__ num, float* vectors, uint8_t* valid,
                     float* vector_sum, int64_t N, int C, int64_t K, int mode, int start_mean, float m,
                     float one_minus_m, float cap, const FinalizeArgs fin) {
-    __shared__ uint8_t ok[kUpdChunk];
-    __shared__ float red[8];
-    const int c = blockIdx.x, tid = threadIdx.x;
+    constexpr int S = 16 / R;
+    __shared__ float red[8][S];
+    __shared__ int cnt_g[S], cnt_a[S];
+    __shared__ uint8_t ok[S];
+    const int c = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const bool fused = fin.sums != nullptr;
+    const bool need_sum = fused || vector_sum == nullptr;  // the `vector.sum() == 0` test is evaluated here
     float cnt = num[c];
-    const int ract = static_cast<int>((K + 255) / 256);  // live channel slots per thread (uniform)
-    float p[kUpdR];
+    float p[R];
 #pragma unroll
-    for (int r = 0; r < kUpdR; ++r) p[r] = (tid + r * 256 < K) ? protos[c * K + tid + r * 256] : 0.f;
+    for (int r = 0; r < R; ++r) p[r] = (tid + r * 256 < K) ? protos[c * K + tid + r * 256] : 0.f;
 
-    auto apply = [&](const float (&v)[kUpdR]) {
-        const bool mean = (mode == TSS_UPDATE_MEAN) || (start_mean && cnt < 100.f);
-        if (mean) {
-            const float cnt1 = cnt + 1.f;
-#pragma unroll
-            for (int r = 0; r < kUpdR; ++r)
-                if (r < ract) p[r] = __fdiv_rn(__fadd_rn(__fmul_rn(p[r], cnt), v[r]), cnt1);
-            cnt = fminf(cnt1, cap);
-        } else {
-#pragma unroll
-            for (int r = 0; r < kUpdR; ++r)
-                if (r < ract) p[r] = __fadd_rn(__fmul_rn(p[r], one_minus_m), __fmul_rn(m, v[r]));
-            cnt = fminf(cnt + 1.f, cap);
-        }
-    };
-    auto load = [&](int64_t n, float (&v)[kUpdR]) {
-        const float* src = vectors + (n * C + c) * K;
-#pragma unroll
-        for (int r = 0; r < kUpdR; ++r) v[r] = (tid + r * 256 < K) ? src[tid + r * 256] : 0.f;
-    };
-
-    for (int64_t n0 = 0; n0 < N; n0 += kUpdChunk) {
-        const int len = static_cast<int>(min(static_cast<int64_t>(kUpdChunk), N - n0));
-        __syncthreads();
-        if (fin.sums != nullptr) {
-            // fused finalize: one warp per image of the chunk -- counts from the tile records, vector = sum / count
-            // (written out: the same tensors tss_proto_finalize produces), skip flags straight into shared memory
-            const int warp = tid >> 5, lane = tid & 31;
+    for (int64_t n0 = 0; n0 < N; n0 += S) {
+        const int len = static_cast<int>(min(static_cast<int64_t>(S), N - n0));
+        if (fused) {
             for (int i = warp; i < len; i += 8) {
-                const int64_t n = n0 + i, nc = n * C + c;
                 int g, a;
-                tile_counts(fin.records + n * fin.tiles, fin.tiles, c, lane, g, a);
-                const bool good = g > 0 && a >= fin.min_pixels;
-                const float denom = static_cast<float>(g);
-                float sacc = 0.f;
-                for (int64_t k = lane; k < K; k += 32) {
-                    const float v = good ? __fdiv_rn(fin.sums[nc * K + k], denom) : 0.f;
-                    vectors[nc * K + k] = v;
-                    sacc += v;
-                }
-                sacc = warp_sum(sacc);
-                if (lane == 0) {
-                    vector_sum[nc] = sacc;
-                    valid[nc] = good ? 1 : 0;
-                    fin.cnt_all[nc] = a;
-                    fin.cnt_gated[nc] = g;
-                    ok[i] = (good && sacc != 0.f) ? 1 : 0;
+                tile_counts(fin.records + (n0 + i) * fin.tiles, fin.tiles, c, lane, g, a);
+                if (lane == 0) { cnt_g[i] = g; cnt_a[i] = a; }
+            }
+            __syncthreads();
+        }
+        float v[S][R];
+#pragma unroll
+        for (int i = 0; i < S; ++i) {
+            const int64_t nc = (n0 + i) * C + c;
+            const float* src = fused ? fin.sums : vectors;
+#pragma unroll
+            for (int r = 0; r < R; ++r) v[i][r] = (i < len && tid + r * 256 < K) ? src[nc * K + tid + r * 256] : 0.f;
+        }
+        if (fused) {
+#pragma unroll
+            for (int i = 0; i < S; ++i) {
+                if (i < len) {
+                    const int64_t nc = (n0 + i) * C + c;
+                    const bool good = cnt_g[i] > 0 && cnt_a[i] >= fin.min_pixels;
+                    const float denom = static_cast<float>(cnt_g[i]);
+#pragma unroll
+                    for (int r = 0; r < R; ++r) {
+                        v[i][r] = good ? __fdiv_rn(v[i][r], denom) : 0.f;
+                        if (tid + r * 256 < K) vectors[nc * K + tid + r * 256] = v[i][r];
+                    }
                 }
             }
-        } else if (vector_sum != nullptr) {
-            if (tid < len) {
-                const int64_t nc = (n0 + tid) * C + c;
-                ok[tid] = ((valid == nullptr || valid[nc]) && vector_sum[nc] != 0.f) ? 1 : 0;
-            }
-        } else {
-            // single-vector form: the `vector.sum() == 0` test is evaluated here
-            for (int i = 0; i < len; ++i) {
-                const int64_t nc = (n0 + i) * C + c;
+        }
+        if (need_sum) {
+#pragma unroll
+            for (int i = 0; i < S; ++i) {
                 float sacc = 0.f;
-                for (int64_t k = tid; k < K; k += 256) sacc += vectors[nc * K + k];
+#pragma unroll
+                for (int r = 0; r < R; ++r) sacc += v[i][r];
                 sacc = warp_sum(sacc);
-                __syncthreads();
-                if ((tid & 31) == 0) red[tid >> 5] = sacc;
-                __syncthreads();
-                if (tid == 0) {
-                    float tot = 0.f;
-                    for (int w = 0; w < 8; ++w) tot += red[w];
-                    ok[i] = ((valid == nullptr || valid[nc]) && tot != 0.f) ? 1 : 0;
-                }
+                if (lane == 0) red[warp][i] = sacc;
             }
         }
         __syncthreads();
-        for (int i = 0; i < len; i += 4) {
-            float v0[kUpdR], v1[kUpdR], v2[kUpdR], v3[kUpdR];
-            const bool k0 = ok[i], k1 = i + 1 < len && ok[i + 1], k2 = i + 2 < len && ok[i + 2], k3 = i + 3 < len && ok[i + 3];
-            if (k0) load(n0 + i, v0);
-            if (k1) load(n0 + i + 1, v1);
-            if (k2) load(n0 + i + 2, v2);
-            if (k3) load(n0 + i + 3, v3);
-            if (k0) apply(v0);
-            if (k1) apply(v1);
-            if (k2) apply(v2);
-            if (k3) apply(v3);
+        if (tid < len) {
+            const int64_t nc = (n0 + tid) * C + c;
+            float tot = 0.f;
+            if (need_sum) {
+                for (int w = 0; w < 8; ++w) tot += red[w][tid];
+            } else {
+                tot = vector_sum[nc];
+            }
+            bool good;
+            if (fused) {
+                good = cnt_g[tid] > 0 && cnt_a[tid] >= fin.min_pixels;
+                vector_sum[nc] = tot;
+                valid[nc] = good ? 1 : 0;
+                fin.cnt_all[nc] = cnt_a[tid];
+                fin.cnt_gated[nc] = cnt_g[tid];
+            } else {
+                good = valid == nullptr || valid[nc];
+            }
+            ok[tid] = (good && tot != 0.f) ? 1 : 0;
         }
+        __syncthreads();
+#pragma unroll
+        for (int i = 0; i < S; ++i) {
+            if (i < len && ok[i]) {
+                const bool mean = (mode == TSS_UPDATE_MEAN) || (start_mean && cnt < 100.f);
+                if (mean) {
+                    const float cnt1 = cnt + 1.f;
+#pragma unroll
+                    for (int r = 0; r < R; ++r) p[r] = __fdiv_rn(__fadd_rn(__fmul_rn(p[r], cnt), v[i][r]), cnt1);
+                    cnt = fminf(cnt1, cap);
+                } else {
+#pragma unroll
+                    for (int r = 0; r < R; ++r) p[r] = __fadd_rn(__fmul_rn(p[r], one_minus_m), __fmul_rn(m, v[i][r]));
+                    cnt = fminf(cnt + 1.f, cap);
+                }
+            }
+        }
+        __syncthreads();  // ok[] / cnt_*[] are rewritten by the next group
     }
 #pragma unroll
-    for (int r = 0; r < kUpdR; ++r)
+    for (int r = 0; r < R; ++r)
         if (tid + r * 256 < K) protos[c * K + tid + r * 256] = p[r];
     if (tid == 0) num[c] = cnt;
+}
+
+template <typename... A>
+static void launch_update(int64_t K, int C, cudaStream_t st, A... args) {
+    if (K <= 256) proto_update_kernel<1><<<C, 256, 0, st>>>(args...);
+    else if (K <= 512) proto_update_kernel<2><<<C, 256, 0, st>>>(args...);
+    else if (K <= 1024) proto_update_kernel<4><<<C, 256, 0, st>>>(args...);
+    else proto_update_kernel<8><<<C, 256, 0, st>>>(args...);
 }
 
 // closed-form weights of the same recurrence, for the sharded (all-reduce) form
@@ -633,7 +651,7 @@ extern "C" int tss_proto_update(float* protos, float* num, const float* vectors,
     if (rc != TSS_OK) return rc;
     if (n_img == 0) return TSS_OK;
     // python evaluates (1 - momentum) in double before the fp32 tensor multiply
-    proto_update_kernel<<<num_classes, 256, 0, as_stream(stream)>>>(
+    launch_update(channels, num_classes, as_stream(stream),
         protos, num, const_cast<float*>(vectors), const_cast<uint8_t*>(valid), const_cast<float*>(vector_sum), n_img,
         num_classes, channels, mode, start_mean, static_cast<float>(momentum), static_cast<float>(1.0 - momentum),
         static_cast<float>(cap), FinalizeArgs{nullptr, nullptr, 0, 0, nullptr, nullptr});
@@ -652,7 +670,7 @@ extern "C" int tss_proto_finalize_update(const float* sums, const void* records,
     const int rc = check_update_args("tss_proto_finalize_update", protos, num, vectors, n_img, num_classes, channels, mode);
     if (rc != TSS_OK) return rc;
     if (n_img == 0) return TSS_OK;
-    proto_update_kernel<<<num_classes, 256, 0, as_stream(stream)>>>(
+    launch_update(channels, num_classes, as_stream(stream),
         protos, num, vectors, valid, vector_sum, n_img, num_classes, channels, mode, start_mean, static_cast<float>(momentum),
         static_cast<float>(1.0 - momentum), static_cast<float>(cap),
         FinalizeArgs{sums, static_cast<const TileRecord*>(records), (plane + kPT - 1) / kPT, min_pixels, count_all, count_gated});

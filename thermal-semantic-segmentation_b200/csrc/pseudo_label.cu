@@ -427,11 +427,10 @@ __global__ void __launch_bounds__(256) pl_direct_kernel(const PLArgs a, int64_t 
         float v[4][CT];
         if (a.vec_ok && valid == 4) {
 #pragma unroll
-            for (int c = 0; c < CT; ++c)
-                if (c < C) {
-                    const float4 t = ldg_stream_f4(base + c * plane);
-                    v[0][c] = t.x; v[1][c] = t.y; v[2][c] = t.z; v[3][c] = t.w;
-                }
+            for (int c = 0; c < CT; ++c) {  // unconditional (clamped class): all C 128-bit loads in flight together
+                const float4 t = ldg_stream_f4(base + static_cast<int64_t>(min(c, C - 1)) * plane);
+                v[0][c] = t.x; v[1][c] = t.y; v[2][c] = t.z; v[3][c] = t.w;
+            }
         } else {
 #pragma unroll
             for (int c = 0; c < CT; ++c)
@@ -457,13 +456,12 @@ __global__ void __launch_bounds__(256) softmax_nchw_kernel(const float* __restri
         const int64_t n = i / plane, p = i - n * plane;
         const float* px = x + n * C * plane + p;
         float v[CT];
+#pragma unroll
+        for (int c = 0; c < CT; ++c) v[c] = __ldg(px + static_cast<int64_t>(min(c, C - 1)) * plane);  // all in flight
         float m = -INFINITY;
 #pragma unroll
         for (int c = 0; c < CT; ++c)
-            if (c < C) {
-                v[c] = px[c * plane];
-                m = fmaxf(m, v[c]);
-            }
+            if (c < C) m = fmaxf(m, v[c]);
         float s = 0.f;
 #pragma unroll
         for (int c = 0; c < CT; ++c)
