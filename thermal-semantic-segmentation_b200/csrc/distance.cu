@@ -7,17 +7,24 @@
 // reference's direct-difference form (p - f)^2 with packed fp32x2 math (FADD2/FFMA2: two channels per
 // issue slot), prototypes broadcast from shared memory as 128-bit loads.
 //
-// CTA = 8 warps, tile = 64 pixels (lane l owns pixels l and l+32).  The K channels are split across the
-// 8 warps (intra-CTA split-K) so that even a single 129x257 image yields > 4000 warps of loads in flight;
-// partial squared distances are combined through shared memory, then 64 threads finish sqrt / min /
-// softmax / rectify for their pixel.
+// CTA = 8 warps, persistent (one per SM, up to 255 registers per thread).  The whole prototype matrix is staged
+// ONCE per CTA when it fits shared memory (156 KB at C = 19, K = 2048).  A lane owns FOUR pixels (p, p+32, p+64,
+// p+96 of a 128-pixel warp tile) packed as two f32x2 pairs, and keeps their 2 x C squared-distance accumulators in
+// registers; a prototype value is a scalar operand broadcast to both halves of FADD2 / FFMA2.  One 128-bit
+// broadcast shared load (4 channels of one class) then feeds 16 packed FP32 instructions: the shared-memory
+// return path (128 B/clk/SM) stays at half the FP32 pipe's time -- with one or two pixels per lane it is the
+// bound.  K is split S ways across warps (S = 1 when the batch has enough tiles to fill the machine), the S
+// partials meet in shared memory.  Feature loads run D four-channel groups ahead of the arithmetic in a rotating
+// register pipeline: the kernel is FP32-pipe bound (2 flop-slots per pixel, channel and class), what has to be
+// hidden is the HBM latency.  sqrt / min / softmax / rectify finish per pixel straight from registers.
 #include "common.cuh"
 
 namespace tss {
 
 constexpr int kDThreads = 256;
 constexpr int kDWarps = 8;
-constexpr int kDTile = 64;
+constexpr int kDDepth = 4;    // four-channel groups in flight per warp (16 loads each)
+constexpr int kDWarpPx = 128; // pixels per warp tile
 
 struct DistArgs {
     const float* feat;
@@ -33,17 +40,13 @@ struct DistArgs {
     int hard_dtype, ignore;
 };
 
-// per-pixel epilogue: weights (A8) and rectified label (A10) from the C distances of pixel p of image n
+// per-pixel epilogue: weights (A8) and rectified label (A10) from the C distances d[] of pixel p of image n
 template <int CT>
-__device__ __forceinline__ void distance_epilogue(const DistArgs& a, const float* dsm, int px, int64_t n, int64_t p) {
-    float d[CT];
+__device__ __forceinline__ void distance_epilogue(const DistArgs& a, float (&d)[CT], int64_t n, int64_t p) {
     float dmin = INFINITY;
 #pragma unroll
     for (int c = 0; c < CT; ++c)
-        if (c < a.C) {
-            d[c] = dsm[c * kDTile + px];
-            dmin = fminf(dmin, d[c]);
-        }
+        if (c < a.C) dmin = fminf(dmin, d[c]);
     const int64_t obase = n * a.C * a.P + p;
     if (a.dist_out) {
 #pragma unroll
@@ -91,21 +94,23 @@ __device__ __forceinline__ void distance_epilogue(const DistArgs& a, const float
     a.label_out[n * a.P + p] = out;
 }
 
-// Persistent CTAs walk 64-pixel tiles.  When the whole prototype matrix fits shared memory (KC == K: 156 KB at
-// C = 19, K = 2048) it is staged ONCE per CTA; otherwise K is processed in chunks of KC channels that are
+// Persistent CTAs.  Warp w: pixel group w / S (128 pixels), K part w % S.  When the whole prototype matrix fits
+// shared memory (KC == K) it is staged once per CTA; otherwise K is processed in chunks of KC channels that are
 // re-staged per tile.
 template <int CT>
-__global__ void __launch_bounds__(kDThreads, 1) distance_kernel(const DistArgs a, int64_t tiles) {
+__global__ void __launch_bounds__(kDThreads, 1) distance_kernel(const DistArgs a, int64_t tiles, int S) {
     extern __shared__ __align__(16) float sm[];
     const int KC = a.KC, PS = KC + 4;  // prototype row stride in shared memory (16-byte aligned rows)
     float* ps = sm;                    // [CT][PS]
-    float* red = sm + CT * PS;         // [8][CT][64] split-K partials
-    float* dsm = red + kDWarps * CT * kDTile;  // [CT][64] distances
+    float* red = sm + CT * PS;         // [8][CT][2][32] split-K partials of one pixel pair (S > 1)
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int64_t tiles_per_img = (a.P + kDTile - 1) / kDTile;
+    const int G = kDWarps / S;         // pixel groups per CTA
+    const int grp = warp / S, part = warp - grp * S;
+    const int tile_px = kDWarpPx * G;
+    const int64_t tiles_per_img = (a.P + tile_px - 1) / tile_px;
     const bool resident = KC == a.K;
-    const int KW = KC / kDWarps;  // channels per warp per chunk (multiple of 4)
-    const int kb = warp * KW;
+    const int KW = KC / S;             // channels per warp per chunk (multiple of 4: K % 32 == 0, S <= 8)
+    const int kb = part * KW;
 
     auto stage = [&](int64_t kc0) {
         for (int i = tid; i < CT * KC; i += kDThreads) {
@@ -118,12 +123,14 @@ __global__ void __launch_bounds__(kDThreads, 1) distance_kernel(const DistArgs a
 
     for (int64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
         const int64_t n = tile / tiles_per_img;
-        const int64_t p0 = (tile - n * tiles_per_img) * kDTile;
-        const int64_t pa = min(p0 + lane, a.P - 1), pb = min(p0 + 32 + lane, a.P - 1);
+        const int64_t p0 = (tile - n * tiles_per_img) * tile_px + grp * kDWarpPx + lane;
         const float* fimg = a.feat + n * a.K * a.P;
-        f32x2 accA[CT], accB[CT];
+        int64_t po[4];
 #pragma unroll
-        for (int c = 0; c < CT; ++c) { accA[c] = 0ull; accB[c] = 0ull; }
+        for (int j = 0; j < 4; ++j) po[j] = min(p0 + 32 * j, a.P - 1);
+        f32x2 acc[CT][2];
+#pragma unroll
+        for (int c = 0; c < CT; ++c) { acc[c][0] = 0ull; acc[c][1] = 0ull; }
 
         for (int64_t kc0 = 0; kc0 < a.K; kc0 += KC) {
             if (!resident) {
@@ -131,77 +138,101 @@ __global__ void __launch_bounds__(kDThreads, 1) distance_kernel(const DistArgs a
                 stage(kc0);
                 __syncthreads();
             }
-            const float* fa = fimg + (kc0 + kb) * a.P + pa;
-            const float* fb = fimg + (kc0 + kb) * a.P + pb;
-            // four channels x two pixels of features against every class: 1 broadcast LDS.128 + 8 packed FP32 ops
-            auto compute4 = [&](const float (&r)[8], int kk) {
-                const f32x2 A01 = pack2(r[0], r[1]), A23 = pack2(r[2], r[3]), B01 = pack2(r[4], r[5]), B23 = pack2(r[6], r[7]);
+            const float* f = fimg + (kc0 + kb) * a.P;
+            const float* pk = ps + kb;
+            // raw loaded values [group][channel][pixel]; they are paired into f32x2 operands only where they are
+            // consumed -- a pack (MOV) next to the load would make the in-order warp wait for the load at once
+            float r[kDDepth][4][4];
+            auto load_group = [&](float (&dst)[4][4], int k0) {
 #pragma unroll
-                for (int c = 0; c < CT; ++c) {
-                    const ulonglong2 p = *reinterpret_cast<const ulonglong2*>(ps + c * PS + kb + kk);
-                    f32x2 d;
-                    d = sub2(p.x, A01); accA[c] = fma2(d, d, accA[c]);
-                    d = sub2(p.y, A23); accA[c] = fma2(d, d, accA[c]);
-                    d = sub2(p.x, B01); accB[c] = fma2(d, d, accB[c]);
-                    d = sub2(p.y, B23); accB[c] = fma2(d, d, accB[c]);
+                for (int q = 0; q < 4; ++q) {
+                    const float* row = f + (k0 + q) * a.P;
+#pragma unroll
+                    for (int j4 = 0; j4 < 4; ++j4) dst[q][j4] = ldg_stream_f(row + po[j4]);
                 }
             };
-            auto load4 = [&](float (&r)[8], int kk) {
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    r[j] = ldg_stream_f(fa + (kk + j) * a.P);
-                    r[4 + j] = ldg_stream_f(fb + (kk + j) * a.P);
+            for (int j = 0; j < kDDepth; ++j)
+                if (4 * j < KW) load_group(r[j], 4 * j);
+            for (int kk = 0; kk < KW; kk += 4 * kDDepth) {
+#pragma unroll
+                for (int j = 0; j < kDDepth; ++j) {
+                    const int k0 = kk + 4 * j;
+                    if (k0 < KW) {  // warp-uniform
+                        f32x2 fp[4][2];
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) {
+                            fp[q][0] = pack2(r[j][q][0], r[j][q][1]);
+                            fp[q][1] = pack2(r[j][q][2], r[j][q][3]);
+                        }
+#pragma unroll
+                        for (int c = 0; c < CT; ++c) {
+                            const float4 pr = *reinterpret_cast<const float4*>(pk + c * PS + k0);
+                            const float pv[4] = {pr.x, pr.y, pr.z, pr.w};
+#pragma unroll
+                            for (int q = 0; q < 4; ++q) {
+                                const f32x2 pp = pack2(pv[q], pv[q]);  // scalar operand, broadcast to both halves
+                                f32x2 d;
+                                d = sub2(pp, fp[q][0]); acc[c][0] = fma2(d, d, acc[c][0]);
+                                d = sub2(pp, fp[q][1]); acc[c][1] = fma2(d, d, acc[c][1]);
+                            }
+                        }
+                        const int kn = k0 + 4 * kDDepth;
+                        if (kn < KW) load_group(r[j], kn);
+                    }
                 }
-            };
-            // register pipeline, three groups deep: the loads of group g+2 are issued before group g is consumed
-            // (the kernel is FP32-pipe bound; what has to be hidden is the ~1 us HBM latency with 8 warps per SM)
-            float r0[8], r1[8], r2[8];
-            load4(r0, 0);
-            if (4 < KW) load4(r1, 4);
-            int kk = 0;
-            for (; kk + 12 <= KW; kk += 12) {
-                if (kk + 8 < KW) load4(r2, kk + 8);
-                compute4(r0, kk);
-                if (kk + 12 < KW) load4(r0, kk + 12);
-                compute4(r1, kk + 4);
-                if (kk + 16 < KW) load4(r1, kk + 16);
-                compute4(r2, kk + 8);
             }
-            // tail: 0, 4 or 8 channels left; r0 / r1 already hold them
-            if (kk < KW) compute4(r0, kk);
-            if (kk + 4 < KW) compute4(r1, kk + 4);
         }
+        // squared distances of the lane's four pixels
+        float d2[4][CT];
 #pragma unroll
         for (int c = 0; c < CT; ++c) {
-            float lo, hi;
-            unpack2(accA[c], lo, hi);
-            red[(warp * CT + c) * kDTile + lane] = lo + hi;
-            unpack2(accB[c], lo, hi);
-            red[(warp * CT + c) * kDTile + 32 + lane] = lo + hi;
+            unpack2(acc[c][0], d2[0][c], d2[1][c]);
+            unpack2(acc[c][1], d2[2][c], d2[3][c]);
         }
-        __syncthreads();
-        {
-            const int px = tid & (kDTile - 1);
-            for (int c = tid >> 6; c < a.C; c += kDThreads / kDTile) {
-                float s = 0.f;
+        if (S > 1) {  // CTA-uniform: combine the S partials, one pixel pair per round (shared-memory budget)
 #pragma unroll
-                for (int w = 0; w < kDWarps; ++w) s += red[(w * CT + c) * kDTile + px];
-                dsm[c * kDTile + px] = sqrtf(s);
+            for (int h = 0; h < 2; ++h) {
+                __syncthreads();  // the previous round's partials have been consumed
+#pragma unroll
+                for (int c = 0; c < CT; ++c) {
+                    red[((warp * CT + c) * 2 + 0) * 32 + lane] = d2[2 * h][c];
+                    red[((warp * CT + c) * 2 + 1) * 32 + lane] = d2[2 * h + 1][c];
+                }
+                __syncthreads();
+                if (part == 0) {
+                    for (int s2 = 1; s2 < S; ++s2) {
+#pragma unroll
+                        for (int c = 0; c < CT; ++c) {
+                            d2[2 * h][c] += red[(((warp + s2) * CT + c) * 2 + 0) * 32 + lane];
+                            d2[2 * h + 1][c] += red[(((warp + s2) * CT + c) * 2 + 1) * 32 + lane];
+                        }
+                    }
+                }
             }
         }
-        __syncthreads();
-        if (tid < kDTile && p0 + tid < a.P) distance_epilogue<CT>(a, dsm, tid, n, p0 + tid);
-        // the next tile's writes to red[] / dsm[] come after its own K loop and the __syncthreads above
-        // red[] is rewritten only after every thread has passed the second barrier; dsm[] readers (tid < 64) reach
-        // the first barrier of the next tile before anyone writes dsm[] again
+        if (part == 0) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int64_t p = p0 + 32 * j;
+                if (p < a.P) {
+                    float d[CT];
+#pragma unroll
+                    for (int c = 0; c < CT; ++c) d[c] = sqrtf(d2[j][c]);
+                    distance_epilogue<CT>(a, d, n, p);
+                }
+            }
+        }
     }
 }
+
+static int g_dist_split = 0;  // tuning hook: 0 = automatic
 
 template <int CT>
 static int launch_distance(DistArgs& a, cudaStream_t st) {
     // whole prototype matrix resident when it fits; else the largest K chunk 32*g (g | K/32, g <= 16)
-    const size_t fixed = sizeof(float) * (static_cast<size_t>(kDWarps) * CT * kDTile + CT * kDTile);
-    const size_t budget = 220 * 1024;
+    const size_t fixed = sizeof(float) * static_cast<size_t>(kDWarps) * CT * 2 * 32;
+    const size_t budget = 224 * 1024;
     if (fixed + sizeof(float) * CT * (a.K + 4) <= budget) {
         a.KC = static_cast<int>(a.K);
     } else {
@@ -214,18 +245,26 @@ static int launch_distance(DistArgs& a, cudaStream_t st) {
     const size_t smem = fixed + sizeof(float) * CT * (a.KC + 4);
     cudaError_t e = cudaFuncSetAttribute(distance_kernel<CT>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
     if (e != cudaSuccess) return cuda_status(e, "tss_proto_distance: smem attribute");
-    const int64_t tiles = a.N * ((a.P + kDTile - 1) / kDTile);
-    int cps = static_cast<int>(budget / (smem + 1024));   // CTAs per SM by shared memory (registers allow 1 x 255 or 2 x 128 ...)
-    if (cps > 2) cps = 2;
-    if (cps < 1) cps = 1;
-    const int64_t slots = static_cast<int64_t>(kNumSMs) * cps;
-    const unsigned grid = static_cast<unsigned>(tiles < slots ? tiles : slots);
-    distance_kernel<CT><<<grid, kDThreads, smem, st>>>(a, tiles);
+    // K split: the smallest S in {1,2,4,8} that gives every warp of the machine ~6 warp tiles (load balance)
+    const int64_t groups = a.N * ((a.P + kDWarpPx - 1) / kDWarpPx);
+    int S = 1;
+    while (S < 8 && groups * S < 6ll * kNumSMs * kDWarps) S *= 2;
+    if (g_dist_split > 0) S = g_dist_split;
+    const int tile_px = kDWarpPx * (kDWarps / S);
+    const int64_t tiles = a.N * ((a.P + tile_px - 1) / tile_px);
+    const unsigned grid = static_cast<unsigned>(tiles < kNumSMs ? tiles : kNumSMs);
+    distance_kernel<CT><<<grid, kDThreads, smem, st>>>(a, tiles, S);
     TSS_LAUNCH_CHECK("tss_proto_distance");
     return TSS_OK;
 }
 
 }  // namespace tss
+
+extern "C" int tss_tune_distance_split(int v) {
+    int old = tss::g_dist_split;
+    if (v >= 0 && (v == 0 || v == 1 || v == 2 || v == 4 || v == 8)) tss::g_dist_split = v;
+    return old;
+}
 
 extern "C" int tss_proto_distance(const float* feat, const float* protos, int64_t n_img, int64_t channels,
                                   int64_t plane, int num_classes, float temperature, float* dist_out,
