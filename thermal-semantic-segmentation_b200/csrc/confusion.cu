@@ -5,7 +5,7 @@
 //  * confusion_atomic<T>: any label dtype.  Persistent grid (multiple of 148 CTAs); every warp owns a
 //    private C*C uint32 histogram in shared memory and bumps it with shared-memory atomics; one global
 //    64-bit atomic per non-zero bin per CTA at the end.
-//  * confusion_u8_packed: uint8 labels, 16 pixels per 128-bit load.  Shared-memory atomics cannot keep
+//  * confusion_packed<T>: 16 pixels per lane and round, 128-bit loads (1 per array for uint8, 8 for int64).  Shared-memory atomics cannot keep
 //    up with 2 B/px at HBM speed (~12 px/clk/SM), so each THREAD owns a private histogram of packed
 //    8-bit counters laid out [word][lane] (bank == lane: conflict-free, no atomics), flushed into the
 //    CTA histogram every <= 240 pixels per thread, before any counter can wrap.
@@ -79,10 +79,45 @@ __device__ __forceinline__ void count4(unsigned int* lane_base, unsigned int g4,
     bump(lane_base, k23 >> 16);
 }
 
+// 16 pixels of one lane as four packed-byte quads, values clamped to <= C (anything outside [0, C) becomes C).
+// Every load instruction of the warp covers 512 contiguous bytes (lane l takes bytes [16 l, 16 l + 16)), so wider
+// label types take several loads per 16 pixels: `p` points at the first element of the warp's 512-pixel block.
+template <typename T>
+__device__ __forceinline__ void load_quads(const T* p, int lane, unsigned int C, unsigned int (&q)[4]);
+template <>
+__device__ __forceinline__ void load_quads<uint8_t>(const uint8_t* p, int lane, unsigned int, unsigned int (&q)[4]) {
+    const uint4 x = ldg_stream_u4(p + lane * 16);   // clamped later by count4's min
+    q[0] = x.x; q[1] = x.y; q[2] = x.z; q[3] = x.w;
+}
+__device__ __forceinline__ unsigned int clamp_pack4(unsigned int a, unsigned int b, unsigned int c, unsigned int d, unsigned int C) {
+    return min(a, C) | (min(b, C) << 8) | (min(c, C) << 16) | (min(d, C) << 24);   // unsigned min: negatives -> C
+}
+template <>
+__device__ __forceinline__ void load_quads<int32_t>(const int32_t* p, int lane, unsigned int C, unsigned int (&q)[4]) {
+    uint4 x[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) x[k] = ldg_stream_u4(p + k * 128 + lane * 4);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) q[k] = clamp_pack4(x[k].x, x[k].y, x[k].z, x[k].w, C);
+}
+template <>
+__device__ __forceinline__ void load_quads<int64_t>(const int64_t* p, int lane, unsigned int C, unsigned int (&q)[4]) {
+    uint4 x[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) x[k] = ldg_stream_u4(p + k * 64 + lane * 2);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const uint4 a = x[2 * k], b = x[2 * k + 1];   // two int64 each: {lo, hi, lo, hi}
+        q[k] = clamp_pack4(a.y ? C : a.x, a.w ? C : a.z, b.y ? C : b.x, b.w ? C : b.z, C);
+    }
+}
+
+template <typename T>
 __global__ void __launch_bounds__(kPackedWarps * 32)
-confusion_u8_packed(const uint8_t* __restrict__ pred, const uint8_t* __restrict__ gt, int64_t n_vec, int C, int iters,
-                    unsigned long long* __restrict__ hist, unsigned long long* __restrict__ bad) {
-    // n_vec = number of 16-pixel vectors (both pointers 16-byte aligned; the tail goes to the atomic kernel)
+confusion_packed(const T* __restrict__ pred, const T* __restrict__ gt, int64_t n_vec, int C, int iters,
+                 unsigned long long* __restrict__ hist, unsigned long long* __restrict__ bad) {
+    // n_vec = number of 16-pixel vectors, a multiple of 32 (both pointers 16-byte aligned; the tail goes to the
+    // atomic kernel)
     extern __shared__ unsigned int sh[];
     const int CP = C + 1;
     const int bins = CP * CP;
@@ -96,24 +131,21 @@ confusion_u8_packed(const uint8_t* __restrict__ pred, const uint8_t* __restrict_
     for (int i = lane; i < words * 32; i += 32) warp_base[i] = 0;
     __syncthreads();
     const unsigned int cmax2 = static_cast<unsigned int>(C) * 0x00010001u;
-    const uint4* pv = reinterpret_cast<const uint4*>(pred);
-    const uint4* gv = reinterpret_cast<const uint4*>(gt);
-    // chunk = 15 consecutive warp-wide rounds; chunks are dealt round-robin to all warps of the grid
+    // chunk = `iters` consecutive warp-wide rounds of 512 pixels; chunks are dealt round-robin to all warps
     const int64_t warps_total = static_cast<int64_t>(gridDim.x) * kPackedWarps;
     const int64_t chunk_vecs = static_cast<int64_t>(iters) * 32;  // iters <= kPackedIters: no counter can wrap
     for (int64_t chunk = static_cast<int64_t>(blockIdx.x) * kPackedWarps + warp;; chunk += warps_total) {
         const int64_t v0 = chunk * chunk_vecs;
         if (v0 >= n_vec) break;
-#pragma unroll 3
+#pragma unroll 1
         for (int it = 0; it < iters; ++it) {
-            const int64_t v = v0 + static_cast<int64_t>(it) * 32 + lane;
-            if (v < n_vec) {
-                const uint4 p = ldg_stream_u4(pv + v);
-                const uint4 g = ldg_stream_u4(gv + v);
-                count4(lane_base, g.x, p.x, CP, cmax2);
-                count4(lane_base, g.y, p.y, CP, cmax2);
-                count4(lane_base, g.z, p.z, CP, cmax2);
-                count4(lane_base, g.w, p.w, CP, cmax2);
+            const int64_t vb = v0 + static_cast<int64_t>(it) * 32;   // first vector of this round (warp-uniform)
+            if (vb < n_vec) {
+                unsigned int pq[4], gq[4];
+                load_quads<T>(pred + vb * 16, lane, static_cast<unsigned int>(C), pq);
+                load_quads<T>(gt + vb * 16, lane, static_cast<unsigned int>(C), gq);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) count4(lane_base, gq[k], pq[k], CP, cmax2);
             }
         }
         // flush this warp's 32 private columns into the CTA histogram; lane l sums word (l + 32 r) over the
@@ -183,17 +215,16 @@ extern "C" int tss_confusion(const void* pred, const void* gt, int dtype, int64_
         return static_cast<int>(need < cap ? (need < 1 ? 1 : need) : cap);
     };
     int64_t done = 0;
-    if (dtype == TSS_U8 && g_hist_variant == 1 && n >= 16 * 32 * kPackedIters &&
+    if (g_hist_variant == 1 && n >= 16 * 32 * kPackedIters &&
         (reinterpret_cast<uintptr_t>(pred) & 15) == 0 && (reinterpret_cast<uintptr_t>(gt) & 15) == 0) {
         const int CP = C + 1, bins = CP * CP, words = (bins + 3) / 4;
         const size_t sh = (static_cast<size_t>((bins + 31) & ~31) + static_cast<size_t>(kPackedWarps) * words * 32) * 4;
-        static bool attr_set = false;
-        if (!attr_set) {
-            cudaError_t e = cudaFuncSetAttribute(confusion_u8_packed, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-            if (e != cudaSuccess) return cuda_status(e, "tss_confusion: smem attribute");
-            attr_set = true;
-        }
-        const int64_t n_vec = n / 16;
+        cudaError_t e = cudaSuccess;
+        if (dtype == TSS_U8) e = cudaFuncSetAttribute(confusion_packed<uint8_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        else if (dtype == TSS_I32) e = cudaFuncSetAttribute(confusion_packed<int32_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        else e = cudaFuncSetAttribute(confusion_packed<int64_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        if (e != cudaSuccess) return cuda_status(e, "tss_confusion: smem attribute");
+        const int64_t n_vec = (n / 512) * 32;   // whole 512-pixel warp rounds
         int ctas_per_sm = static_cast<int>((220 * 1024) / (sh + 1024));
         if (ctas_per_sm > 8) ctas_per_sm = 8;
         if (ctas_per_sm < 1) ctas_per_sm = 1;
@@ -203,9 +234,12 @@ extern "C" int tss_confusion(const void* pred, const void* gt, int dtype, int64_
         if (iters > kPackedIters) iters = kPackedIters;
         if (iters < 1) iters = 1;
         const int grid = grid_for(n_vec, kPackedWarps * 32 * static_cast<int>(iters), ctas_per_sm);
-        confusion_u8_packed<<<grid, kPackedWarps * 32, sh, st>>>(static_cast<const uint8_t*>(pred),
-                                                                  static_cast<const uint8_t*>(gt), n_vec, C,
-                                                                  static_cast<int>(iters), h, b);
+        if (dtype == TSS_U8)
+            confusion_packed<uint8_t><<<grid, kPackedWarps * 32, sh, st>>>(static_cast<const uint8_t*>(pred), static_cast<const uint8_t*>(gt), n_vec, C, static_cast<int>(iters), h, b);
+        else if (dtype == TSS_I32)
+            confusion_packed<int32_t><<<grid, kPackedWarps * 32, sh, st>>>(static_cast<const int32_t*>(pred), static_cast<const int32_t*>(gt), n_vec, C, static_cast<int>(iters), h, b);
+        else
+            confusion_packed<int64_t><<<grid, kPackedWarps * 32, sh, st>>>(static_cast<const int64_t*>(pred), static_cast<const int64_t*>(gt), n_vec, C, static_cast<int>(iters), h, b);
         TSS_LAUNCH_CHECK("tss_confusion(packed)");
         done = n_vec * 16;
     }

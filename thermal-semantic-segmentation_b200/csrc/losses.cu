@@ -10,15 +10,19 @@ namespace tss {
 constexpr int kLossThreads = 256;
 constexpr int kLossMaxBlocks = kNumSMs * 8;
 
-template <int CT>
+template <int CT, bool EXACT>
 struct PixelSoftmax {
     float p[CT];   // exp(x - max), later normalised on demand
     float m, s;
     float xy;      // raw logit of class y (picked from registers: the streaming loads bypass L1)
-    __device__ __forceinline__ void load(const float* x, int C, int64_t plane, int y = -1) {
-        // unconditional loads (class index clamped): all C loads of the pixel are in flight together
+    __device__ __forceinline__ void load(const float* x, int Crt, int64_t plane, int y = -1) {
+        const int C = EXACT ? CT : Crt;   // EXACT: the class count is the template constant, every guard folds
+        // unconditional loads (class index clamped when not EXACT): all C loads of the pixel are in flight together
 #pragma unroll
-        for (int c = 0; c < CT; ++c) p[c] = ldg_stream_f(x + static_cast<int64_t>(min(c, C - 1)) * plane);
+        for (int c = 0; c < CT; ++c) {
+            p[c] = ldg_stream_f(x);
+            if (EXACT || c + 1 < C) x += plane;
+        }
         m = -INFINITY;
         xy = 0.f;
 #pragma unroll
@@ -95,12 +99,13 @@ __global__ void __launch_bounds__(256) reduce_partials_kernel(const double* __re
 // -log(clamp(0, 1e-4, 1)) in fp32, as torch.log(torch.clamp(one_hot, min=1e-4)) yields off the label
 __device__ __forceinline__ float rce_log_floor() { return -logf(1e-4f); }
 
-template <int CT, typename T>
+template <int CT, bool EXACT, typename T>
 __global__ void __launch_bounds__(kLossThreads)
 ce_rce_fwd_kernel(const float* __restrict__ logits, const void* __restrict__ target, int64_t N, int C, int64_t P,
                   int ignore, int with_rce, double* __restrict__ part) {
     double acc[4] = {0, 0, 0, 0};
     const int64_t total = N * P;
+    const int Cc = EXACT ? CT : C;   // per-class guards fold at compile time when EXACT
     const float A = rce_log_floor();
     const int64_t first = blockIdx.x * static_cast<int64_t>(kLossThreads) + threadIdx.x;
     const int64_t stride = static_cast<int64_t>(gridDim.x) * kLossThreads;
@@ -109,7 +114,7 @@ ce_rce_fwd_kernel(const float* __restrict__ logits, const void* __restrict__ tar
         const long long y = target_at<T>(target, i);
         if (y == ignore) continue;
         if (y < 0 || y >= C) { acc[3] += 1.0; continue; }
-        PixelSoftmax<CT> sm;
+        PixelSoftmax<CT, EXACT> sm;
         sm.load(logits + w.n * C * P + w.p, C, P, static_cast<int>(y));
         // -log_softmax[y] = log(s) - (x_y - m)
         acc[0] += static_cast<double>(sm.log_s() - (sm.xy - sm.m));
@@ -119,20 +124,21 @@ ce_rce_fwd_kernel(const float* __restrict__ logits, const void* __restrict__ tar
             float r = 0.f;
 #pragma unroll
             for (int c = 0; c < CT; ++c)
-                if (c < C && c != static_cast<int>(y)) r += fminf(fmaxf(sm.p[c] * inv, 1e-7f), 1.0f);
+                if (c < Cc && c != static_cast<int>(y)) r += fminf(fmaxf(sm.p[c] * inv, 1e-7f), 1.0f);
             acc[1] += static_cast<double>(A * r);
         }
     }
     block_reduce4(acc, part + blockIdx.x * 4);
 }
 
-template <int CT, typename T>
+template <int CT, bool EXACT, typename T>
 __global__ void __launch_bounds__(kLossThreads)
 ce_rce_bwd_kernel(const float* __restrict__ logits, const void* __restrict__ target, int64_t N, int C, int64_t P,
                   int ignore, const float* __restrict__ scales, float* __restrict__ grad) {
     const float ce_scale = scales[0], rce_scale = scales[1];
     const float A = rce_log_floor();
     const int64_t total = N * P;
+    const int Cc = EXACT ? CT : C;   // per-class guards fold at compile time when EXACT
     const int64_t first = blockIdx.x * static_cast<int64_t>(kLossThreads) + threadIdx.x;
     const int64_t stride = static_cast<int64_t>(gridDim.x) * kLossThreads;
     PixelWalk w(first, stride, P);
@@ -142,23 +148,23 @@ ce_rce_bwd_kernel(const float* __restrict__ logits, const void* __restrict__ tar
         if (y == ignore || y < 0 || y >= C) {
 #pragma unroll
             for (int c = 0; c < CT; ++c)
-                if (c < C) g[c * P] = 0.f;
+                if (c < Cc) g[c * P] = 0.f;
             continue;
         }
-        PixelSoftmax<CT> sm;
+        PixelSoftmax<CT, EXACT> sm;
         sm.load(logits + w.n * C * P + w.p, C, P);
         const float inv = sm.inv_s();
         float S = 0.f;  // sum over j != y of [1e-7 <= p_j <= 1] p_j  (clamp passes gradient inside its range)
 #pragma unroll
         for (int c = 0; c < CT; ++c)
-            if (c < C) {
+            if (c < Cc) {
                 sm.p[c] = sm.p[c] * inv;
                 if (c != static_cast<int>(y) && sm.p[c] >= 1e-7f && sm.p[c] <= 1.0f) S += sm.p[c];
             }
         const float rs = rce_scale * A;
 #pragma unroll
         for (int c = 0; c < CT; ++c)
-            if (c < C) {
+            if (c < Cc) {
                 const float pc = sm.p[c];
                 const bool is_y = c == static_cast<int>(y);
                 const float gate = (!is_y && pc >= 1e-7f && pc <= 1.0f) ? 1.f : 0.f;
@@ -175,19 +181,20 @@ __device__ __forceinline__ float focal_weight(float pt, float gamma) {
     return powf(q, gamma);
 }
 
-template <int CT, typename T>
+template <int CT, bool EXACT, typename T>
 __global__ void __launch_bounds__(kLossThreads)
 focal_fwd_kernel(const float* __restrict__ logits, const void* __restrict__ target, int64_t N, int C, int64_t P,
                  float gamma, const float* __restrict__ alpha, double* __restrict__ part) {
     double acc[4] = {0, 0, 0, 0};
     const int64_t total = N * P;
+    const int Cc = EXACT ? CT : C;   // per-class guards fold at compile time when EXACT
     const int64_t first = blockIdx.x * static_cast<int64_t>(kLossThreads) + threadIdx.x;
     const int64_t stride = static_cast<int64_t>(gridDim.x) * kLossThreads;
     PixelWalk w(first, stride, P);
     for (int64_t i = first; i < total; i += stride, w.next()) {
         const long long y = target_at<T>(target, i);
         if (y < 0 || y >= C) { acc[3] += 1.0; continue; }
-        PixelSoftmax<CT> sm;
+        PixelSoftmax<CT, EXACT> sm;
         sm.load(logits + w.n * C * P + w.p, C, P, static_cast<int>(y));
         float logpt = (sm.xy - sm.m) - sm.log_s();
         const float pt = __expf(logpt);
@@ -198,12 +205,13 @@ focal_fwd_kernel(const float* __restrict__ logits, const void* __restrict__ targ
     block_reduce4(acc, part + blockIdx.x * 4);
 }
 
-template <int CT, typename T>
+template <int CT, bool EXACT, typename T>
 __global__ void __launch_bounds__(kLossThreads)
 focal_bwd_kernel(const float* __restrict__ logits, const void* __restrict__ target, int64_t N, int C, int64_t P,
                  float gamma, const float* __restrict__ alpha, const float* __restrict__ scale, float* __restrict__ grad) {
     const float sc = scale[0];
     const int64_t total = N * P;
+    const int Cc = EXACT ? CT : C;   // per-class guards fold at compile time when EXACT
     const int64_t first = blockIdx.x * static_cast<int64_t>(kLossThreads) + threadIdx.x;
     const int64_t stride = static_cast<int64_t>(gridDim.x) * kLossThreads;
     PixelWalk w(first, stride, P);
@@ -213,10 +221,10 @@ focal_bwd_kernel(const float* __restrict__ logits, const void* __restrict__ targ
         if (y < 0 || y >= C) {
 #pragma unroll
             for (int c = 0; c < CT; ++c)
-                if (c < C) g[c * P] = 0.f;
+                if (c < Cc) g[c * P] = 0.f;
             continue;
         }
-        PixelSoftmax<CT> sm;
+        PixelSoftmax<CT, EXACT> sm;
         sm.load(logits + w.n * C * P + w.p, C, P, static_cast<int>(y));
         const float pt = __expf((sm.xy - sm.m) - sm.log_s());
         // pt is detached in the reference (logpt.data.exp()): d loss / d x_c = -w * alpha_y * (delta_cy - p_c)
@@ -224,7 +232,7 @@ focal_bwd_kernel(const float* __restrict__ logits, const void* __restrict__ targ
         const float inv = sm.inv_s();
 #pragma unroll
         for (int c = 0; c < CT; ++c)
-            if (c < C) g[c * P] = coef * ((c == static_cast<int>(y) ? 1.f : 0.f) - sm.p[c] * inv);
+            if (c < Cc) g[c * P] = coef * ((c == static_cast<int>(y) ? 1.f : 0.f) - sm.p[c] * inv);
     }
 }
 
@@ -234,21 +242,20 @@ static int loss_grid(int64_t total) {
     return static_cast<int>(b < 1 ? 1 : b);
 }
 
+#define TSS_DISPATCH_T(KERNEL, CT, EX, DT, GRID, ST, ...)                                                  \
+    do {                                                                                                      \
+        if ((DT) == TSS_U8) KERNEL<CT, EX, uint8_t><<<GRID, kLossThreads, 0, ST>>>(__VA_ARGS__);              \
+        else if ((DT) == TSS_I32) KERNEL<CT, EX, int32_t><<<GRID, kLossThreads, 0, ST>>>(__VA_ARGS__);        \
+        else KERNEL<CT, EX, int64_t><<<GRID, kLossThreads, 0, ST>>>(__VA_ARGS__);                             \
+    } while (0)
+// 13 (Freiburg) and 19 (Cityscapes) classes get exact specialisations; other counts the guarded generic form
 #define TSS_DISPATCH_CT_T(KERNEL, C, DT, GRID, ST, ...)                                                       \
     do {                                                                                                      \
-        if ((C) <= 13) {                                                                                      \
-            if ((DT) == TSS_U8) KERNEL<13, uint8_t><<<GRID, kLossThreads, 0, ST>>>(__VA_ARGS__);              \
-            else if ((DT) == TSS_I32) KERNEL<13, int32_t><<<GRID, kLossThreads, 0, ST>>>(__VA_ARGS__);        \
-            else KERNEL<13, int64_t><<<GRID, kLossThreads, 0, ST>>>(__VA_ARGS__);                             \
-        } else if ((C) <= 19) {                                                                               \
-            if ((DT) == TSS_U8) KERNEL<19, uint8_t><<<GRID, kLossThreads, 0, ST>>>(__VA_ARGS__);              \
-            else if ((DT) == TSS_I32) KERNEL<19, int32_t><<<GRID, kLossThreads, 0, ST>>>(__VA_ARGS__);        \
-            else KERNEL<19, int64_t><<<GRID, kLossThreads, 0, ST>>>(__VA_ARGS__);                             \
-        } else {                                                                                              \
-            if ((DT) == TSS_U8) KERNEL<TSS_MAX_CLASSES, uint8_t><<<GRID, kLossThreads, 0, ST>>>(__VA_ARGS__); \
-            else if ((DT) == TSS_I32) KERNEL<TSS_MAX_CLASSES, int32_t><<<GRID, kLossThreads, 0, ST>>>(__VA_ARGS__); \
-            else KERNEL<TSS_MAX_CLASSES, int64_t><<<GRID, kLossThreads, 0, ST>>>(__VA_ARGS__);                \
-        }                                                                                                     \
+        if ((C) == 13) TSS_DISPATCH_T(KERNEL, 13, true, DT, GRID, ST, __VA_ARGS__);                           \
+        else if ((C) == 19) TSS_DISPATCH_T(KERNEL, 19, true, DT, GRID, ST, __VA_ARGS__);                      \
+        else if ((C) < 13) TSS_DISPATCH_T(KERNEL, 13, false, DT, GRID, ST, __VA_ARGS__);                      \
+        else if ((C) < 19) TSS_DISPATCH_T(KERNEL, 19, false, DT, GRID, ST, __VA_ARGS__);                      \
+        else TSS_DISPATCH_T(KERNEL, TSS_MAX_CLASSES, false, DT, GRID, ST, __VA_ARGS__);                       \
     } while (0)
 
 static int check_loss_args(const char* who, const void* logits, const void* target, int dt, int64_t N, int C, int64_t P) {

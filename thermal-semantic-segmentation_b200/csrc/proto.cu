@@ -234,22 +234,19 @@ proto_accum_kernel(const float* __restrict__ feat, const TileRecord* __restrict_
         uint32_t phase = 0;
         int64_t cur_unit = -1;
         const int s0 = warp * (kPT / kConsumers), s1 = s0 + kPT / kConsumers;
+        // (image, channel group) finished: every warp adds its register accumulators straight to the global sums
+        // with fire-and-forget reductions (RED.ADD.F32 resolves in L2, the SM does not wait).  A CTA-level
+        // pre-reduction through shared-memory atomics costs more than it saves here: 16 warps x C ATOMS at
+        // ~64 cycles each serialise on the one shared-atomic unit (~7 us per flush).
         auto flush = [&](int64_t u) {
+            const int64_t kg = u % KG, n = u / KG;
+            float* out = sums + (n * C) * K + kg * kKT + lane;
 #pragma unroll
             for (int c = 0; c < CT; ++c)
                 if (c < C) {
-                    if (racc[c] != 0.f) atomicAdd(&acc[c * 32 + lane], racc[c]);
+                    if (racc[c] != 0.f) atomicAdd(out + c * K, racc[c]);
                     racc[c] = 0.f;
                 }
-            consumer_bar();
-            const int64_t kg = u % KG, n = u / KG;
-            float* out = sums + (n * C) * K + kg * kKT + lane;
-            for (int c = warp; c < C; c += kConsumers) {
-                const float v = acc[c * 32 + lane];
-                acc[c * 32 + lane] = 0.f;
-                if (v != 0.f) atomicAdd(out + c * K, v);
-            }
-            consumer_bar();
         };
         for (int64_t j = j0; j < j1; ++j) {
             const int64_t t = j % T;
