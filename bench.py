@@ -232,18 +232,24 @@ def run_b200(args):
         return pl, means
 
     # One CUDA graph per resident input set: the step's launch sequence is fixed, so the host issues ONE
-    # replay per step (b200seg.graphs).  At N > 1 the prototype exchange (two small kernels + all_gather +
-    # all_reduce) runs eagerly after the replay.
+    # replay per step (b200seg.graphs).  At N > 1 the prototype exchange follows the replay on the same stream:
+    # one all_gather of this rank's [16,13,256] mean vectors + the sequential update kernel over the gathered
+    # list (sharding.ShardedPrototypes.update_gathered: bit-identical banks on every rank).
+    # Tried and rejected: NCCL inside the captured graph (no gain, process-group teardown hung on this stack);
+    # the exchange on a side stream (its NCCL kernels only get SM slots between our full-machine kernels and
+    # fall behind: 0.40 ms/step against 0.29 serialised).
     step_graphs = [GraphedCall(lambda i=i: local_step(i)) for i in range(N_SETS)]
-    launches_per_step = step_graphs[0].launches + (2 if ws > 1 else 0)
+    launches_per_step = step_graphs[0].launches + (1 if ws > 1 else 0)
 
     def step(i):
         pl, means = step_graphs[i % N_SETS].replay()
         if ws > 1:
-            bank.update(means)
+            bank.update_gathered(means)
         return pl
 
     def fence():
+        if ws > 1:
+            bank.join()
         torch.cuda.synchronize()
         if ws > 1:
             dist.barrier()
@@ -265,6 +271,8 @@ def run_b200(args):
     ev0.record()
     for i in range(args.steps):
         step(i)
+    if ws > 1:
+        bank.join()                 # the timed region ends when the last exchange has landed
     sharding.all_reduce_confusion(meter.hist, meter.bad)
     ev1.record()
     fence()
@@ -275,6 +283,13 @@ def run_b200(args):
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     ms = float(ms.item())
     miou = dropin.metrics_from_hist(meter.result(), C)[2]
+    bank_spread = 0.0
+    if ws > 1:   # the replicated bank must be bit-identical on every rank (exact gathered update)
+        bank.join()
+        hi, lo = bank.protos.clone(), bank.protos.clone()
+        dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+        bank_spread = float((hi - lo).abs().max().item())
 
     # ---- per-stage device time: one graph per (stage, input set), CUDA events around every replay -> roofline
     pl_graphs = [GraphedCall(lambda i=i: stage_pl(i)) for i in range(N_SETS)]
@@ -321,9 +336,9 @@ def run_b200(args):
                    "feat": [frames, c["K"], c["h"], c["w"]], "labels": [frames, c["H"], c["W"]],
                    "l2": "inputs rotate over %d resident sets (780 MB working set > 126 MB L2)" % N_SETS,
                    "launch": "one CUDA-graph replay per step (b200seg.graphs.GraphedCall), %d kernels per replay" % launches_per_step,
-                   "parallelism": "image-sharded x%d; collectives: prototype partial [13,258] fp32 per step, "
-                                  "confusion [13,13] int64 once" % ws,
-                   "miou": float(miou)},
+                   "parallelism": "image-sharded x%d; collectives: prototype means [16,13,256] fp32 per rank and step (%s), "
+                                  "confusion [13,13] int64 once" % (ws, "one all_gather of the mean vectors + sequential update" if ws > 1 else "none at N=1"),
+                   "miou": float(miou), "bank_max_spread_over_ranks": bank_spread},
         "stages_ms": {k: round(v, 5) for k, v in stage_ms.items()},
         "stages_gbs": {k: round(alg[k] / (stage_ms[k] * 1e-3) / 1e9, 1) for k in stage_ms},
         "roofline": {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": peak, "unit": "GB/s",

@@ -299,3 +299,22 @@ def test_full_size_properties_cfg2(mods):
     assert int(m1.count_all.sum()) == n * h * w and torch.equal(m1.count_all, m1.count_gated)
     lab_low = logits.argmax(1).reshape(n, -1)
     assert torch.equal(m1.seg_label.long(), lab_low)
+
+
+def test_update_from_vectors_only_equals_flagged_update(mods):
+    """The multi-GPU exact exchange ships only the mean vectors (sharding.update_gathered): the update kernel
+    must reach the same bank from vectors alone (invalid vectors are all-zero and the kernel's own
+    `vector.sum() == 0` skip drops them) as from vectors + validity flags + sums."""
+    r = rs(77)
+    n, c, k, h, w = 6, 13, 256, 9, 17
+    feat = r.randn(n, k, h, w).astype(np.float32)
+    logits = (3 * r.randn(n, c, h, w)).astype(np.float32)
+    m = mods.ops.class_means(G(feat), G(logits), c)
+    for mode, start_mean in ((mods.ops.UPDATE_MEAN, True), (mods.ops.UPDATE_MOVING_AVERAGE, False)):
+        p1, n1 = torch.zeros(c, k, device="cuda"), torch.zeros(c, device="cuda")
+        p2, n2 = torch.zeros(c, k, device="cuda"), torch.zeros(c, device="cuda")
+        mods.ops.prototype_update(p1, n1, m, mode, start_mean, 0.05)
+        bare = mods.ops.ClassMeans(m.vectors, None, None, None, None, None, None)
+        mods.ops.prototype_update(p2, n2, bare, mode, start_mean, 0.05)
+        assert torch.equal(p1, p2) and torch.equal(n1, n2)
+        assert float(n1.sum()) > 0

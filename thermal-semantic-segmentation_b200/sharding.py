@@ -96,6 +96,7 @@ class ShardedPrototypes:
         self.protos = torch.zeros(num_classes, dim, device=device)
         self.num = torch.zeros(num_classes, device=device)
         self.mode, self.start_mean, self.momentum, self.cap, self.group = mode, start_mean, momentum, cap, group
+        self._comm = None          # side stream of update_overlapped
 
     def update(self, means) -> None:
         """means: ops.ClassMeans of this rank's batch.  Two kernels + (all_gather, all_reduce) per step."""
@@ -107,3 +108,49 @@ class ShardedPrototypes:
         partial, scale0, num_after = ops.prototype_update_partial(means, self.num, self.mode, self.start_mean,
                                                                   self.momentum, first, total, self.cap)
         apply_prototype_partial(self.protos, self.num, partial, scale0, num_after, self.group)
+
+    def update_gathered(self, means) -> None:
+        """Exact form for equal per-rank batches: ONE all_gather of the per-(image, class) mean vectors in rank
+        order = global image order, then the SAME sequential update kernel as the single-GPU path over the
+        gathered list.  Vectors that fail the validity rules are all-zero, and the kernel re-evaluates the
+        reference's `vector.sum() == 0` skip itself, so no flags travel.  Every rank ends with the
+        bit-identical bank the reference's loop would produce; one small collective (n*C*K*4 bytes per rank:
+        213 KB at 16 x 13 x 256) and one launch per step."""
+        from . import ops
+
+        rank, ws = world(self.group)
+        if ws == 1:
+            ops.prototype_update(self.protos, self.num, means, self.mode, self.start_mean, self.momentum, self.cap)
+            return
+        n, c, k = means.vectors.shape
+        if getattr(self, "_gkey", None) != (n, c, k):
+            self._gv = torch.empty((ws * n, c, k), dtype=torch.float32, device=self.protos.device)
+            self._gkey = (n, c, k)
+        dist.all_gather_into_tensor(self._gv, means.vectors, group=self.group)
+        gathered = ops.ClassMeans(self._gv, None, None, None, None, None, None)
+        ops.prototype_update(self.protos, self.num, gathered, self.mode, self.start_mean, self.momentum, self.cap)
+
+    def update_overlapped(self, means, gathered: bool = True):
+        """Same as update(), on a side stream: the exchange is two tiny kernels and two latency-bound
+        collectives, and nothing on the compute stream reads the bank until the NEXT exchange, so it overlaps
+        the following step's label kernels.  ``means`` must stay untouched until the returned event has
+        completed (wait on it before overwriting those tensors); call join() before reading protos / num."""
+        cur = torch.cuda.current_stream(self.protos.device)
+        if self._comm is None:
+            self._comm = torch.cuda.Stream(self.protos.device)
+        ready = torch.cuda.Event()
+        ready.record(cur)
+        with torch.cuda.stream(self._comm):
+            self._comm.wait_event(ready)
+            if gathered:
+                self.update_gathered(means)
+            else:
+                self.update(means)
+            done = torch.cuda.Event()
+            done.record(self._comm)
+        return done
+
+    def join(self) -> None:
+        """Make the current stream wait for every overlapped exchange issued so far."""
+        if self._comm is not None:
+            torch.cuda.current_stream(self.protos.device).wait_stream(self._comm)
