@@ -369,6 +369,24 @@ def test_distance_vs_oracle_shapes(ops, shape):
         assert bad.mean() < 1e-3
 
 
+@pytest.mark.parametrize("variant", [0, 1, 2, 4])
+@pytest.mark.parametrize("split", [0, 1, 2, 4])
+def test_distance_kernel_forms_agree(ops, variant, split):
+    """every kernel form / K split behind tss_proto_distance gives the oracle's distances (ragged plane: 23*37 px)"""
+    from b200seg import lib
+    n, k, c, h, w = 2, 128, 19, 23, 37
+    feat, protos = gi.randn(1400, n, k, h, w), gi.randn(1401, c, k)
+    d_ref = O.prototype_distance(T(feat), T(protos)).numpy()
+    old_v, old_s = lib().tss_tune_distance_variant(variant), lib().tss_tune_distance_split(split)
+    try:
+        d, _, _ = ops.prototype_distance(G(feat), G(protos), temperature=0.5, want_dist=True)
+        got = d.cpu().numpy()
+    finally:
+        lib().tss_tune_distance_variant(old_v)
+        lib().tss_tune_distance_split(old_s)
+    np.testing.assert_allclose(got, d_ref, rtol=RTOL)
+
+
 # ------------------------------------------------------------------------------------------- A11-A13
 def test_ce_rce_golden(ops, golden):
     logits, label = gi.ce_inputs()

@@ -226,10 +226,173 @@ __global__ void __launch_bounds__(kDThreads, 1) distance_kernel(const DistArgs a
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Thread-level-parallel form.  ONE large CTA per SM shares the whole prototype matrix in shared memory and every
+// warp works on its own pixel unit with no CTA-wide synchronisation after the prologue.  A lane owns PX (2 or 4)
+// pixels as packed pairs, so a thread needs CT*PX accumulator registers + one 4-channel group of loaded values
+// and the SM holds 12-32 warps: the latency of the feature loads is hidden by warp switching instead of by a
+// register pipeline (whose loads share the warp's few scoreboards, so waiting for the oldest group also waits
+// for the newest).  Load balance comes from an INTRA-warp K split: the warp's lanes form SI (1, 2 or 4) parts
+// of L = 32/SI lanes; all parts cover the same PX*L pixels, part s reads channels [s*K/SI, (s+1)*K/SI), and the
+// partial sums meet in log2(SI) xor-shuffles -- no shared-memory exchange, no barrier, and units small enough
+// (down to 16 pixels) that the last round of the persistent loop is nearly full.  A quarter warp (8 lanes) always
+// lies inside one part, so the float4 prototype read stays a broadcast.
+template <int CT, int PX>
+struct TlpCfg {
+    static constexpr int kAcc = CT * PX;
+    static constexpr int kWarps = kAcc <= 26 ? 32 : kAcc <= 40 ? 24 : kAcc <= 56 ? 20 : kAcc <= 80 ? 16 : 12;
+    static constexpr int kThreads = kWarps * 32;
+};
+
+template <int CT, int PX>
+__global__ void __launch_bounds__(TlpCfg<CT, PX>::kThreads, 1) distance_tlp_kernel(const DistArgs a, int64_t units, int SI) {
+    constexpr int W = TlpCfg<CT, PX>::kWarps;
+    constexpr int PP = PX / 2;
+    extern __shared__ __align__(16) float ps[];  // [CT][K], rows >= C zero
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int K = static_cast<int>(a.K);
+    for (int i = tid; i < CT * K; i += TlpCfg<CT, PX>::kThreads) ps[i] = (i < a.C * K) ? a.protos[i] : 0.f;
+    __syncthreads();
+
+    const int L = 32 / SI;
+    const int part = lane / L, j = lane - part * L;
+    const int unit_px = PX * L;
+    const int64_t units_per_img = (a.P + unit_px - 1) / unit_px;
+    const int KW = K / SI;
+    const float* pk = ps + part * KW;
+    const int64_t P = a.P;
+
+    for (int64_t u = static_cast<int64_t>(blockIdx.x) * W + warp; u < units; u += static_cast<int64_t>(gridDim.x) * W) {
+        const int64_t n = u / units_per_img;
+        const int64_t base = (u - n * units_per_img) * unit_px + j;
+        const int64_t first = min(base, P - 1);
+        int off[PX];
+#pragma unroll
+        for (int i = 0; i < PX; ++i) off[i] = static_cast<int>(min(base + i * L, P - 1) - first);
+        const float* row = a.feat + (n * a.K + static_cast<int64_t>(part) * KW) * P + first;
+        f32x2 acc[CT][PP];
+#pragma unroll
+        for (int c = 0; c < CT; ++c)
+#pragma unroll
+            for (int h = 0; h < PP; ++h) acc[c][h] = 0ull;
+
+#pragma unroll(PX == 2 ? 2 : 1)
+        for (int kk = 0; kk < KW; kk += 4) {
+            float x[4][PX];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+#pragma unroll
+                for (int i = 0; i < PX; ++i) x[q][i] = ldg_stream_f(row + off[i]);
+                row += P;
+            }
+            f32x2 xp[4][PP];
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+#pragma unroll
+                for (int h = 0; h < PP; ++h) xp[q][h] = pack2(x[q][2 * h], x[q][2 * h + 1]);
+#pragma unroll
+            for (int c = 0; c < CT; ++c) {
+                const float4 pr = *reinterpret_cast<const float4*>(pk + c * K + kk);
+                const float pv[4] = {pr.x, pr.y, pr.z, pr.w};
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const f32x2 pb = pack2(pv[q], pv[q]);
+#pragma unroll
+                    for (int h = 0; h < PP; ++h) {
+                        const f32x2 d = sub2(pb, xp[q][h]);
+                        acc[c][h] = fma2(d, d, acc[c][h]);
+                    }
+                }
+            }
+        }
+        for (int o = 16; o >= L; o >>= 1) {  // partial sums of the SI parts (no iteration when SI == 1)
+#pragma unroll
+            for (int c = 0; c < CT; ++c)
+#pragma unroll
+                for (int h = 0; h < PP; ++h) acc[c][h] = add2(acc[c][h], __shfl_xor_sync(0xffffffffu, acc[c][h], o));
+        }
+#pragma unroll
+        for (int i = 0; i < PX; ++i) {   // pixel i of the unit is finished by part i mod SI
+            const int64_t p = base + i * L;
+            if ((i & (SI - 1)) == part && p < P) {
+                float d[CT];
+#pragma unroll
+                for (int c = 0; c < CT; ++c) {
+                    float lo, hi;
+                    unpack2(acc[c][i >> 1], lo, hi);
+                    d[c] = sqrtf((i & 1) ? hi : lo);
+                }
+                distance_epilogue<CT>(a, d, n, p);
+            }
+        }
+    }
+}
+
+// Relative cost of one (PX, SI) form on this problem: rounds of the persistent loop on the busiest warp x channel
+// steps per round x pixels a round retires per SM x the measured per-pixel-channel cost of the form (4 px per
+// lane holds fewer warps: x1.12; 8-lane parts fetch 32-byte pieces of a row: x1.2 / x1.1).  B200 measurements
+// behind the factors: profiles/r01_distance_forms.txt.
+template <int CT, int PX>
+static double tlp_cost(const DistArgs& a, int SI) {
+    constexpr int W = TlpCfg<CT, PX>::kWarps;
+    const int unit_px = PX * 32 / SI;
+    const int64_t units = a.N * ((a.P + unit_px - 1) / unit_px);
+    const int64_t slots = static_cast<int64_t>(kNumSMs) * W;
+    const double rounds = static_cast<double>((units + slots - 1) / slots);
+    double f = (PX == 4) ? 1.12 : 1.0;
+    if (SI == 4) f *= (PX == 4) ? 1.1 : 1.2;
+    return rounds * (static_cast<double>(a.K) / SI + 16.0) * (W * PX * 32) * f;
+}
+
+template <int CT, int PX>
+static int launch_distance_tlp(DistArgs& a, int SI, cudaStream_t st) {
+    constexpr int W = TlpCfg<CT, PX>::kWarps;
+    const size_t smem = sizeof(float) * CT * static_cast<size_t>(a.K);
+    const int unit_px = PX * 32 / SI;
+    const int64_t units = a.N * ((a.P + unit_px - 1) / unit_px);
+    cudaError_t e = cudaFuncSetAttribute(distance_tlp_kernel<CT, PX>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+    if (e != cudaSuccess) return cuda_status(e, "tss_proto_distance: smem attribute");
+    const int64_t ctas = (units + W - 1) / W;
+    const unsigned grid = static_cast<unsigned>(ctas < kNumSMs ? ctas : kNumSMs);
+    distance_tlp_kernel<CT, PX><<<grid, TlpCfg<CT, PX>::kThreads, smem, st>>>(a, units, SI);
+    TSS_LAUNCH_CHECK("tss_proto_distance(tlp)");
+    return TSS_OK;
+}
+
+// tuning hooks: form 0 = automatic, 1 = 8-warp register-pipeline kernel, 2 / 4 = thread-level-parallel kernel with
+// 2 / 4 pixels per lane; split 0 = automatic, else the K split
+static int g_dist_variant = 0;
+int g_dist_split_value();
+
+// returns TSS_OK after a launch, or -1 when the thread-level-parallel form does not apply
+template <int CT>
+static int launch_distance_auto(DistArgs& a, cudaStream_t st) {
+    if (g_dist_variant == 1) return -1;
+    if (sizeof(float) * CT * static_cast<size_t>(a.K) > 226 * 1024) return -1;   // prototypes must be resident
+    const int forced = g_dist_split_value();
+    int best_px = 2, best_si = 1;
+    double best = 1e300;
+    for (int px = 2; px <= 4; px += 2) {
+        if (g_dist_variant != 0 && g_dist_variant != px) continue;
+        for (int si = 1; si <= 4; si *= 2) {
+            if (forced != 0 && forced != si) continue;
+            const double c = (px == 2) ? tlp_cost<CT, 2>(a, si) : tlp_cost<CT, 4>(a, si);
+            if (c < best) { best = c; best_px = px; best_si = si; }
+        }
+    }
+    if (best == 1e300) return -1;   // forced split 8: only the register-pipeline kernel has it
+    return best_px == 2 ? launch_distance_tlp<CT, 2>(a, best_si, st) : launch_distance_tlp<CT, 4>(a, best_si, st);
+}
+
 static int g_dist_split = 0;  // tuning hook: 0 = automatic
+int g_dist_split_value() { return g_dist_split; }
 
 template <int CT>
 static int launch_distance(DistArgs& a, cudaStream_t st) {
+    {
+        const int r = launch_distance_auto<CT>(a, st);
+        if (r != -1) return r;
+    }
     // whole prototype matrix resident when it fits; else the largest K chunk 32*g (g | K/32, g <= 16)
     const size_t fixed = sizeof(float) * static_cast<size_t>(kDWarps) * CT * 2 * 32;
     const size_t budget = 224 * 1024;
@@ -259,6 +422,12 @@ static int launch_distance(DistArgs& a, cudaStream_t st) {
 }
 
 }  // namespace tss
+
+extern "C" int tss_tune_distance_variant(int v) {
+    int old = tss::g_dist_variant;
+    if (v == 0 || v == 1 || v == 2 || v == 4) tss::g_dist_variant = v;
+    return old;
+}
 
 extern "C" int tss_tune_distance_split(int v) {
     int old = tss::g_dist_split;
