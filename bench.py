@@ -221,6 +221,27 @@ def run_b200(args):
 
     bank = sharding.ShardedPrototypes(C, c["K"], dev, ops.UPDATE_MEAN, True, 0.9999)
     meter = dropin.ConfusionMeter(C, dev)
+    # N > 1: the mean vectors are exchanged by the finalize kernel's own stores into every peer's gather buffer
+    # (sharding.PeerGather, symmetric memory over NVLink); NCCL all_gather is the fallback when peer mapping is
+    # not available.  All ranks must agree, so the outcome is all-reduced.
+    gather, exchange = None, "none at N=1"
+    if ws > 1:
+        ok = torch.ones(1, device=dev)
+        if args.exchange == "peer":
+            try:
+                gather = sharding.PeerGather(frames, C, c["K"], dev)
+            except Exception as e:  # noqa: BLE001
+                print("bench.py: rank %d: peer-memory exchange unavailable (%s: %s), using NCCL all_gather" % (rank, type(e).__name__, e),
+                      file=sys.stderr, flush=True)
+                ok.zero_()
+        else:
+            ok.zero_()
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if ok.item() == 0:
+            gather = None
+        exchange = ("finalize kernel stores its mean vectors into every rank's symmetric-memory gather buffer over NVLink, one barrier, "
+                    "sequential update kernel; all inside the step's CUDA graph" if gather is not None else
+                    "one NCCL all_gather of the mean vectors + sequential update kernel after the graph replay")
 
     def stage_pl(i):
         return ops.pseudo_label(sets[i % N_SETS][0], size=size, thr=c["thr"], keep=c["keep"], ignore_index=c["ignore"])
@@ -229,7 +250,11 @@ def run_b200(args):
         logits, feat, _ = sets[i % N_SETS]
         if ws == 1:
             return ops.class_means(feat, logits, C, update=(bank.protos, bank.num, bank.mode, bank.start_mean, bank.momentum))
-        return ops.class_means(feat, logits, C)     # the exchange (bank.update) follows outside the graph
+        if gather is not None:                      # slots alternate with i: see sharding.PeerGather
+            means = ops.class_means(feat, logits, C, scatter=gather.targets(i % 2))
+            bank.update_from_peers(gather, i % 2)
+            return means
+        return ops.class_means(feat, logits, C)     # the exchange (bank.update_gathered) follows outside the graph
 
     def stage_hist(i, pl):
         ops.confusion_matrix(pl.label.reshape(-1), sets[i % N_SETS][2].reshape(-1), C, meter.hist, meter.bad)
@@ -247,12 +272,13 @@ def run_b200(args):
     # Tried and rejected: NCCL inside the captured graph (no gain, process-group teardown hung on this stack);
     # the exchange on a side stream (its NCCL kernels only get SM slots between our full-machine kernels and
     # fall behind: 0.40 ms/step against 0.29 serialised).
-    step_graphs = [GraphedCall(lambda i=i: local_step(i)) for i in range(N_SETS)]
-    launches_per_step = step_graphs[0].launches + (1 if ws > 1 else 0)
+    # (one warm-up call per graph: consecutive steps must alternate the gather slot)
+    step_graphs = [GraphedCall(lambda i=i: local_step(i), warmup=1) for i in range(N_SETS)]
+    launches_per_step = step_graphs[0].launches + (1 if ws > 1 and gather is None else 0)
 
     def step(i):
         pl, means = step_graphs[i % N_SETS].replay()
-        if ws > 1:
+        if ws > 1 and gather is None:
             bank.update_gathered(means)
         return pl
 
@@ -302,7 +328,7 @@ def run_b200(args):
 
     # ---- per-stage device time: one graph per (stage, input set), CUDA events around every replay -> roofline
     pl_graphs = [GraphedCall(lambda i=i: stage_pl(i)) for i in range(N_SETS)]
-    proto_graphs = [GraphedCall(lambda i=i: stage_proto(i)) for i in range(N_SETS)]
+    proto_graphs = [GraphedCall(lambda i=i: stage_proto(i), warmup=1) for i in range(N_SETS)]
     hist_graphs = [GraphedCall(lambda i=i: stage_hist(i, pl_graphs[i].out)) for i in range(N_SETS)]
     stage_ms = {"pseudo_label": 0.0, "prototype": 0.0, "confusion": 0.0}
     evs = []
@@ -346,7 +372,7 @@ def run_b200(args):
                    "l2": "inputs rotate over %d resident sets (780 MB working set > 126 MB L2)" % N_SETS,
                    "launch": "one CUDA-graph replay per step (b200seg.graphs.GraphedCall), %d kernels per replay" % launches_per_step,
                    "parallelism": "image-sharded x%d; collectives: prototype means [16,13,256] fp32 per rank and step (%s), "
-                                  "confusion [13,13] int64 once" % (ws, "one all_gather of the mean vectors + sequential update" if ws > 1 else "none at N=1"),
+                                  "confusion [13,13] int64 once" % (ws, exchange),
                    "miou": float(miou), "bank_max_spread_over_ranks": bank_spread},
         "stages_ms": {k: round(v, 5) for k, v in stage_ms.items()},
         "stages_gbs": {k: round(alg[k] / (stage_ms[k] * 1e-3) / 1e9, 1) for k in stage_ms},
@@ -417,6 +443,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
+                    help="N > 1 prototype exchange: peer-memory stores from the finalize kernel (default) or NCCL all_gather")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -159,6 +159,17 @@ int tss_proto_accumulate(const float* feat, const void* records, int64_t n_img, 
 int tss_proto_finalize(const float* sums, const void* records, int64_t n_img, int num_classes,
                        int64_t channels, int64_t plane, int min_pixels, int32_t* count_all,
                        int32_t* count_gated, float* vectors, uint8_t* valid, float* vector_sum, void* stream);
+/* Step 3 on a sharded batch: the same outputs, and `vectors` is ALSO stored through
+ * peer_vectors[0 .. n_peers) (n_peers <= 7) -- device pointers into other GPUs' memory that this process has
+ * mapped (CUDA IPC / symmetric memory), each the [N,C,K] slot of this rank in that GPU's gather buffer;
+ * peer_vector_sums (or NULL) likewise receives vector_sum [N,C].  The
+ * exchange of the reference's per-image mean vectors is then the kernel's own NVLink store stream; a barrier
+ * and tss_proto_update over the gathered [ranks*N,C,K] buffer follow on every rank. */
+int tss_proto_finalize_scatter(const float* sums, const void* records, int64_t n_img, int num_classes,
+                               int64_t channels, int64_t plane, int min_pixels, int32_t* count_all,
+                               int32_t* count_gated, float* vectors, uint8_t* valid, float* vector_sum,
+                               float* const* peer_vectors, float* const* peer_vector_sums, int n_peers,
+                               void* stream);
 int tss_proto_finalize_update(const float* sums, const void* records, int64_t n_img, int num_classes,
                               int64_t channels, int64_t plane, int min_pixels, int32_t* count_all,
                               int32_t* count_gated, float* vectors, uint8_t* valid, float* vector_sum,

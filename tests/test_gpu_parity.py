@@ -308,6 +308,25 @@ def test_prototype_update_partial_matches_sequential(ops):
             close_vec(a, b)
 
 
+def test_finalize_scatter_writes_every_destination(ops):
+    """tss_proto_finalize_scatter: the mean vectors land in vectors_out and in every extra destination (the peers'
+    gather slots at N > 1; plain device buffers here), identical to tss_proto_finalize"""
+    n, k, c, h, w = 3, 64, 13, 19, 23
+    feat, logits = G(gi.randn(1500, n, k, h, w)), G(gi.randn(1501, n, c, h, w, scale=3.0))
+    ref = ops.class_means(feat, logits, c)
+    out = torch.full((n, c, k), -7.0, device="cuda")
+    extra = [torch.full((n, c, k), -7.0, device="cuda") for _ in range(3)]
+    out_s = torch.full((n, c), -7.0, device="cuda")
+    extra_s = [torch.full((n, c), -7.0, device="cuda") for _ in range(3)]
+    got = ops.class_means(feat, logits, c, scatter=(out, out_s, [e.data_ptr() for e in extra], [e.data_ptr() for e in extra_s]))
+    assert got.vectors.data_ptr() == out.data_ptr()
+    for t in [out] + extra:
+        assert torch.equal(t, ref.vectors)
+    for t in [out_s] + extra_s:
+        assert torch.equal(t, ref.vector_sum)
+    assert torch.equal(got.valid, ref.valid) and torch.equal(got.count_gated, ref.count_gated)
+
+
 # ------------------------------------------------------------------------------------------- A7/A8/A10
 def test_distance_weight_golden(ops, golden):
     protos = G(gi.selftrain_protos())

@@ -325,10 +325,20 @@ __device__ __forceinline__ void tile_counts(const TileRecord* __restrict__ rec, 
     all = __reduce_add_sync(0xffffffffu, a);
 }
 
+// Destinations in other GPUs' memory (peer-mapped, e.g. symmetric-memory buffers): the multi-GPU prototype
+// exchange is the finalize kernel's own store stream, not a separate collective.
+constexpr int kMaxPeers = 7;
+struct PeerList {
+    float* dst[kMaxPeers];   // [N,C,K] mean vectors
+    float* sum[kMaxPeers];   // [N,C] their sums over K (NULL: not sent)
+    int n;
+};
+
 __global__ void __launch_bounds__(256)
 proto_finalize_kernel(const float* __restrict__ sums, const TileRecord* __restrict__ records, int64_t tiles, int C,
                       int64_t K, int min_pixels, int32_t* __restrict__ cnt_all, int32_t* __restrict__ cnt_gated,
-                      float* __restrict__ vectors, uint8_t* __restrict__ valid, float* __restrict__ vector_sum) {
+                      float* __restrict__ vectors, uint8_t* __restrict__ valid, float* __restrict__ vector_sum,
+                      const PeerList peers) {
     __shared__ float part[8];
     __shared__ int cnt[2];
     const int64_t nc = blockIdx.x;  // n*C + c
@@ -347,6 +357,9 @@ proto_finalize_kernel(const float* __restrict__ sums, const TileRecord* __restri
     for (int64_t k = threadIdx.x; k < K; k += 256) {
         const float v = ok ? __fdiv_rn(sums[nc * K + k], denom) : 0.f;
         vectors[nc * K + k] = v;
+#pragma unroll
+        for (int p = 0; p < kMaxPeers; ++p)   // the same vector into every peer GPU's gather buffer (NVLink stores)
+            if (p < peers.n) peers.dst[p][nc * K + k] = v;
         s += v;
     }
     s = warp_sum(s);
@@ -356,6 +369,9 @@ proto_finalize_kernel(const float* __restrict__ sums, const TileRecord* __restri
         float tot = 0.f;
         for (int w = 0; w < 8; ++w) tot += part[w];
         vector_sum[nc] = tot;
+#pragma unroll
+        for (int p = 0; p < kMaxPeers; ++p)
+            if (p < peers.n && peers.sum[p] != nullptr) peers.sum[p][nc] = tot;
         valid[nc] = ok ? 1 : 0;
         cnt_all[nc] = ca;
         cnt_gated[nc] = cg;
@@ -395,6 +411,18 @@ proto_update_kernel(float* __restrict__ protos, float* __restrict__ num, float* 
 #pragma unroll
     for (int r = 0; r < R; ++r) p[r] = (tid + r * 256 < K) ? protos[c * K + tid + r * 256] : 0.f;
 
+    // group g+1's vectors are loaded while group g is applied (the walk over the images is a latency chain)
+    const float* src = fused ? fin.sums : vectors;
+    float vnext[S][R];
+    auto load_group = [&](int64_t n0) {
+#pragma unroll
+        for (int i = 0; i < S; ++i) {
+            const int64_t nc = (n0 + i) * C + c;
+#pragma unroll
+            for (int r = 0; r < R; ++r) vnext[i][r] = (n0 + i < N && tid + r * 256 < K) ? src[nc * K + tid + r * 256] : 0.f;
+        }
+    };
+    load_group(0);
     for (int64_t n0 = 0; n0 < N; n0 += S) {
         const int len = static_cast<int>(min(static_cast<int64_t>(S), N - n0));
         if (fused) {
@@ -407,12 +435,10 @@ proto_update_kernel(float* __restrict__ protos, float* __restrict__ num, float* 
         }
         float v[S][R];
 #pragma unroll
-        for (int i = 0; i < S; ++i) {
-            const int64_t nc = (n0 + i) * C + c;
-            const float* src = fused ? fin.sums : vectors;
+        for (int i = 0; i < S; ++i)
 #pragma unroll
-            for (int r = 0; r < R; ++r) v[i][r] = (i < len && tid + r * 256 < K) ? src[nc * K + tid + r * 256] : 0.f;
-        }
+            for (int r = 0; r < R; ++r) v[i][r] = vnext[i][r];
+        if (n0 + S < N) load_group(n0 + S);
         if (fused) {
 #pragma unroll
             for (int i = 0; i < S; ++i) {
@@ -624,8 +650,31 @@ extern "C" int tss_proto_finalize(const float* sums, const void* records, int64_
     if (n_img == 0) return TSS_OK;
     proto_finalize_kernel<<<static_cast<unsigned>(n_img * num_classes), 256, 0, as_stream(stream)>>>(
         sums, static_cast<const TileRecord*>(records), (plane + kPT - 1) / kPT, num_classes, channels, min_pixels, count_all,
-        count_gated, vectors, valid, vector_sum);
+        count_gated, vectors, valid, vector_sum, PeerList{{nullptr}, {nullptr}, 0});
     TSS_LAUNCH_CHECK("tss_proto_finalize");
+    return TSS_OK;
+}
+
+extern "C" int tss_proto_finalize_scatter(const float* sums, const void* records, int64_t n_img, int num_classes,
+                                          int64_t channels, int64_t plane, int min_pixels, int32_t* count_all,
+                                          int32_t* count_gated, float* vectors, uint8_t* valid, float* vector_sum,
+                                          float* const* peer_vectors, float* const* peer_vector_sums, int n_peers,
+                                          void* stream) {
+    using namespace tss;
+    TSS_REQUIRE(sums && records && count_all && count_gated && vectors && valid && vector_sum, TSS_E_ARG, "tss_proto_finalize_scatter: null pointer");
+    TSS_REQUIRE(n_img >= 0 && channels > 0 && plane > 0 && num_classes >= 1 && num_classes <= TSS_MAX_CLASSES, TSS_E_ARG, "tss_proto_finalize_scatter: bad extents");
+    TSS_REQUIRE(n_peers >= 0 && n_peers <= kMaxPeers && (n_peers == 0 || peer_vectors), TSS_E_ARG, "tss_proto_finalize_scatter: n_peers %d outside [0, %d]", n_peers, kMaxPeers);
+    if (n_img == 0) return TSS_OK;
+    PeerList pl{{nullptr}, {nullptr}, n_peers};
+    for (int p = 0; p < n_peers; ++p) {
+        TSS_REQUIRE(peer_vectors[p] != nullptr, TSS_E_ARG, "tss_proto_finalize_scatter: null peer pointer %d", p);
+        pl.dst[p] = peer_vectors[p];
+        pl.sum[p] = peer_vector_sums ? peer_vector_sums[p] : nullptr;
+    }
+    proto_finalize_kernel<<<static_cast<unsigned>(n_img * num_classes), 256, 0, as_stream(stream)>>>(
+        sums, static_cast<const TileRecord*>(records), (plane + kPT - 1) / kPT, num_classes, channels, min_pixels, count_all,
+        count_gated, vectors, valid, vector_sum, pl);
+    TSS_LAUNCH_CHECK("tss_proto_finalize_scatter");
     return TSS_OK;
 }
 

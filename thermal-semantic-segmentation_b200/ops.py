@@ -228,10 +228,14 @@ def _check_bank(protos: torch.Tensor, num: torch.Tensor, c: int, k: int) -> None
 
 def class_means(feat: torch.Tensor, logits: torch.Tensor, num_classes: int, labels_val: Optional[torch.Tensor] = None,
                 overflow_channel: Optional[int] = None, conf_thresh: Optional[float] = None,
-                use_conf_gate: bool = False, min_pixels: int = 10, update=None) -> ClassMeans:
+                use_conf_gate: bool = False, min_pixels: int = 10, update=None, scatter=None) -> ClassMeans:
     """A5 (three launches: labels -> segmented sums -> means).  ``update=(protos, num, mode, start_mean,
     momentum[, cap])``: the sequential prototype update A6 runs inside the third launch
-    (tss_proto_finalize_update), as cal_prototype.py:72-75 / self_training.py:124-126 chain the two."""
+    (tss_proto_finalize_update), as cal_prototype.py:72-75 / self_training.py:124-126 chain the two.
+    ``scatter=(vectors_out, sums_out, peer_ptrs, peer_sum_ptrs)`` (image-sharded batches, sharding.PeerGather): the
+    mean vectors / their sums are written into ``vectors_out`` [N,C,K] / ``sums_out`` [N,C] (this rank's slot of the
+    local gather buffer) and through every device pointer of ``peer_ptrs`` / ``peer_sum_ptrs`` (the same slot in
+    the other GPUs' buffers) by the third launch itself."""
     f = _dev(feat, torch.float32, "feat")
     x = _dev(logits, torch.float32, "logits")
     n, k = f.shape[0], f.shape[1]
@@ -259,7 +263,24 @@ def class_means(feat: torch.Tensor, logits: torch.Tensor, num_classes: int, labe
     vec = torch.empty_like(sums)
     valid = torch.empty((n, num_classes), dtype=torch.uint8, device=dev)
     vsum = torch.empty((n, num_classes), dtype=torch.float32, device=dev)
-    if update is None:
+    if scatter is not None:
+        if update is not None:
+            raise ValueError("scatter and update are exclusive (the update follows the exchange)")
+        vec, vsum_out, peers, peer_sums = scatter
+        if not (vec.is_cuda and vec.dtype == torch.float32 and vec.is_contiguous() and tuple(vec.shape) == (n, num_classes, k)):
+            raise TssError("scatter: vectors_out must be a contiguous fp32 CUDA tensor [%d,%d,%d]" % (n, num_classes, k))
+        if vsum_out is not None:
+            if not (vsum_out.is_cuda and vsum_out.dtype == torch.float32 and vsum_out.is_contiguous() and vsum_out.numel() == n * num_classes):
+                raise TssError("scatter: sums_out must be a contiguous fp32 CUDA tensor [%d,%d]" % (n, num_classes))
+            vsum = vsum_out.view(n, num_classes)
+        if peer_sums is not None and len(peer_sums) != len(peers):
+            raise ValueError("scatter: peer_sum_ptrs must match peer_ptrs")
+        arr = (ctypes.c_void_p * max(len(peers), 1))(*[ctypes.c_void_p(int(a)) for a in peers])
+        arr_s = None if peer_sums is None else (ctypes.c_void_p * max(len(peers), 1))(*[ctypes.c_void_p(int(a)) for a in peer_sums])
+        check(L.tss_proto_finalize_scatter(_ptr(sums), _ptr(rec), n, num_classes, k, plane, int(min_pixels), _ptr(ca),
+                                           _ptr(cg), _ptr(vec), _ptr(valid), _ptr(vsum), arr, arr_s, len(peers), st),
+              "tss_proto_finalize_scatter")
+    elif update is None:
         check(L.tss_proto_finalize(_ptr(sums), _ptr(rec), n, num_classes, k, plane, int(min_pixels), _ptr(ca), _ptr(cg),
                                    _ptr(vec), _ptr(valid), _ptr(vsum), st), "tss_proto_finalize")
     else:

@@ -22,7 +22,7 @@ import torch
 import torch.distributed as dist
 
 __all__ = ["shard_range", "world", "all_reduce_confusion", "all_reduce_loss", "prototype_positions",
-           "apply_prototype_partial", "ShardedPrototypes"]
+           "apply_prototype_partial", "ShardedPrototypes", "PeerGather"]
 
 
 def world(group=None) -> Tuple[int, int]:
@@ -130,6 +130,17 @@ class ShardedPrototypes:
         gathered = ops.ClassMeans(self._gv, None, None, None, None, None, None)
         ops.prototype_update(self.protos, self.num, gathered, self.mode, self.start_mean, self.momentum, self.cap)
 
+    def update_from_peers(self, gather: "PeerGather", slot: int) -> None:
+        """The exchange already happened inside the finalize kernel (ops.class_means(scatter=gather.targets(slot))):
+        wait for every rank's stores, then the sequential update over the gathered list -- the same kernel and the
+        same bit-identical bank as update_gathered."""
+        from . import ops
+
+        gather.barrier()
+        vec, vsum = gather.gathered(slot)
+        gathered = ops.ClassMeans(vec, None, vsum, None, None, None, None)
+        ops.prototype_update(self.protos, self.num, gathered, self.mode, self.start_mean, self.momentum, self.cap)
+
     def update_overlapped(self, means, gathered: bool = True):
         """Same as update(), on a side stream: the exchange is two tiny kernels and two latency-bound
         collectives, and nothing on the compute stream reads the bank until the NEXT exchange, so it overlaps
@@ -154,3 +165,61 @@ class ShardedPrototypes:
         """Make the current stream wait for every overlapped exchange issued so far."""
         if self._comm is not None:
             torch.cuda.current_stream(self.protos.device).wait_stream(self._comm)
+
+
+class PeerGather:
+    """Gather buffer for the per-(image, class) mean vectors in peer-mapped (symmetric) memory: every rank's
+    finalize kernel stores its vectors straight into ALL ranks' buffers over NVLink (ops.class_means(scatter=...)),
+    one barrier follows, and each rank runs the sequential update kernel over its own complete copy
+    [ranks*N, C, K] -- rank order = the reference's global image order.  No NCCL kernel, no staging copy, and the
+    stores, the barrier and the update are ordinary stream work, so the whole step (exchange included) replays
+    as ONE CUDA graph.  Two slots alternate: a rank can only start writing slot s again after every rank has
+    passed the barrier of the step in between, i.e. has finished reading slot s.
+
+    Needs torch.distributed._symmetric_memory (CUDA peer mapping inside one node); ShardedPrototypes.update_gathered
+    is the NCCL form of the same exchange."""
+
+    SLOTS = 2
+
+    def __init__(self, n_img: int, num_classes: int, dim: int, device, group=None):
+        import torch.distributed._symmetric_memory as symm
+
+        self.group = group if group is not None else dist.group.WORLD
+        self.rank, self.ws = world(group)
+        if self.ws > 8:
+            raise ValueError("PeerGather: at most 8 ranks (one NVLink domain), got %d" % self.ws)
+        self.shape = (int(n_img), int(num_classes), int(dim))
+        self.vec_elems = self.ws * n_img * num_classes * dim       # per slot: [ranks,N,C,K] vectors, then [ranks,N,C] sums
+        self.slot_elems = self.vec_elems + self.ws * n_img * num_classes
+        self.buf = symm.empty(self.SLOTS * self.slot_elems, dtype=torch.float32, device=device)
+        self.hdl = symm.rendezvous(self.buf, self.group)
+        self.buf.zero_()
+        self._ptrs = [int(p) for p in self.hdl.buffer_ptrs]
+        self._step = 0
+        torch.cuda.synchronize(device)
+        self.hdl.barrier(channel=0)
+
+    def targets(self, slot: int):
+        """scatter= argument of ops.class_means: this rank's [N,C,K] / [N,C] slices of the local buffer and the
+        device addresses of the same slices on every peer."""
+        n, c, k = self.shape
+        base = slot * self.slot_elems
+        ov = base + self.rank * n * c * k
+        os_ = base + self.vec_elems + self.rank * n * c
+        local_v = self.buf[ov:ov + n * c * k].view(n, c, k)
+        local_s = self.buf[os_:os_ + n * c].view(n, c)
+        peers = [p + 4 * ov for r, p in enumerate(self._ptrs) if r != self.rank]
+        peer_sums = [p + 4 * os_ for r, p in enumerate(self._ptrs) if r != self.rank]
+        return local_v, local_s, peers, peer_sums
+
+    def gathered(self, slot: int):
+        """([ranks*N, C, K] mean vectors, [ranks*N, C] sums) of every rank, in rank = global image order."""
+        n, c, k = self.shape
+        base = slot * self.slot_elems
+        vec = self.buf[base:base + self.vec_elems].view(self.ws * n, c, k)
+        sm = self.buf[base + self.vec_elems:base + self.slot_elems].view(self.ws * n, c)
+        return vec, sm
+
+    def barrier(self) -> None:
+        """All ranks' stores of this step have landed (stream-ordered on every rank)."""
+        self.hdl.barrier(channel=0)
