@@ -246,13 +246,17 @@ def run_b200(args):
     def stage_pl(i):
         return ops.pseudo_label(sets[i % N_SETS][0], size=size, thr=c["thr"], keep=c["keep"], ignore_index=c["ignore"])
 
-    def stage_proto(i):
+    tail = torch.cuda.Stream(dev)   # the latency-bound end of the prototype stage runs beside the confusion kernel
+
+    def stage_proto(i, tail_stream=None):
         logits, feat, _ = sets[i % N_SETS]
         if ws == 1:
-            return ops.class_means(feat, logits, C, update=(bank.protos, bank.num, bank.mode, bank.start_mean, bank.momentum))
+            return ops.class_means(feat, logits, C, update=(bank.protos, bank.num, bank.mode, bank.start_mean, bank.momentum),
+                                   tail_stream=tail_stream)
         if gather is not None:                      # slots alternate with i: see sharding.PeerGather
-            means = ops.class_means(feat, logits, C, scatter=gather.targets(i % 2))
-            bank.update_from_peers(gather, i % 2)
+            means = ops.class_means(feat, logits, C, scatter=gather.targets(i % 2), tail_stream=tail_stream)
+            with torch.cuda.stream(tail_stream if tail_stream is not None else torch.cuda.current_stream(dev)):
+                bank.update_from_peers(gather, i % 2)
             return means
         return ops.class_means(feat, logits, C)     # the exchange (bank.update_gathered) follows outside the graph
 
@@ -260,9 +264,12 @@ def run_b200(args):
         ops.confusion_matrix(pl.label.reshape(-1), sets[i % N_SETS][2].reshape(-1), C, meter.hist, meter.bad)
 
     def local_step(i):
+        # pseudo-labels -> segmented sums -> { means + prototype update (+ exchange) on `tail` || confusion matrix }
         pl = stage_pl(i)
-        means = stage_proto(i)
+        means = stage_proto(i, None if args.no_overlap else tail)
         stage_hist(i, pl)
+        if not args.no_overlap:
+            torch.cuda.current_stream(dev).wait_stream(tail)
         return pl, means
 
     # One CUDA graph per resident input set: the step's launch sequence is fixed, so the host issues ONE
@@ -370,7 +377,8 @@ def run_b200(args):
         "config": {"workload": workload_name(), "frames_per_gpu_per_step": frames, "logits": [frames, C, c["h"], c["w"]],
                    "feat": [frames, c["K"], c["h"], c["w"]], "labels": [frames, c["H"], c["W"]],
                    "l2": "inputs rotate over %d resident sets (780 MB working set > 126 MB L2)" % N_SETS,
-                   "launch": "one CUDA-graph replay per step (b200seg.graphs.GraphedCall), %d kernels per replay" % launches_per_step,
+                   "launch": "one CUDA-graph replay per step (b200seg.graphs.GraphedCall), %d kernels per replay%s" % (
+                       launches_per_step, "" if args.no_overlap else "; the prototype finalize/update(/exchange) node runs beside the confusion node"),
                    "parallelism": "image-sharded x%d; collectives: prototype means [16,13,256] fp32 per rank and step (%s), "
                                   "confusion [13,13] int64 once" % (ws, exchange),
                    "miou": float(miou), "bank_max_spread_over_ranks": bank_spread},
@@ -443,6 +451,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-overlap", action="store_true", help="keep the whole step on one stream (A/B of the tail overlap)")
     ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
                     help="N > 1 prototype exchange: peer-memory stores from the finalize kernel (default) or NCCL all_gather")
     args = ap.parse_args()

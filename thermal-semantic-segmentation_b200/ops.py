@@ -228,14 +228,18 @@ def _check_bank(protos: torch.Tensor, num: torch.Tensor, c: int, k: int) -> None
 
 def class_means(feat: torch.Tensor, logits: torch.Tensor, num_classes: int, labels_val: Optional[torch.Tensor] = None,
                 overflow_channel: Optional[int] = None, conf_thresh: Optional[float] = None,
-                use_conf_gate: bool = False, min_pixels: int = 10, update=None, scatter=None) -> ClassMeans:
+                use_conf_gate: bool = False, min_pixels: int = 10, update=None, scatter=None,
+                tail_stream: Optional["torch.cuda.Stream"] = None) -> ClassMeans:
     """A5 (three launches: labels -> segmented sums -> means).  ``update=(protos, num, mode, start_mean,
     momentum[, cap])``: the sequential prototype update A6 runs inside the third launch
     (tss_proto_finalize_update), as cal_prototype.py:72-75 / self_training.py:124-126 chain the two.
     ``scatter=(vectors_out, sums_out, peer_ptrs, peer_sum_ptrs)`` (image-sharded batches, sharding.PeerGather): the
     mean vectors / their sums are written into ``vectors_out`` [N,C,K] / ``sums_out`` [N,C] (this rank's slot of the
     local gather buffer) and through every device pointer of ``peer_ptrs`` / ``peer_sum_ptrs`` (the same slot in
-    the other GPUs' buffers) by the third launch itself."""
+    the other GPUs' buffers) by the third launch itself.
+    ``tail_stream``: issue the third launch (13 latency-bound CTAs at cfg2) on that stream, ordered after the first
+    two, so that independent work queued next on the current stream (the confusion matrix of the same step) runs
+    beside it; the caller joins (``current_stream().wait_stream(tail_stream)``) before reading the means or the bank."""
     f = _dev(feat, torch.float32, "feat")
     x = _dev(logits, torch.float32, "logits")
     n, k = f.shape[0], f.shape[1]
@@ -263,6 +267,11 @@ def class_means(feat: torch.Tensor, logits: torch.Tensor, num_classes: int, labe
     vec = torch.empty_like(sums)
     valid = torch.empty((n, num_classes), dtype=torch.uint8, device=dev)
     vsum = torch.empty((n, num_classes), dtype=torch.float32, device=dev)
+    if tail_stream is not None:
+        tail_stream.wait_stream(torch.cuda.current_stream(dev))
+        for t in (rec, sums, ca, cg, vec, valid, vsum):
+            t.record_stream(tail_stream)
+        st = tail_stream.cuda_stream
     if scatter is not None:
         if update is not None:
             raise ValueError("scatter and update are exclusive (the update follows the exchange)")
