@@ -87,6 +87,31 @@ def test_confusion_sizes_and_variants(ops, n, variant):
     assert int(h.sum().item()) == int((gt < c).sum())
 
 
+@pytest.mark.parametrize("c", [2, 13, 15])
+@pytest.mark.parametrize("n", [512 * 148 * 8, 5_000_003])
+def test_confusion_large_runs_and_bad_values(ops, c, n):
+    """large n: out-of-range values in both arrays, a tail that is not a multiple of 512, long runs of one key
+    (far more than 255 increments of one packed 8-bit counter between flushes); both kernels agree"""
+    r = gi.rs(800 + c)
+    gt = r.randint(0, c + 3, size=n).astype(np.uint8)
+    gt[r.uniform(size=n) < 0.02] = 255
+    gt[1000:300000] = min(1, c - 1)                       # one key for ~300k consecutive pixels
+    pred = np.where(r.uniform(size=n) < 0.7, np.minimum(gt, c - 1), r.randint(0, c, size=n)).astype(np.uint8)
+    pred[r.uniform(size=n) < 0.001] = 250                  # out-of-range predictions -> bad counter
+    h, bad = ops.confusion_matrix(G(pred), G(gt), c)
+    ok = gt < c
+    okp = ok & (pred < c)
+    ref = np.bincount(gt[okp].astype(np.int64) * c + pred[okp], minlength=c * c).reshape(c, c)
+    assert np.array_equal(h.cpu().numpy(), ref)
+    assert int(bad.item()) == int((ok & (pred >= c)).sum())
+    old = ops.lib().tss_tune_confusion_variant(0)
+    try:
+        h1, bad1 = ops.confusion_matrix(G(pred), G(gt), c)
+    finally:
+        ops.lib().tss_tune_confusion_variant(old)
+    assert torch.equal(h, h1) and torch.equal(bad, bad1)
+
+
 def test_confusion_bad_pred_reported(ops):
     gt = np.array([0, 1, 2, 3] * 5000, np.uint8)
     pred = gt.copy()

@@ -182,6 +182,7 @@ STAGES = {
     "dist_rectify_k256": lambda r: stage_dist(r, 16, 13, 256, 81, 241, "cfg2_k256", True),
     "loss_cfg2": lambda r: stage_loss(r, 4, 13, 640, 1920, "4x13x640x1920"),
     "hist_u8": lambda r: stage_hist(r, 2000, 256, 512, 19, torch.uint8, "cfg5_u8_2000maps"),
+    "hist_u8_c13": lambda r: stage_hist(r, 64, 640, 1920, 13, torch.uint8, "cfg2_u8_c13_64maps"),
     "hist_i64": lambda r: stage_hist(r, 500, 256, 512, 19, torch.int64, "cfg5_i64_500maps"),
 }
 
