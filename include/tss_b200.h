@@ -241,6 +241,12 @@ size_t tss_loss_workspace_bytes(void);
 int tss_ce_rce_fwd(const float* logits, const void* target, int target_dtype, int64_t n_img,
                    int num_classes, int64_t plane, int ignore_index, int with_rce, double* out,
                    void* workspace, void* stream);
+/* The same, and losses (DEVICE, 3 floats) = {alpha ce + beta rce, ce, rce} formed in the reduction kernel with the
+ * reference's arithmetic (fp64 division, fp32 rounding, fp32 mix; ce_sum != 0: reduction='sum' for ce), so the op
+ * is two launches with no scalar follow-up (self_training.py:114-118). */
+int tss_ce_rce_fwd_mix(const float* logits, const void* target, int target_dtype, int64_t n_img,
+                       int num_classes, int64_t plane, int ignore_index, int with_rce, double alpha,
+                       double beta, int ce_sum, double* out, float* losses, void* workspace, void* stream);
 /* grad[N,C,P] = ce_scale * d(sum ce)/dx + rce_scale * d(sum rce)/dx, scales read from the DEVICE
  * array scales[2] (so that no host sync is needed between forward and backward). */
 int tss_ce_rce_bwd(const float* logits, const void* target, int target_dtype, int64_t n_img,

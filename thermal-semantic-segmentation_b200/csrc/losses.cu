@@ -23,6 +23,11 @@ struct PixelSoftmax {
             p[c] = ldg_stream_f(x);
             if (EXACT || c + 1 < C) x += plane;
         }
+        finish(Crt, y);
+    }
+    // p[] holds the raw logits (registers): max, the label's logit, exponentials and their sum
+    __device__ __forceinline__ void finish(int Crt, int y = -1) {
+        const int C = EXACT ? CT : Crt;
         m = -INFINITY;
         xy = 0.f;
 #pragma unroll
@@ -77,7 +82,16 @@ __device__ __forceinline__ void block_reduce4(double (&v)[4], double* out4) {
     }
 }
 
-__global__ void __launch_bounds__(256) reduce_partials_kernel(const double* __restrict__ part, int blocks, double* __restrict__ out) {
+// losses (or NULL): {alpha ce + beta rce, ce, rce} in fp32 with the host mirror's own arithmetic -- sums divided in
+// fp64, rounded to fp32, mixed in fp32 -- so that the op needs no scalar follow-up kernels
+struct LossMix {
+    float* losses;
+    float alpha, beta;
+    int with_rce, ce_sum;
+};
+
+__global__ void __launch_bounds__(256) reduce_partials_kernel(const double* __restrict__ part, int blocks, double* __restrict__ out,
+                                                              const LossMix mix = LossMix{nullptr, 0.f, 0.f, 0, 0}) {
     __shared__ double sh[4][8];
     double v[4] = {0, 0, 0, 0};
     for (int b = threadIdx.x; b < blocks; b += 256)
@@ -89,43 +103,92 @@ __global__ void __launch_bounds__(256) reduce_partials_kernel(const double* __re
 #pragma unroll
         for (int i = 0; i < 4; ++i) sh[i][threadIdx.x >> 5] = v[i];
     __syncthreads();
+    __shared__ double tot[4];
     if (threadIdx.x < 4) {
         double t = 0.0;
         for (int w = 0; w < 8; ++w) t += sh[threadIdx.x][w];
         out[threadIdx.x] = t;
+        tot[threadIdx.x] = t;
+    }
+    __syncthreads();
+    if (mix.losses != nullptr && threadIdx.x == 0) {
+        const double valid = tot[2];
+        const float ce = static_cast<float>(mix.ce_sum ? tot[0] : tot[0] / valid);   // mean: nan when nothing is valid, as torch
+        const float rce = static_cast<float>(tot[1] / (valid + 1e-6));
+        float t = __fmul_rn(mix.alpha, ce);
+        if (mix.with_rce) t = __fadd_rn(t, __fmul_rn(mix.beta, rce));
+        mix.losses[0] = t;
+        mix.losses[1] = ce;
+        mix.losses[2] = rce;
     }
 }
 
 // -log(clamp(0, 1e-4, 1)) in fp32, as torch.log(torch.clamp(one_hot, min=1e-4)) yields off the label
 __device__ __forceinline__ float rce_log_floor() { return -logf(1e-4f); }
 
-template <int CT, bool EXACT, typename T>
+// one pixel's CE / RCE terms from a finished PixelSoftmax (acc: 0 CE sum, 1 RCE sum, 2 valid, 3 bad labels)
+template <int CT, bool EXACT>
+__device__ __forceinline__ void ce_rce_pixel(const PixelSoftmax<CT, EXACT>& sm, long long y, int C, int ignore, int with_rce,
+                                             float A, double (&acc)[4]) {
+    if (y == ignore) return;
+    if (y < 0 || y >= C) { acc[3] += 1.0; return; }
+    const int Cc = EXACT ? CT : C;
+    // -log_softmax[y] = log(s) - (x_y - m)
+    acc[0] += static_cast<double>(sm.log_s() - (sm.xy - sm.m));
+    acc[2] += 1.0;
+    if (with_rce) {
+        const float inv = sm.inv_s();
+        float r = 0.f;
+#pragma unroll
+        for (int c = 0; c < CT; ++c)
+            if (c < Cc && c != static_cast<int>(y)) r += fminf(fmaxf(sm.p[c] * inv, 1e-7f), 1.0f);
+        acc[1] += static_cast<double>(A * r);
+    }
+}
+
+// VEC: four consecutive pixels per thread and iteration (plane % 4 == 0, 16-byte aligned logits): C 128-bit loads
+// in flight per thread instead of C 32-bit ones -- the scalar form cannot keep enough bytes in flight for HBM.
+// Label and logits are loaded together (the logit loads do not wait for the ignore test; ignored pixels cost the
+// same bytes either way, their sectors hold valid neighbours).
+template <int CT, bool EXACT, typename T, bool VEC>
 __global__ void __launch_bounds__(kLossThreads)
 ce_rce_fwd_kernel(const float* __restrict__ logits, const void* __restrict__ target, int64_t N, int C, int64_t P,
                   int ignore, int with_rce, double* __restrict__ part) {
     double acc[4] = {0, 0, 0, 0};
-    const int64_t total = N * P;
-    const int Cc = EXACT ? CT : C;   // per-class guards fold at compile time when EXACT
     const float A = rce_log_floor();
     const int64_t first = blockIdx.x * static_cast<int64_t>(kLossThreads) + threadIdx.x;
     const int64_t stride = static_cast<int64_t>(gridDim.x) * kLossThreads;
-    PixelWalk w(first, stride, P);
-    for (int64_t i = first; i < total; i += stride, w.next()) {
-        const long long y = target_at<T>(target, i);
-        if (y == ignore) continue;
-        if (y < 0 || y >= C) { acc[3] += 1.0; continue; }
-        PixelSoftmax<CT, EXACT> sm;
-        sm.load(logits + w.n * C * P + w.p, C, P, static_cast<int>(y));
-        // -log_softmax[y] = log(s) - (x_y - m)
-        acc[0] += static_cast<double>(sm.log_s() - (sm.xy - sm.m));
-        acc[2] += 1.0;
-        if (with_rce) {
-            const float inv = sm.inv_s();
-            float r = 0.f;
+    if (VEC) {
+        const int64_t Pq = P >> 2, total = N * Pq;
+        PixelWalk w(first, stride, Pq);
+        for (int64_t q = first; q < total; q += stride, w.next()) {
+            const float* x = logits + w.n * C * P + 4 * w.p;
+            float4 v[CT];
 #pragma unroll
-            for (int c = 0; c < CT; ++c)
-                if (c < Cc && c != static_cast<int>(y)) r += fminf(fmaxf(sm.p[c] * inv, 1e-7f), 1.0f);
-            acc[1] += static_cast<double>(A * r);
+            for (int c = 0; c < CT; ++c) {
+                v[c] = ldg_stream_f4(x);
+                if (EXACT || c + 1 < C) x += P;
+            }
+            long long y[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) y[j] = target_at<T>(target, 4 * q + j);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                PixelSoftmax<CT, EXACT> sm;
+#pragma unroll
+                for (int c = 0; c < CT; ++c) sm.p[c] = j == 0 ? v[c].x : j == 1 ? v[c].y : j == 2 ? v[c].z : v[c].w;
+                sm.finish(C, static_cast<int>(y[j]));
+                ce_rce_pixel<CT, EXACT>(sm, y[j], C, ignore, with_rce, A, acc);
+            }
+        }
+    } else {
+        const int64_t total = N * P;
+        PixelWalk w(first, stride, P);
+        for (int64_t i = first; i < total; i += stride, w.next()) {
+            const long long y = target_at<T>(target, i);
+            PixelSoftmax<CT, EXACT> sm;
+            sm.load(logits + w.n * C * P + w.p, C, P, static_cast<int>(y));
+            ce_rce_pixel<CT, EXACT>(sm, y, C, ignore, with_rce, A, acc);
         }
     }
     block_reduce4(acc, part + blockIdx.x * 4);
@@ -145,14 +208,14 @@ ce_rce_bwd_kernel(const float* __restrict__ logits, const void* __restrict__ tar
     for (int64_t i = first; i < total; i += stride, w.next()) {
         const long long y = target_at<T>(target, i);
         float* g = grad + w.n * C * P + w.p;
+        PixelSoftmax<CT, EXACT> sm;
+        sm.load(logits + w.n * C * P + w.p, C, P);   // together with the label (see the forward kernel)
         if (y == ignore || y < 0 || y >= C) {
 #pragma unroll
             for (int c = 0; c < CT; ++c)
                 if (c < Cc) g[c * P] = 0.f;
             continue;
         }
-        PixelSoftmax<CT, EXACT> sm;
-        sm.load(logits + w.n * C * P + w.p, C, P);
         const float inv = sm.inv_s();
         float S = 0.f;  // sum over j != y of [1e-7 <= p_j <= 1] p_j  (clamp passes gradient inside its range)
 #pragma unroll
@@ -193,9 +256,9 @@ focal_fwd_kernel(const float* __restrict__ logits, const void* __restrict__ targ
     PixelWalk w(first, stride, P);
     for (int64_t i = first; i < total; i += stride, w.next()) {
         const long long y = target_at<T>(target, i);
-        if (y < 0 || y >= C) { acc[3] += 1.0; continue; }
         PixelSoftmax<CT, EXACT> sm;
         sm.load(logits + w.n * C * P + w.p, C, P, static_cast<int>(y));
+        if (y < 0 || y >= C) { acc[3] += 1.0; continue; }
         float logpt = (sm.xy - sm.m) - sm.log_s();
         const float pt = __expf(logpt);
         if (alpha) logpt *= alpha[y];
@@ -218,14 +281,14 @@ focal_bwd_kernel(const float* __restrict__ logits, const void* __restrict__ targ
     for (int64_t i = first; i < total; i += stride, w.next()) {
         const long long y = target_at<T>(target, i);
         float* g = grad + w.n * C * P + w.p;
+        PixelSoftmax<CT, EXACT> sm;
+        sm.load(logits + w.n * C * P + w.p, C, P, static_cast<int>(y));
         if (y < 0 || y >= C) {
 #pragma unroll
             for (int c = 0; c < CT; ++c)
                 if (c < Cc) g[c * P] = 0.f;
             continue;
         }
-        PixelSoftmax<CT, EXACT> sm;
-        sm.load(logits + w.n * C * P + w.p, C, P, static_cast<int>(y));
         const float pt = __expf((sm.xy - sm.m) - sm.log_s());
         // pt is detached in the reference (logpt.data.exp()): d loss / d x_c = -w * alpha_y * (delta_cy - p_c)
         const float coef = -sc * focal_weight(pt, gamma) * (alpha ? alpha[y] : 1.0f);
@@ -258,6 +321,22 @@ static int loss_grid(int64_t total) {
         else TSS_DISPATCH_T(KERNEL, TSS_MAX_CLASSES, false, DT, GRID, ST, __VA_ARGS__);                       \
     } while (0)
 
+// the same with a trailing bool template argument (VEC)
+#define TSS_DISPATCH_TV(KERNEL, CT, EX, V, DT, GRID, ST, ...)                                              \
+    do {                                                                                                      \
+        if ((DT) == TSS_U8) KERNEL<CT, EX, uint8_t, V><<<GRID, kLossThreads, 0, ST>>>(__VA_ARGS__);           \
+        else if ((DT) == TSS_I32) KERNEL<CT, EX, int32_t, V><<<GRID, kLossThreads, 0, ST>>>(__VA_ARGS__);     \
+        else KERNEL<CT, EX, int64_t, V><<<GRID, kLossThreads, 0, ST>>>(__VA_ARGS__);                          \
+    } while (0)
+#define TSS_DISPATCH_CT_TV(KERNEL, V, C, DT, GRID, ST, ...)                                                   \
+    do {                                                                                                      \
+        if ((C) == 13) TSS_DISPATCH_TV(KERNEL, 13, true, V, DT, GRID, ST, __VA_ARGS__);                       \
+        else if ((C) == 19) TSS_DISPATCH_TV(KERNEL, 19, true, V, DT, GRID, ST, __VA_ARGS__);                  \
+        else if ((C) < 13) TSS_DISPATCH_TV(KERNEL, 13, false, V, DT, GRID, ST, __VA_ARGS__);                  \
+        else if ((C) < 19) TSS_DISPATCH_TV(KERNEL, 19, false, V, DT, GRID, ST, __VA_ARGS__);                  \
+        else TSS_DISPATCH_TV(KERNEL, TSS_MAX_CLASSES, false, V, DT, GRID, ST, __VA_ARGS__);                   \
+    } while (0)
+
 static int check_loss_args(const char* who, const void* logits, const void* target, int dt, int64_t N, int C, int64_t P) {
     TSS_REQUIRE(logits && target, TSS_E_ARG, "%s: null pointer", who);
     TSS_REQUIRE(N >= 0 && P > 0, TSS_E_ARG, "%s: bad extents", who);
@@ -270,18 +349,40 @@ static int check_loss_args(const char* who, const void* logits, const void* targ
 
 extern "C" size_t tss_loss_workspace_bytes(void) { return static_cast<size_t>(tss::kLossMaxBlocks) * 4 * sizeof(double); }
 
+static int ce_rce_fwd_impl(const float* logits, const void* target, int target_dtype, int64_t n_img, int num_classes,
+                           int64_t plane, int ignore_index, int with_rce, double* out, void* workspace, void* stream,
+                           const tss::LossMix mix);
+
 extern "C" int tss_ce_rce_fwd(const float* logits, const void* target, int target_dtype, int64_t n_img, int num_classes,
                               int64_t plane, int ignore_index, int with_rce, double* out, void* workspace, void* stream) {
+    return ce_rce_fwd_impl(logits, target, target_dtype, n_img, num_classes, plane, ignore_index, with_rce, out, workspace,
+                           stream, tss::LossMix{nullptr, 0.f, 0.f, 0, 0});
+}
+
+extern "C" int tss_ce_rce_fwd_mix(const float* logits, const void* target, int target_dtype, int64_t n_img, int num_classes,
+                                  int64_t plane, int ignore_index, int with_rce, double alpha, double beta, int ce_sum,
+                                  double* out, float* losses, void* workspace, void* stream) {
+    TSS_REQUIRE(losses != nullptr, TSS_E_ARG, "tss_ce_rce_fwd_mix: null losses");
+    return ce_rce_fwd_impl(logits, target, target_dtype, n_img, num_classes, plane, ignore_index, with_rce, out, workspace,
+                           stream, tss::LossMix{losses, static_cast<float>(alpha), static_cast<float>(beta), with_rce, ce_sum});
+}
+
+static int ce_rce_fwd_impl(const float* logits, const void* target, int target_dtype, int64_t n_img, int num_classes,
+                           int64_t plane, int ignore_index, int with_rce, double* out, void* workspace, void* stream,
+                           const tss::LossMix mix) {
     using namespace tss;
     if (int r = check_loss_args("tss_ce_rce_fwd", logits, target, target_dtype, n_img, num_classes, plane)) return r;
     TSS_REQUIRE(out && workspace, TSS_E_ARG, "tss_ce_rce_fwd: null out/workspace");
     cudaStream_t st = as_stream(stream);
-    const int grid = loss_grid(n_img * plane);
+    const bool vec = plane % 4 == 0 && (reinterpret_cast<uintptr_t>(logits) & 15) == 0;
+    const int grid = loss_grid(vec ? n_img * plane / 4 : n_img * plane);
     double* part = static_cast<double*>(workspace);
-    TSS_DISPATCH_CT_T(ce_rce_fwd_kernel, num_classes, target_dtype, grid, st, logits, target, n_img, num_classes, plane,
-                      ignore_index, with_rce, part);
+    if (vec) TSS_DISPATCH_CT_TV(ce_rce_fwd_kernel, true, num_classes, target_dtype, grid, st, logits, target, n_img, num_classes, plane,
+                                ignore_index, with_rce, part);
+    else TSS_DISPATCH_CT_TV(ce_rce_fwd_kernel, false, num_classes, target_dtype, grid, st, logits, target, n_img, num_classes, plane,
+                            ignore_index, with_rce, part);
     TSS_LAUNCH_CHECK("tss_ce_rce_fwd");
-    reduce_partials_kernel<<<1, 256, 0, st>>>(part, grid, out);
+    reduce_partials_kernel<<<1, 256, 0, st>>>(part, grid, out, mix);
     TSS_LAUNCH_CHECK("tss_ce_rce_fwd(reduce)");
     return TSS_OK;
 }

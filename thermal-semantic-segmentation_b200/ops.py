@@ -459,15 +459,15 @@ class _CeRce(torch.autograd.Function):
         if t.numel() != n * plane:
             raise ValueError("target must have N*H*W elements")
         out = torch.empty(4, dtype=torch.float64, device=x.device)
-        check(lib().tss_ce_rce_fwd(_ptr(x), _ptr(t), _DT[t.dtype], n, c, plane, int(ignore_index), 1 if with_rce else 0,
-                                   _ptr(out), _ptr(_loss_workspace(x.device)), _stream()), "tss_ce_rce_fwd")
+        losses = torch.empty(3, dtype=torch.float32, device=x.device)
+        # ce = sum / valid (nan when nothing is valid, as torch), rce = sum / (valid + 1e-6), total = alpha ce + beta rce:
+        # formed inside the reduction launch (tss_ce_rce_fwd_mix) instead of eight scalar torch kernels
+        check(lib().tss_ce_rce_fwd_mix(_ptr(x), _ptr(t), _DT[t.dtype], n, c, plane, int(ignore_index), 1 if with_rce else 0,
+                                       float(alpha), float(beta), 1 if ce_sum else 0, _ptr(out), _ptr(losses),
+                                       _ptr(_loss_workspace(x.device)), _stream()), "tss_ce_rce_fwd_mix")
         ctx.save_for_backward(x, t, out)
         ctx.meta = (int(ignore_index), float(alpha), float(beta), bool(with_rce), bool(ce_sum))
-        valid = out[2]
-        ce = (out[0] if ce_sum else out[0] / valid).to(torch.float32)   # mean: nan when nothing is valid, as torch
-        rce = (out[1] / (valid + 1e-6)).to(torch.float32)
-        total = alpha * ce + (beta * rce if with_rce else 0.0)
-        return total, ce, rce, out[3]
+        return losses[0], losses[1], losses[2], out[3]
 
     @staticmethod
     def backward(ctx, g_total, g_ce, g_rce, _g_bad):

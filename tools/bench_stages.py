@@ -141,7 +141,25 @@ def stage_loss(reps, N, C, H, W, tag):
     def fwd(x, y):
         return ops.ce_rce(x, y, 255, 0.1, 1.0)
     med, mn = timed(fwd, sets, reps)
-    report("ce_rce_fwd_" + tag, [N, C, H, W], med, mn, nb + 8 * N * H * W, N * H * W, 2, "int64 targets as the reference")
+    report("ce_rce_fwd_" + tag, [N, C, H, W], med, mn, nb + 8 * N * H * W, N * H * W, 2, "ops.ce_rce: int64 targets as the reference; includes ~8 scalar torch kernels (mean, alpha/beta mix)")
+
+    out4 = torch.empty(4, dtype=torch.float64, device=dev)
+    wsp = torch.empty(int(ops.lib().tss_loss_workspace_bytes()), dtype=torch.uint8, device=dev)
+
+    def fwd_abi(x, y):   # the two forward launches alone (sums in fp64), without the scalar torch arithmetic of ops.ce_rce
+        ops.check(ops.lib().tss_ce_rce_fwd(x.data_ptr(), y.data_ptr(), 2, N, C, H * W, 255, 1, out4.data_ptr(), wsp.data_ptr(),
+                                          torch.cuda.current_stream().cuda_stream), "tss_ce_rce_fwd")
+    med, mn = timed(fwd_abi, sets, reps)
+    report("ce_rce_fwd_abi_" + tag, [N, C, H, W], med, mn, nb + 8 * N * H * W, N * H * W, 2, "tss_ce_rce_fwd alone (kernel + partial reduction)")
+    scales = torch.tensor([1.0 / (N * H * W), 0.1 / (N * H * W)], device=dev)
+
+    def bwd(x, y):   # the backward kernel alone, through the C ABI (graph-timed like every other stage)
+        grad = torch.empty_like(x)
+        ops.check(ops.lib().tss_ce_rce_bwd(x.data_ptr(), y.data_ptr(), 2, N, C, H * W, 255, scales.data_ptr(), grad.data_ptr(),
+                                          torch.cuda.current_stream().cuda_stream), "tss_ce_rce_bwd")
+        return grad
+    med, mn = timed(bwd, sets, reps)
+    report("ce_rce_bwd_" + tag, [N, C, H, W], med, mn, 2 * nb + 8 * N * H * W, N * H * W, 1, "logits read once, gradient written once")
 
     def fwdbwd(x, y):
         xr = x.requires_grad_(True)
@@ -150,7 +168,7 @@ def stage_loss(reps, N, C, H, W, tag):
         xr.grad = None
     med, mn = timed_eager(fwdbwd, sets, reps)
     report("ce_rce_fwd_bwd_" + tag, [N, C, H, W], med, mn, 3 * nb + 16 * N * H * W, N * H * W, 4,
-           "forward + backward (logits read twice, grad written once) incl. autograd overhead")
+           "forward + backward through torch.autograd, eager launches: host-bound, not a kernel number")
 
 
 def stage_hist(reps, n_maps, H, W, C, dtype, tag):
