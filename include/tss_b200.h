@@ -253,6 +253,14 @@ int tss_ce_rce_bwd(const float* logits, const void* target, int target_dtype, in
                    int num_classes, int64_t plane, int ignore_index, const float* scales, float* grad,
                    void* stream);
 
+/* The same with the scales formed in the kernel from the upstream gradients upstream3 = {d/d total, d/d ce, d/d rce}
+ * (DEVICE, 3 floats) and the forward's `out` sums: ce_scale = (g_total alpha + g_ce) / valid, rce_scale =
+ * (g_total beta + g_rce) / (valid + 1e-6) -- the autograd backward is one launch. */
+int tss_ce_rce_bwd_mix(const float* logits, const void* target, int target_dtype, int64_t n_img,
+                       int num_classes, int64_t plane, int ignore_index, int with_rce, double alpha,
+                       double beta, int ce_sum, const float* upstream3, const double* fwd_out, float* grad,
+                       void* stream);
+
 /* A13  focal loss -- FocalLoss.forward (utils/loss.py:164-184): loss_px = -(1-pt)^gamma * alpha[y] *
  * log pt with pt detached; no ignore handling.  out (DEVICE, 2 doubles) = {sum loss, pixel count}.
  * alpha: DEVICE [C] fp32 or NULL.  bwd: grad = scale[0] * d(sum loss)/dx. */

@@ -47,6 +47,7 @@ _SIGNATURES = {
     "tss_one_hot_overflow": (c_int, [c_vp, c_i64, c_i64, c_int, c_int, c_vp, c_vp]),
     "tss_loss_workspace_bytes": (c_sz, []),
     "tss_ce_rce_fwd": (c_int, [c_vp, c_vp, c_int, c_i64, c_int, c_i64, c_int, c_int, c_vp, c_vp, c_vp]),
+    "tss_ce_rce_bwd_mix": (c_int, [c_vp, c_vp, c_int, c_i64, c_int, c_i64, c_int, c_int, c_f64, c_f64, c_int, c_vp, c_vp, c_vp, c_vp]),
     "tss_ce_rce_fwd_mix": (c_int, [c_vp, c_vp, c_int, c_i64, c_int, c_i64, c_int, c_int, c_f64, c_f64, c_int, c_vp, c_vp, c_vp, c_vp]),
     "tss_ce_rce_bwd": (c_int, [c_vp, c_vp, c_int, c_i64, c_int, c_i64, c_int, c_vp, c_vp, c_vp]),
     "tss_focal_fwd": (c_int, [c_vp, c_vp, c_int, c_i64, c_int, c_i64, c_f32, c_vp, c_vp, c_vp, c_vp]),

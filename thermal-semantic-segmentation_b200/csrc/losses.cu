@@ -194,11 +194,31 @@ ce_rce_fwd_kernel(const float* __restrict__ logits, const void* __restrict__ tar
     block_reduce4(acc, part + blockIdx.x * 4);
 }
 
+// upstream gradients {g_total, g_ce, g_rce} (DEVICE) + the forward's sums: the backward kernel forms its own scales
+struct GradMix {
+    const float* grads;
+    const double* fwd_out;
+    float alpha, beta;
+    int with_rce, ce_sum;
+};
+
 template <int CT, bool EXACT, typename T>
 __global__ void __launch_bounds__(kLossThreads)
 ce_rce_bwd_kernel(const float* __restrict__ logits, const void* __restrict__ target, int64_t N, int C, int64_t P,
-                  int ignore, const float* __restrict__ scales, float* __restrict__ grad) {
-    const float ce_scale = scales[0], rce_scale = scales[1];
+                  int ignore, const float* __restrict__ scales, float* __restrict__ grad, const GradMix gm) {
+    float ce_scale, rce_scale;
+    if (gm.grads != nullptr) {
+        // scales from the upstream gradients of (total, ce, rce) and the forward sums, with the host mirror's arithmetic:
+        // gce = g_total alpha + g_ce, grce = g_total beta + g_rce (fp32); ce_scale = gce / valid (fp64), rce likewise
+        const float gt = gm.grads[0], gce = __fadd_rn(__fmul_rn(gt, gm.alpha), gm.grads[1]);
+        const float grce = __fadd_rn(gm.with_rce ? __fmul_rn(gt, gm.beta) : 0.f, gm.grads[2]);
+        const double valid = gm.fwd_out[2];
+        ce_scale = static_cast<float>(gm.ce_sum ? static_cast<double>(gce) : static_cast<double>(gce) / valid);
+        rce_scale = static_cast<float>(static_cast<double>(grce) / (valid + 1e-6));
+    } else {
+        ce_scale = scales[0];
+        rce_scale = scales[1];
+    }
     const float A = rce_log_floor();
     const int64_t total = N * P;
     const int Cc = EXACT ? CT : C;   // per-class guards fold at compile time when EXACT
@@ -387,18 +407,33 @@ static int ce_rce_fwd_impl(const float* logits, const void* target, int target_d
     return TSS_OK;
 }
 
-extern "C" int tss_ce_rce_bwd(const float* logits, const void* target, int target_dtype, int64_t n_img, int num_classes,
-                              int64_t plane, int ignore_index, const float* scales, float* grad, void* stream) {
+static int ce_rce_bwd_impl(const float* logits, const void* target, int target_dtype, int64_t n_img, int num_classes,
+                           int64_t plane, int ignore_index, const float* scales, float* grad, void* stream,
+                           const tss::GradMix gm) {
     using namespace tss;
     if (int r = check_loss_args("tss_ce_rce_bwd", logits, target, target_dtype, n_img, num_classes, plane)) return r;
-    TSS_REQUIRE(scales && grad, TSS_E_ARG, "tss_ce_rce_bwd: null scales/grad");
+    TSS_REQUIRE((scales || gm.grads) && grad, TSS_E_ARG, "tss_ce_rce_bwd: null scales/grad");
     if (n_img == 0) return TSS_OK;
     cudaStream_t st = as_stream(stream);
     const int grid = loss_grid(n_img * plane);
     TSS_DISPATCH_CT_T(ce_rce_bwd_kernel, num_classes, target_dtype, grid, st, logits, target, n_img, num_classes, plane,
-                      ignore_index, scales, grad);
+                      ignore_index, scales, grad, gm);
     TSS_LAUNCH_CHECK("tss_ce_rce_bwd");
     return TSS_OK;
+}
+
+extern "C" int tss_ce_rce_bwd_mix(const float* logits, const void* target, int target_dtype, int64_t n_img, int num_classes,
+                                  int64_t plane, int ignore_index, int with_rce, double alpha, double beta, int ce_sum,
+                                  const float* upstream3, const double* fwd_out, float* grad, void* stream) {
+    TSS_REQUIRE(upstream3 && fwd_out, TSS_E_ARG, "tss_ce_rce_bwd_mix: null upstream gradients / forward sums");
+    return ce_rce_bwd_impl(logits, target, target_dtype, n_img, num_classes, plane, ignore_index, nullptr, grad, stream,
+                           tss::GradMix{upstream3, fwd_out, static_cast<float>(alpha), static_cast<float>(beta), with_rce, ce_sum});
+}
+
+extern "C" int tss_ce_rce_bwd(const float* logits, const void* target, int target_dtype, int64_t n_img, int num_classes,
+                              int64_t plane, int ignore_index, const float* scales, float* grad, void* stream) {
+    return ce_rce_bwd_impl(logits, target, target_dtype, n_img, num_classes, plane, ignore_index, scales, grad, stream,
+                           tss::GradMix{nullptr, nullptr, 0.f, 0.f, 0, 0});
 }
 
 extern "C" int tss_focal_fwd(const float* logits, const void* target, int target_dtype, int64_t n_img, int num_classes,

@@ -475,14 +475,12 @@ class _CeRce(torch.autograd.Function):
         ignore_index, alpha, beta, with_rce, ce_sum = ctx.meta
         n, c = x.shape[0], x.shape[1]
         plane = x[0, 0].numel()
-        valid = out[2]
-        gce = g_total * alpha + g_ce
-        grce = (g_total * beta if with_rce else torch.zeros_like(g_total)) + g_rce
-        scales = torch.stack([gce.double() if ce_sum else (gce.double() / valid),
-                              (grce.double() / (valid + 1e-6))]).to(torch.float32).contiguous()
+        # ce_scale = (g_total alpha + g_ce) / valid, rce_scale = (g_total beta + g_rce) / (valid + 1e-6): formed in the kernel
+        up = torch.stack([g_total, g_ce, g_rce]).to(torch.float32)
         grad = torch.empty_like(x)
-        check(lib().tss_ce_rce_bwd(_ptr(x), _ptr(t), _DT[t.dtype], n, c, plane, ignore_index, _ptr(scales), _ptr(grad),
-                                   _stream()), "tss_ce_rce_bwd")
+        check(lib().tss_ce_rce_bwd_mix(_ptr(x), _ptr(t), _DT[t.dtype], n, c, plane, ignore_index, 1 if with_rce else 0,
+                                       float(alpha), float(beta), 1 if ce_sum else 0, _ptr(up), _ptr(out), _ptr(grad),
+                                       _stream()), "tss_ce_rce_bwd_mix")
         return grad, None, None, None, None, None, None
 
 
