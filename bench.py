@@ -297,6 +297,14 @@ def run_b200(args):
             dist.barrier()
             torch.cuda.synchronize()
 
+    if ws > 1:
+        # setup, not warm-up steps: the first multi-GPU replays also pay for peer mappings, NCCL channel set-up and
+        # rank skew (one first run at N=8 measured 0.87 ms/step against 0.24-0.26 on every later one); settle them
+        for i in range(24):
+            step(i)
+        scratch = meter.hist.clone()
+        sharding.all_reduce_confusion(scratch, meter.bad.clone())
+        fence()
     for i in range(max(args.warmup, 3)):
         step(i)
     fence()
