@@ -248,18 +248,25 @@ template <int CT, int PX>
 __global__ void __launch_bounds__(TlpCfg<CT, PX>::kThreads, 1) distance_tlp_kernel(const DistArgs a, int64_t units, int SI) {
     constexpr int W = TlpCfg<CT, PX>::kWarps;
     constexpr int PP = PX / 2;
-    extern __shared__ __align__(16) float ps[];  // [CT][K], rows >= C zero
+    // [CT][K + 4 SI], rows >= C zero.  The K/SI channels of part s start 16 bytes (4 s floats) later than their
+    // natural place: the SI addresses of one float4 read (same class, same step, channel offsets s K/SI -- multiples
+    // of 128 bytes) would otherwise fall into the same four banks and cost SI wavefronts instead of one.
+    extern __shared__ __align__(16) float ps[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int K = static_cast<int>(a.K);
-    for (int i = tid; i < CT * K; i += TlpCfg<CT, PX>::kThreads) ps[i] = (i < a.C * K) ? a.protos[i] : 0.f;
+    const int KW = K / SI;
+    const int PS = K + 4 * SI;
+    for (int i = tid; i < CT * K; i += TlpCfg<CT, PX>::kThreads) {
+        const int c = i / K, k = i - c * K;
+        ps[c * PS + k + 4 * (k / KW)] = (c < a.C) ? a.protos[i] : 0.f;
+    }
     __syncthreads();
 
     const int L = 32 / SI;
     const int part = lane / L, j = lane - part * L;
     const int unit_px = PX * L;
     const int64_t units_per_img = (a.P + unit_px - 1) / unit_px;
-    const int KW = K / SI;
-    const float* pk = ps + part * KW;
+    const float* pk = ps + part * (KW + 4);
     const int64_t P = a.P;
 
     for (int64_t u = static_cast<int64_t>(blockIdx.x) * W + warp; u < units; u += static_cast<int64_t>(gridDim.x) * W) {
@@ -292,7 +299,7 @@ __global__ void __launch_bounds__(TlpCfg<CT, PX>::kThreads, 1) distance_tlp_kern
                 for (int h = 0; h < PP; ++h) xp[q][h] = pack2(x[q][2 * h], x[q][2 * h + 1]);
 #pragma unroll
             for (int c = 0; c < CT; ++c) {
-                const float4 pr = *reinterpret_cast<const float4*>(pk + c * K + kk);
+                const float4 pr = *reinterpret_cast<const float4*>(pk + c * PS + kk);
                 const float pv[4] = {pr.x, pr.y, pr.z, pr.w};
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
@@ -329,9 +336,9 @@ __global__ void __launch_bounds__(TlpCfg<CT, PX>::kThreads, 1) distance_tlp_kern
 }
 
 // Relative cost of one (PX, SI) form on this problem: rounds of the persistent loop on the busiest warp x channel
-// steps per round x pixels a round retires per SM x the measured per-pixel-channel cost of the form (4 px per
-// lane holds fewer warps: x1.12; 8-lane parts fetch 32-byte pieces of a row: x1.2 / x1.1).  B200 measurements
-// behind the factors: profiles/r01_distance_forms.txt.
+// steps per round (+ a per-unit constant) x pixels a round retires per SM x the measured per-pixel-channel cost of
+// the form (4 px per lane holds fewer warps: x1.05; 8-lane parts fetch 32-byte pieces of a row: x1.05).  B200
+// measurements behind the factors: profiles/r01_distance_forms.txt.
 template <int CT, int PX>
 static double tlp_cost(const DistArgs& a, int SI) {
     constexpr int W = TlpCfg<CT, PX>::kWarps;
@@ -339,15 +346,15 @@ static double tlp_cost(const DistArgs& a, int SI) {
     const int64_t units = a.N * ((a.P + unit_px - 1) / unit_px);
     const int64_t slots = static_cast<int64_t>(kNumSMs) * W;
     const double rounds = static_cast<double>((units + slots - 1) / slots);
-    double f = (PX == 4) ? 1.12 : 1.0;
-    if (SI == 4) f *= (PX == 4) ? 1.1 : 1.2;
+    double f = (PX == 4) ? 1.05 : 1.0;
+    if (SI == 4) f *= 1.05;
     return rounds * (static_cast<double>(a.K) / SI + 16.0) * (W * PX * 32) * f;
 }
 
 template <int CT, int PX>
 static int launch_distance_tlp(DistArgs& a, int SI, cudaStream_t st) {
     constexpr int W = TlpCfg<CT, PX>::kWarps;
-    const size_t smem = sizeof(float) * CT * static_cast<size_t>(a.K);
+    const size_t smem = sizeof(float) * CT * static_cast<size_t>(a.K + 4 * SI);
     const int unit_px = PX * 32 / SI;
     const int64_t units = a.N * ((a.P + unit_px - 1) / unit_px);
     cudaError_t e = cudaFuncSetAttribute(distance_tlp_kernel<CT, PX>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
@@ -368,7 +375,7 @@ int g_dist_split_value();
 template <int CT>
 static int launch_distance_auto(DistArgs& a, cudaStream_t st) {
     if (g_dist_variant == 1) return -1;
-    if (sizeof(float) * CT * static_cast<size_t>(a.K) > 226 * 1024) return -1;   // prototypes must be resident
+    if (sizeof(float) * CT * static_cast<size_t>(a.K + 16) > 226 * 1024) return -1;   // prototypes must be resident
     const int forced = g_dist_split_value();
     int best_px = 2, best_si = 1;
     double best = 1e300;

@@ -1,5 +1,5 @@
 """Run one stage of the bench step a few times (for ncu / quick timing).  usage: prof_stage.py STAGE [reps]
-STAGE in pl | proto | hist | dist | ce | all."""
+STAGE in pl | proto | hist | all (the bench step) | dist | ce | distce."""
 import os
 import sys
 
@@ -43,5 +43,24 @@ for i in range(reps):
         timed("proto", f)
     if stage in ("hist", "all"):
         timed("hist", lambda: ops.confusion_matrix(pl0.label.reshape(-1), gt.reshape(-1), c["C"], hist, bad))
+if stage in ("dist", "distce"):
+    for (N, C, K, h, w) in ((2, 19, 2048, 129, 257), (16, 13, 256, 81, 241)):
+        f2 = torch.randn(N, K, h, w, device=dev)
+        soft = torch.softmax(3.0 * torch.randn(N, C, h, w, device=dev), 1)
+        hard = torch.full((N, 1, h, w), 255, dtype=torch.uint8, device=dev)
+        pr = torch.randn(C, K, device=dev)
+        for i in range(reps):
+            timed("dist_rectify_C%d_K%d" % (C, K), lambda: ops.prototype_distance(
+                f2, pr, 0.5, want_dist=False, want_weight=True, soft=soft, hard=hard, train_thred=0.0, ignore_index=255))
+        del f2, soft, hard
+if stage in ("ce", "distce"):
+    x = torch.randn(4, 13, 640, 1920, device=dev)
+    y = torch.randint(0, 13, (4, 640, 1920), device=dev, dtype=torch.int64)
+    for i in range(reps):
+        def g():
+            xr = x.requires_grad_(True)
+            ops.ce_rce(xr, y, 255, 0.1, 1.0)[0].backward()
+            xr.grad = None
+        timed("ce_rce_fwd_bwd", g)
 for k, v in times.items():
     print(k, "us:", " ".join("%.1f" % t for t in v))
