@@ -421,14 +421,17 @@ def test_distance_kernel_forms_agree(ops, variant, split):
     n, k, c, h, w = 2, 128, 19, 23, 37
     feat, protos = gi.randn(1400, n, k, h, w), gi.randn(1401, c, k)
     d_ref = O.prototype_distance(T(feat), T(protos)).numpy()
-    old_v, old_s = lib().tss_tune_distance_variant(variant), lib().tss_tune_distance_split(split)
-    try:
-        d, _, _ = ops.prototype_distance(G(feat), G(protos), temperature=0.5, want_dist=True)
-        got = d.cpu().numpy()
-    finally:
-        lib().tss_tune_distance_variant(old_v)
-        lib().tss_tune_distance_split(old_s)
-    np.testing.assert_allclose(got, d_ref, rtol=RTOL)
+    for prefetch in (0, 1):
+        old_v, old_s = lib().tss_tune_distance_variant(variant), lib().tss_tune_distance_split(split)
+        old_p = lib().tss_tune_distance_prefetch(prefetch)
+        try:
+            d, _, _ = ops.prototype_distance(G(feat), G(protos), temperature=0.5, want_dist=True)
+            got = d.cpu().numpy()
+        finally:
+            lib().tss_tune_distance_variant(old_v)
+            lib().tss_tune_distance_split(old_s)
+            lib().tss_tune_distance_prefetch(old_p)
+        np.testing.assert_allclose(got, d_ref, rtol=RTOL)
 
 
 # ------------------------------------------------------------------------------------------- A11-A13

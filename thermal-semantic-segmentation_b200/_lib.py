@@ -22,6 +22,7 @@ _SIGNATURES = {
     "tss_tune_confusion_variant": (c_int, [c_int]),
     "tss_tune_pl_force_tile": (c_int, [c_int]),
     "tss_tune_distance_variant": (c_int, [c_int]),
+    "tss_tune_distance_prefetch": (c_int, [c_int]),
     "tss_tune_distance_split": (c_int, [c_int]),
     "tss_confusion": (c_int, [c_vp, c_vp, c_int, c_i64, c_int, c_vp, c_vp, c_vp]),
     "tss_softmax_nchw": (c_int, [c_vp, c_vp, c_i64, c_int, c_i64, c_vp]),

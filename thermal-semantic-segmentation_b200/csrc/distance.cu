@@ -237,16 +237,19 @@ __global__ void __launch_bounds__(kDThreads, 1) distance_kernel(const DistArgs a
 // partial sums meet in log2(SI) xor-shuffles -- no shared-memory exchange, no barrier, and units small enough
 // (down to 16 pixels) that the last round of the persistent loop is nearly full.  A quarter warp (8 lanes) always
 // lies inside one part, so the float4 prototype read stays a broadcast.
-template <int CT, int PX>
+// PF: the next 4-channel group is loaded into a second register set while the current one is used.  It costs
+// 4 PX registers (fewer warps per SM) and buys 7-15 % per pixel-channel; which of the two wins depends on how well
+// the resulting number of warp slots divides the problem (tlp_cost).
+template <int CT, int PX, bool PF>
 struct TlpCfg {
-    static constexpr int kAcc = CT * PX;
+    static constexpr int kAcc = CT * PX + (PF ? 4 * PX : 0);
     static constexpr int kWarps = kAcc <= 26 ? 32 : kAcc <= 40 ? 24 : kAcc <= 56 ? 20 : kAcc <= 80 ? 16 : 12;
     static constexpr int kThreads = kWarps * 32;
 };
 
-template <int CT, int PX>
-__global__ void __launch_bounds__(TlpCfg<CT, PX>::kThreads, 1) distance_tlp_kernel(const DistArgs a, int64_t units, int SI) {
-    constexpr int W = TlpCfg<CT, PX>::kWarps;
+template <int CT, int PX, bool PF>
+__global__ void __launch_bounds__(TlpCfg<CT, PX, PF>::kThreads, 1) distance_tlp_kernel(const DistArgs a, int64_t units, int SI) {
+    constexpr int W = TlpCfg<CT, PX, PF>::kWarps;
     constexpr int PP = PX / 2;
     // [CT][K + 4 SI], rows >= C zero.  The K/SI channels of part s start 16 bytes (4 s floats) later than their
     // natural place: the SI addresses of one float4 read (same class, same step, channel offsets s K/SI -- multiples
@@ -256,7 +259,7 @@ __global__ void __launch_bounds__(TlpCfg<CT, PX>::kThreads, 1) distance_tlp_kern
     const int K = static_cast<int>(a.K);
     const int KW = K / SI;
     const int PS = K + 4 * SI;
-    for (int i = tid; i < CT * K; i += TlpCfg<CT, PX>::kThreads) {
+    for (int i = tid; i < CT * K; i += TlpCfg<CT, PX, PF>::kThreads) {
         const int c = i / K, k = i - c * K;
         ps[c * PS + k + 4 * (k / KW)] = (c < a.C) ? a.protos[i] : 0.f;
     }
@@ -283,14 +286,37 @@ __global__ void __launch_bounds__(TlpCfg<CT, PX>::kThreads, 1) distance_tlp_kern
 #pragma unroll
             for (int h = 0; h < PP; ++h) acc[c][h] = 0ull;
 
-#pragma unroll(PX == 2 ? 2 : 1)
-        for (int kk = 0; kk < KW; kk += 4) {
-            float x[4][PX];
+        float xn[PF ? 4 : 1][PF ? PX : 1];
+        if (PF) {
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
 #pragma unroll
-                for (int i = 0; i < PX; ++i) x[q][i] = ldg_stream_f(row + off[i]);
+                for (int i = 0; i < PX; ++i) xn[PF ? q : 0][PF ? i : 0] = ldg_stream_f(row + off[i]);
                 row += P;
+            }
+        }
+#pragma unroll(PF ? 1 : (PX == 2 ? 2 : 1))
+        for (int kk = 0; kk < KW; kk += 4) {
+            float x[4][PX];
+            if (PF) {
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+#pragma unroll
+                    for (int i = 0; i < PX; ++i) x[q][i] = xn[PF ? q : 0][PF ? i : 0];
+                if (kk + 4 >= KW) row -= 4 * P;   // last group: re-read it (in range) instead of branching around the loads
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+#pragma unroll
+                    for (int i = 0; i < PX; ++i) xn[PF ? q : 0][PF ? i : 0] = ldg_stream_f(row + off[i]);
+                    row += P;
+                }
+            } else {
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+#pragma unroll
+                    for (int i = 0; i < PX; ++i) x[q][i] = ldg_stream_f(row + off[i]);
+                    row += P;
+                }
             }
             f32x2 xp[4][PP];
 #pragma unroll
@@ -339,29 +365,29 @@ __global__ void __launch_bounds__(TlpCfg<CT, PX>::kThreads, 1) distance_tlp_kern
 // steps per round (+ a per-unit constant) x pixels a round retires per SM x the measured per-pixel-channel cost of
 // the form (4 px per lane holds fewer warps: x1.05; 8-lane parts fetch 32-byte pieces of a row: x1.05).  B200
 // measurements behind the factors: profiles/r01_distance_forms.txt.
-template <int CT, int PX>
+template <int CT, int PX, bool PF>
 static double tlp_cost(const DistArgs& a, int SI) {
-    constexpr int W = TlpCfg<CT, PX>::kWarps;
+    constexpr int W = TlpCfg<CT, PX, PF>::kWarps;
     const int unit_px = PX * 32 / SI;
     const int64_t units = a.N * ((a.P + unit_px - 1) / unit_px);
     const int64_t slots = static_cast<int64_t>(kNumSMs) * W;
     const double rounds = static_cast<double>((units + slots - 1) / slots);
-    double f = (PX == 4) ? 1.05 : 1.0;
+    double f = PF ? (PX == 4 ? 0.87 : 0.93) : 1.0;
     if (SI == 4) f *= 1.05;
     return rounds * (static_cast<double>(a.K) / SI + 16.0) * (W * PX * 32) * f;
 }
 
-template <int CT, int PX>
+template <int CT, int PX, bool PF>
 static int launch_distance_tlp(DistArgs& a, int SI, cudaStream_t st) {
-    constexpr int W = TlpCfg<CT, PX>::kWarps;
+    constexpr int W = TlpCfg<CT, PX, PF>::kWarps;
     const size_t smem = sizeof(float) * CT * static_cast<size_t>(a.K + 4 * SI);
     const int unit_px = PX * 32 / SI;
     const int64_t units = a.N * ((a.P + unit_px - 1) / unit_px);
-    cudaError_t e = cudaFuncSetAttribute(distance_tlp_kernel<CT, PX>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+    cudaError_t e = cudaFuncSetAttribute(distance_tlp_kernel<CT, PX, PF>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
     if (e != cudaSuccess) return cuda_status(e, "tss_proto_distance: smem attribute");
     const int64_t ctas = (units + W - 1) / W;
     const unsigned grid = static_cast<unsigned>(ctas < kNumSMs ? ctas : kNumSMs);
-    distance_tlp_kernel<CT, PX><<<grid, TlpCfg<CT, PX>::kThreads, smem, st>>>(a, units, SI);
+    distance_tlp_kernel<CT, PX, PF><<<grid, TlpCfg<CT, PX, PF>::kThreads, smem, st>>>(a, units, SI);
     TSS_LAUNCH_CHECK("tss_proto_distance(tlp)");
     return TSS_OK;
 }
@@ -369,6 +395,7 @@ static int launch_distance_tlp(DistArgs& a, int SI, cudaStream_t st) {
 // tuning hooks: form 0 = automatic, 1 = 8-warp register-pipeline kernel, 2 / 4 = thread-level-parallel kernel with
 // 2 / 4 pixels per lane; split 0 = automatic, else the K split
 static int g_dist_variant = 0;
+static int g_dist_prefetch = -1;   // -1 = automatic, 0 / 1 = without / with the register prefetch
 int g_dist_split_value();
 
 // returns TSS_OK after a launch, or -1 when the thread-level-parallel form does not apply
@@ -377,18 +404,23 @@ static int launch_distance_auto(DistArgs& a, cudaStream_t st) {
     if (g_dist_variant == 1) return -1;
     if (sizeof(float) * CT * static_cast<size_t>(a.K + 16) > 226 * 1024) return -1;   // prototypes must be resident
     const int forced = g_dist_split_value();
-    int best_px = 2, best_si = 1;
+    int best_px = 2, best_si = 1, best_pf = 0;
     double best = 1e300;
     for (int px = 2; px <= 4; px += 2) {
         if (g_dist_variant != 0 && g_dist_variant != px) continue;
-        for (int si = 1; si <= 4; si *= 2) {
-            if (forced != 0 && forced != si) continue;
-            const double c = (px == 2) ? tlp_cost<CT, 2>(a, si) : tlp_cost<CT, 4>(a, si);
-            if (c < best) { best = c; best_px = px; best_si = si; }
+        for (int pf = 0; pf <= 1; ++pf) {
+            if (g_dist_prefetch >= 0 && g_dist_prefetch != pf) continue;
+            for (int si = 1; si <= 4; si *= 2) {
+                if (forced != 0 && forced != si) continue;
+                const double c = px == 2 ? (pf ? tlp_cost<CT, 2, true>(a, si) : tlp_cost<CT, 2, false>(a, si))
+                                         : (pf ? tlp_cost<CT, 4, true>(a, si) : tlp_cost<CT, 4, false>(a, si));
+                if (c < best) { best = c; best_px = px; best_si = si; best_pf = pf; }
+            }
         }
     }
     if (best == 1e300) return -1;   // forced split 8: only the register-pipeline kernel has it
-    return best_px == 2 ? launch_distance_tlp<CT, 2>(a, best_si, st) : launch_distance_tlp<CT, 4>(a, best_si, st);
+    if (best_px == 2) return best_pf ? launch_distance_tlp<CT, 2, true>(a, best_si, st) : launch_distance_tlp<CT, 2, false>(a, best_si, st);
+    return best_pf ? launch_distance_tlp<CT, 4, true>(a, best_si, st) : launch_distance_tlp<CT, 4, false>(a, best_si, st);
 }
 
 static int g_dist_split = 0;  // tuning hook: 0 = automatic
@@ -433,6 +465,12 @@ static int launch_distance(DistArgs& a, cudaStream_t st) {
 extern "C" int tss_tune_distance_variant(int v) {
     int old = tss::g_dist_variant;
     if (v == 0 || v == 1 || v == 2 || v == 4) tss::g_dist_variant = v;
+    return old;
+}
+
+extern "C" int tss_tune_distance_prefetch(int v) {
+    int old = tss::g_dist_prefetch;
+    if (v >= -1 && v <= 1) tss::g_dist_prefetch = v;
     return old;
 }
 
