@@ -139,9 +139,11 @@ __device__ __forceinline__ void ce_rce_pixel(const PixelSoftmax<CT, EXACT>& sm, 
     if (with_rce) {
         const float inv = sm.inv_s();
         float r = 0.f;
+        int yi = static_cast<int>(y);
+        asm("" : "+r"(yi));   // keep the C class tests 32-bit (the compiler otherwise folds them back into 64-bit compares of y)
 #pragma unroll
         for (int c = 0; c < CT; ++c)
-            if (c < Cc && c != static_cast<int>(y)) r += fminf(fmaxf(sm.p[c] * inv, 1e-7f), 1.0f);
+            if (c < Cc && c != yi) r += fminf(fmaxf(sm.p[c] * inv, 1e-7f), 1.0f);
         acc[1] += static_cast<double>(A * r);
     }
 }
@@ -238,18 +240,20 @@ ce_rce_bwd_kernel(const float* __restrict__ logits, const void* __restrict__ tar
         }
         const float inv = sm.inv_s();
         float S = 0.f;  // sum over j != y of [1e-7 <= p_j <= 1] p_j  (clamp passes gradient inside its range)
+        int yi = static_cast<int>(y);
+        asm("" : "+r"(yi));   // 32-bit class tests (see the forward kernel)
 #pragma unroll
         for (int c = 0; c < CT; ++c)
             if (c < Cc) {
                 sm.p[c] = sm.p[c] * inv;
-                if (c != static_cast<int>(y) && sm.p[c] >= 1e-7f && sm.p[c] <= 1.0f) S += sm.p[c];
+                if (c != yi && sm.p[c] >= 1e-7f && sm.p[c] <= 1.0f) S += sm.p[c];
             }
         const float rs = rce_scale * A;
 #pragma unroll
         for (int c = 0; c < CT; ++c)
             if (c < Cc) {
                 const float pc = sm.p[c];
-                const bool is_y = c == static_cast<int>(y);
+                const bool is_y = c == yi;
                 const float gate = (!is_y && pc >= 1e-7f && pc <= 1.0f) ? 1.f : 0.f;
                 g[c * P] = ce_scale * (pc - (is_y ? 1.f : 0.f)) + rs * pc * (gate - S);
             }
