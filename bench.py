@@ -265,10 +265,11 @@ def run_b200(args):
 
     def local_step(i):
         # pseudo-labels -> segmented sums -> { means + prototype update (+ exchange) on `tail` || confusion matrix }
+        use_tail = not args.no_overlap and (ws == 1 or gather is not None)   # the NCCL form exchanges after the replay
         pl = stage_pl(i)
-        means = stage_proto(i, None if args.no_overlap else tail)
+        means = stage_proto(i, tail if use_tail else None)
         stage_hist(i, pl)
-        if not args.no_overlap:
+        if use_tail:
             torch.cuda.current_stream(dev).wait_stream(tail)
         return pl, means
 
@@ -386,7 +387,7 @@ def run_b200(args):
                    "feat": [frames, c["K"], c["h"], c["w"]], "labels": [frames, c["H"], c["W"]],
                    "l2": "inputs rotate over %d resident sets (780 MB working set > 126 MB L2)" % N_SETS,
                    "launch": "one CUDA-graph replay per step (b200seg.graphs.GraphedCall), %d kernels per replay%s" % (
-                       launches_per_step, "" if args.no_overlap else "; the prototype finalize/update(/exchange) node runs beside the confusion node"),
+                       launches_per_step, "" if (args.no_overlap or (ws > 1 and gather is None)) else "; the prototype finalize/update(/exchange) node runs beside the confusion node"),
                    "parallelism": "image-sharded x%d; collectives: prototype means [16,13,256] fp32 per rank and step (%s), "
                                   "confusion [13,13] int64 once" % (ws, exchange),
                    "miou": float(miou), "bank_max_spread_over_ranks": bank_spread},
