@@ -214,6 +214,7 @@ def run_b200(args):
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if ws > 1:
+        os.environ.setdefault("NCCL_DEBUG", "NONE")   # stdout carries ONE JSON line (the box default prints a version banner)
         dist.init_process_group("nccl", device_id=dev)
     c = CFG
     frames, C, size = c["frames"], c["C"], (c["H"], c["W"])
