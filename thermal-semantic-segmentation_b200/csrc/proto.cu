@@ -242,10 +242,14 @@ proto_accum_kernel(const float* __restrict__ feat, const TileRecord* __restrict_
         // ===== producer warp: lane l stages channel row l of every tile job
         int stage = 0;
         uint32_t phase = 0;
-        for (int64_t j = j0; j < j1; ++j) {
-            const int64_t t = j % T;
-            const int64_t u = j / T;          // unit = (image, channel group)
-            const int64_t kg = u % KG, n = u / KG;
+        // (tile, channel group, image) walked incrementally: a 64-bit division per tile and warp is ~100 instructions
+        int64_t t = j0 % T, u0 = j0 / T;
+        int64_t kg = u0 % KG, n = u0 / KG;
+        for (int64_t j = j0; j < j1; ++j, ++t) {
+            if (t == T) {
+                t = 0;
+                if (++kg == KG) { kg = 0; ++n; }
+            }
             const int64_t p0 = t * kPT;
             const int len = static_cast<int>(min(static_cast<int64_t>(kPT), P - p0));
             mbar_wait(&empty[stage], phase ^ 1u);
@@ -284,8 +288,8 @@ proto_accum_kernel(const float* __restrict__ feat, const TileRecord* __restrict_
         // with fire-and-forget reductions (RED.ADD.F32 resolves in L2, the SM does not wait).  A CTA-level
         // pre-reduction through shared-memory atomics costs more than it saves here: 16 warps x C ATOMS at
         // ~64 cycles each serialise on the one shared-atomic unit (~7 us per flush).
-        auto flush = [&](int64_t u) {
-            const int64_t kg = u % KG, n = u / KG;
+        int64_t cur_n = 0, cur_kg = 0;
+        auto flush = [&](int64_t n, int64_t kg) {
             float* out = sums + (n * C) * K + kg * kKT + lane;
 #pragma unroll
             for (int c = 0; c < CT; ++c)
@@ -294,14 +298,20 @@ proto_accum_kernel(const float* __restrict__ feat, const TileRecord* __restrict_
                     racc[c] = 0.f;
                 }
         };
-        for (int64_t j = j0; j < j1; ++j) {
-            const int64_t t = j % T;
-            const int64_t u = j / T;
-            if (u != cur_unit) {
-                if (cur_unit >= 0) flush(cur_unit);
-                cur_unit = u;
+        int64_t t = j0 % T, u = j0 / T;
+        int64_t kg = u % KG, n = u / KG;
+        for (int64_t j = j0; j < j1; ++j, ++t) {
+            if (t == T) {
+                t = 0;
+                ++u;
+                if (++kg == KG) { kg = 0; ++n; }
             }
-            const int64_t kg = u % KG, n = u / KG;
+            if (u != cur_unit) {
+                if (cur_unit >= 0) flush(cur_n, cur_kg);
+                cur_unit = u;
+                cur_n = n;
+                cur_kg = kg;
+            }
             const int64_t e0 = (n * K + kg * kKT + lane) * P + t * kPT;
             const float* row = rows + (stage * kKT + lane) * kRowStride + row_skew_words(lane) + static_cast<int>(e0 & 3);
             const TileRecord* rec = reinterpret_cast<const TileRecord*>(recs + stage * kRecBytes);
@@ -352,7 +362,7 @@ proto_accum_kernel(const float* __restrict__ feat, const TileRecord* __restrict_
             if (lane == 0) mbar_arrive(&empty[stage]);
             if (++stage == kStages) { stage = 0; phase ^= 1u; }
         }
-        if (cur_unit >= 0) flush(cur_unit);
+        if (cur_unit >= 0) flush(cur_n, cur_kg);
     }
 }
 
