@@ -158,4 +158,17 @@ __device__ __forceinline__ long long load_label<int64_t>(const void* p, int64_t 
     return static_cast<const int64_t*>(p)[i];
 }
 
+// (image, pixel) walk of a 1-D grid-stride loop without a 64-bit division per element
+struct PixelWalk {
+    int64_t n, p, P, sn, sp;
+    __device__ __forceinline__ PixelWalk(int64_t first, int64_t stride, int64_t plane) : P(plane) {
+        n = first / plane; p = first - n * plane;
+        sn = stride / plane; sp = stride - sn * plane;
+    }
+    __device__ __forceinline__ void next() {
+        n += sn; p += sp;
+        if (p >= P) { p -= P; ++n; }
+    }
+};
+
 }  // namespace tss

@@ -50,19 +50,6 @@ struct PixelSoftmax {
     __device__ __forceinline__ float inv_s() const { return __frcp_rn(s); }
 };
 
-// (image, pixel) walk of a 1-D grid-stride loop without a 64-bit division per element
-struct PixelWalk {
-    int64_t n, p, P, sn, sp;
-    __device__ __forceinline__ PixelWalk(int64_t first, int64_t stride, int64_t plane) : P(plane) {
-        n = first / plane; p = first - n * plane;
-        sn = stride / plane; sp = stride - sn * plane;
-    }
-    __device__ __forceinline__ void next() {
-        n += sn; p += sp;
-        if (p >= P) { p -= P; ++n; }
-    }
-};
-
 template <typename T>
 __device__ __forceinline__ long long target_at(const void* t, int64_t i) { return load_label<T>(t, i); }
 

@@ -418,10 +418,12 @@ __global__ void __launch_bounds__(256) pl_direct_kernel(const PLArgs a, int64_t 
     const int64_t plane = static_cast<int64_t>(a.H) * a.W;
     const int64_t quads_per_img = (plane + 3) / 4;
     const int64_t total = n_img * quads_per_img;
-    for (int64_t q = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; q < total;
-         q += static_cast<int64_t>(gridDim.x) * blockDim.x) {
-        const int64_t n = q / quads_per_img;
-        const int64_t p = (q - n * quads_per_img) * 4;
+    const int64_t q0 = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
+    const int64_t qs = static_cast<int64_t>(gridDim.x) * blockDim.x;
+    PixelWalk w(q0, qs, quads_per_img);   // (image, quad) without a 64-bit division per iteration
+    for (int64_t q = q0; q < total; q += qs, w.next()) {
+        const int64_t n = w.n;
+        const int64_t p = w.p * 4;
         const int valid = static_cast<int>(min(static_cast<int64_t>(4), plane - p));
         const float* base = a.src + n * C * plane + p;
         float v[4][CT];
@@ -451,9 +453,11 @@ template <int CT>
 __global__ void __launch_bounds__(256) softmax_nchw_kernel(const float* __restrict__ x, float* __restrict__ y,
                                                            int64_t n_img, int C, int64_t plane) {
     const int64_t total = n_img * plane;
-    for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
-         i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
-        const int64_t n = i / plane, p = i - n * plane;
+    const int64_t i0 = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
+    const int64_t is = static_cast<int64_t>(gridDim.x) * blockDim.x;
+    PixelWalk w(i0, is, plane);
+    for (int64_t i = i0; i < total; i += is, w.next()) {
+        const int64_t n = w.n, p = w.p;
         const float* px = x + n * C * plane + p;
         float v[CT];
 #pragma unroll
