@@ -214,8 +214,19 @@ def run_b200(args):
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if ws > 1:
-        os.environ.setdefault("NCCL_DEBUG", "NONE")   # stdout carries ONE JSON line (the box default prints a version banner)
-        dist.init_process_group("nccl", device_id=dev)
+        # stdout carries ONE JSON line: NCCL prints a version banner to fd 1 when its communicator is created, so
+        # the init and the first collective run with fd 1 pointing at stderr
+        sys.stdout.flush()
+        saved = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", device_id=dev)
+            dist.barrier()
+            torch.cuda.synchronize()
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved, 1)
+            os.close(saved)
     c = CFG
     frames, C, size = c["frames"], c["C"], (c["H"], c["W"])
     sets = [make_inputs(dev, 1234 + 1000 * rank + s, frames) for s in range(N_SETS)]
