@@ -31,7 +31,7 @@ static_assert(kRowStride % 4 == 0, "rows must start 16-byte aligned");
 static_assert(kRecBytes % 16 == 0, "records are bulk-copied");
 
 struct TileRecord {
-    uint16_t idx[kPT];   // pixel offsets of the tile sorted by class (bucket C = pixels that join no sum)
+    uint16_t idx[kPT];   // BYTE offsets (4 x pixel index) of the tile's pixels sorted by class (bucket C = pixels that join no sum)
     uint16_t off[64];    // off[c] = first sorted position of class c; off[c+1]-off[c] = gated count in the tile
     uint16_t call[32];   // ungated one-hot count per class in the tile (the "< 10 pixels" rule)
 };
@@ -130,7 +130,7 @@ proto_label_kernel(const float* __restrict__ logits, const float* __restrict__ l
     __syncthreads();
     TileRecord* rec = records + n * tiles + tile;
 #pragma unroll
-    for (int r = 0; r < 2; ++r) rec->idx[wcnt[r * 8 + warp][bucket[r]] + rank[r]] = static_cast<uint16_t>(r * 256 + tid);
+    for (int r = 0; r < 2; ++r) rec->idx[wcnt[r * 8 + warp][bucket[r]] + rank[r]] = static_cast<uint16_t>((r * 256 + tid) * 4);
     if (tid < 64) rec->off[tid] = static_cast<uint16_t>(tid <= C + 1 ? boff[tid] : kPT);
     if (tid < 32) {
         const int g = tid < C ? boff[tid + 1] - boff[tid] : 0;  // gated count of this class in the tile
@@ -337,14 +337,14 @@ proto_accum_kernel(const float* __restrict__ feat, const TileRecord* __restrict_
                     for (int base = pos & ~7; base < b; base += 8) {
                         const uint4 iq = *reinterpret_cast<const uint4*>(&rec->idx[base]);
                         float v[8];
-                        v[0] = lds_f32(row_addr + ((iq.x & 0xffffu) << 2));
-                        v[1] = lds_f32(row_addr + ((iq.x >> 16) << 2));
-                        v[2] = lds_f32(row_addr + ((iq.y & 0xffffu) << 2));
-                        v[3] = lds_f32(row_addr + ((iq.y >> 16) << 2));
-                        v[4] = lds_f32(row_addr + ((iq.z & 0xffffu) << 2));
-                        v[5] = lds_f32(row_addr + ((iq.z >> 16) << 2));
-                        v[6] = lds_f32(row_addr + ((iq.w & 0xffffu) << 2));
-                        v[7] = lds_f32(row_addr + ((iq.w >> 16) << 2));
+                        v[0] = lds_f32(row_addr + (iq.x & 0xffffu));   // the record holds byte offsets
+                        v[1] = lds_f32(row_addr + (iq.x >> 16));
+                        v[2] = lds_f32(row_addr + (iq.y & 0xffffu));
+                        v[3] = lds_f32(row_addr + (iq.y >> 16));
+                        v[4] = lds_f32(row_addr + (iq.z & 0xffffu));
+                        v[5] = lds_f32(row_addr + (iq.z >> 16));
+                        v[6] = lds_f32(row_addr + (iq.w & 0xffffu));
+                        v[7] = lds_f32(row_addr + (iq.w >> 16));
                         const int first = pos - base, last = b - base;  // valid q: first <= q < last
                         if (first > 0 || last < 8) {
 #pragma unroll
