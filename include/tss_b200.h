@@ -52,7 +52,7 @@ uint64_t tss_launch_count(void);
 int tss_tune_confusion_variant(int v);   /* 0 shared-memory atomics, 1 packed private counters (uint8) */
 int tss_tune_pl_force_tile(int v);       /* 1 = use the tiled kernel even when H==h and W==w */
 int tss_tune_distance_variant(int v);    /* 0 = automatic, 1 = 8-warp register-pipeline kernel, 2 / 4 = thread-level-parallel kernel, 2 / 4 px per lane */
-int tss_tune_distance_prefetch(int v);   /* -1 = automatic, 0 / 1 = thread-level-parallel kernel without / with register prefetch */
+int tss_tune_distance_prefetch(int v);   /* -1 = automatic, 0 / 1 / 2 = register prefetch depth (4-channel groups) of the thread-level-parallel kernel */
 int tss_tune_distance_split(int v);      /* 0 = automatic, else the K split 1 | 2 | 4 | 8 of tss_proto_distance */
 
 /* ---------------------------------------------------------------------------------------------

@@ -421,7 +421,7 @@ def test_distance_kernel_forms_agree(ops, variant, split):
     n, k, c, h, w = 2, 128, 19, 23, 37
     feat, protos = gi.randn(1400, n, k, h, w), gi.randn(1401, c, k)
     d_ref = O.prototype_distance(T(feat), T(protos)).numpy()
-    for prefetch in (0, 1):
+    for prefetch in (0, 1, 2):
         old_v, old_s = lib().tss_tune_distance_variant(variant), lib().tss_tune_distance_split(split)
         old_p = lib().tss_tune_distance_prefetch(prefetch)
         try:

@@ -240,14 +240,14 @@ __global__ void __launch_bounds__(kDThreads, 1) distance_kernel(const DistArgs a
 // PF: the next 4-channel group is loaded into a second register set while the current one is used.  It costs
 // 4 PX registers (fewer warps per SM) and buys 7-15 % per pixel-channel; which of the two wins depends on how well
 // the resulting number of warp slots divides the problem (tlp_cost).
-template <int CT, int PX, bool PF>
+template <int CT, int PX, int PF>
 struct TlpCfg {
-    static constexpr int kAcc = CT * PX + (PF ? 4 * PX : 0);
+    static constexpr int kAcc = CT * PX + PF * 4 * PX;
     static constexpr int kWarps = kAcc <= 26 ? 32 : kAcc <= 40 ? 24 : kAcc <= 56 ? 20 : kAcc <= 80 ? 16 : 12;
     static constexpr int kThreads = kWarps * 32;
 };
 
-template <int CT, int PX, bool PF>
+template <int CT, int PX, int PF>
 __global__ void __launch_bounds__(TlpCfg<CT, PX, PF>::kThreads, 1) distance_tlp_kernel(const DistArgs a, int64_t units, int SI) {
     constexpr int W = TlpCfg<CT, PX, PF>::kWarps;
     constexpr int PP = PX / 2;
@@ -286,36 +286,49 @@ __global__ void __launch_bounds__(TlpCfg<CT, PX, PF>::kThreads, 1) distance_tlp_
 #pragma unroll
             for (int h = 0; h < PP; ++h) acc[c][h] = 0ull;
 
-        float xn[PF ? 4 : 1][PF ? PX : 1];
-        if (PF) {
+        // PF = prefetch depth in 4-channel groups (0: loads of a group are issued when it is used)
+        constexpr int DS = PF > 0 ? PF : 1;
+        float xn[DS][PF > 0 ? 4 : 1][PF > 0 ? PX : 1];
+        const float* ld = row;                                              // next group to fetch
+        const float* last = row + static_cast<int64_t>(KW - 4) * P;         // the part's last group (always in range)
+        if (PF > 0) {
 #pragma unroll
-            for (int q = 0; q < 4; ++q) {
-#pragma unroll
-                for (int i = 0; i < PX; ++i) xn[PF ? q : 0][PF ? i : 0] = ldg_stream_f(row + off[i]);
-                row += P;
-            }
-        }
-#pragma unroll(PF ? 1 : (PX == 2 ? 2 : 1))
-        for (int kk = 0; kk < KW; kk += 4) {
-            float x[4][PX];
-            if (PF) {
-#pragma unroll
-                for (int q = 0; q < 4; ++q)
-#pragma unroll
-                    for (int i = 0; i < PX; ++i) x[q][i] = xn[PF ? q : 0][PF ? i : 0];
-                if (kk + 4 >= KW) row -= 4 * P;   // last group: re-read it (in range) instead of branching around the loads
+            for (int d = 0; d < DS; ++d) {
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
 #pragma unroll
-                    for (int i = 0; i < PX; ++i) xn[PF ? q : 0][PF ? i : 0] = ldg_stream_f(row + off[i]);
-                    row += P;
+                    for (int i = 0; i < PX; ++i) xn[d][PF > 0 ? q : 0][PF > 0 ? i : 0] = ldg_stream_f(ld + off[i]);
+                    ld += P;
                 }
+            }
+        }
+#pragma unroll(PF > 0 ? 1 : (PX == 2 ? 2 : 1))
+        for (int kk0 = 0; kk0 < KW; kk0 += 4 * DS) {
+#pragma unroll
+          for (int d = 0; d < DS; ++d) {
+            const int kk = kk0 + 4 * d;
+            float x[4][PX];
+            if (PF > 0) {
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+#pragma unroll
+                    for (int i = 0; i < PX; ++i) x[q][i] = xn[d][PF > 0 ? q : 0][PF > 0 ? i : 0];
+                // refill this stage with group kk/4 + PF; past the end the last group is re-read (in range, unused)
+                const bool inr = kk + 4 * DS < KW;   // warp-uniform
+                const float* src = inr ? ld : last;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+#pragma unroll
+                    for (int i = 0; i < PX; ++i) xn[d][PF > 0 ? q : 0][PF > 0 ? i : 0] = ldg_stream_f(src + off[i]);
+                    src += P;
+                }
+                if (inr) ld = src;
             } else {
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
 #pragma unroll
-                    for (int i = 0; i < PX; ++i) x[q][i] = ldg_stream_f(row + off[i]);
-                    row += P;
+                    for (int i = 0; i < PX; ++i) x[q][i] = ldg_stream_f(ld + off[i]);
+                    ld += P;
                 }
             }
             f32x2 xp[4][PP];
@@ -332,11 +345,12 @@ __global__ void __launch_bounds__(TlpCfg<CT, PX, PF>::kThreads, 1) distance_tlp_
                     const f32x2 pb = pack2(pv[q], pv[q]);
 #pragma unroll
                     for (int h = 0; h < PP; ++h) {
-                        const f32x2 d = sub2(pb, xp[q][h]);
-                        acc[c][h] = fma2(d, d, acc[c][h]);
+                        const f32x2 df = sub2(pb, xp[q][h]);
+                        acc[c][h] = fma2(df, df, acc[c][h]);
                     }
                 }
             }
+          }
         }
         for (int o = 16; o >= L; o >>= 1) {  // partial sums of the SI parts (no iteration when SI == 1)
 #pragma unroll
@@ -365,19 +379,19 @@ __global__ void __launch_bounds__(TlpCfg<CT, PX, PF>::kThreads, 1) distance_tlp_
 // steps per round (+ a per-unit constant) x pixels a round retires per SM x the measured per-pixel-channel cost of
 // the form (4 px per lane holds fewer warps: x1.05; 8-lane parts fetch 32-byte pieces of a row: x1.05).  B200
 // measurements behind the factors: profiles/r01_distance_forms.txt.
-template <int CT, int PX, bool PF>
+template <int CT, int PX, int PF>
 static double tlp_cost(const DistArgs& a, int SI) {
     constexpr int W = TlpCfg<CT, PX, PF>::kWarps;
     const int unit_px = PX * 32 / SI;
     const int64_t units = a.N * ((a.P + unit_px - 1) / unit_px);
     const int64_t slots = static_cast<int64_t>(kNumSMs) * W;
     const double rounds = static_cast<double>((units + slots - 1) / slots);
-    double f = PF ? (PX == 4 ? 0.87 : 0.93) : 1.0;
+    double f = PF == 0 ? 1.0 : PF == 1 ? (PX == 4 ? 0.87 : 0.93) : (PX == 4 ? 0.85 : 0.88);
     if (SI == 4) f *= 1.05;
     return rounds * (static_cast<double>(a.K) / SI + 16.0) * (W * PX * 32) * f;
 }
 
-template <int CT, int PX, bool PF>
+template <int CT, int PX, int PF>
 static int launch_distance_tlp(DistArgs& a, int SI, cudaStream_t st) {
     constexpr int W = TlpCfg<CT, PX, PF>::kWarps;
     const size_t smem = sizeof(float) * CT * static_cast<size_t>(a.K + 4 * SI);
@@ -395,7 +409,7 @@ static int launch_distance_tlp(DistArgs& a, int SI, cudaStream_t st) {
 // tuning hooks: form 0 = automatic, 1 = 8-warp register-pipeline kernel, 2 / 4 = thread-level-parallel kernel with
 // 2 / 4 pixels per lane; split 0 = automatic, else the K split
 static int g_dist_variant = 0;
-static int g_dist_prefetch = -1;   // -1 = automatic, 0 / 1 = without / with the register prefetch
+static int g_dist_prefetch = -1;   // -1 = automatic, 0 / 1 / 2 = register prefetch depth in 4-channel groups
 int g_dist_split_value();
 
 // returns TSS_OK after a launch, or -1 when the thread-level-parallel form does not apply
@@ -408,19 +422,24 @@ static int launch_distance_auto(DistArgs& a, cudaStream_t st) {
     double best = 1e300;
     for (int px = 2; px <= 4; px += 2) {
         if (g_dist_variant != 0 && g_dist_variant != px) continue;
-        for (int pf = 0; pf <= 1; ++pf) {
+        for (int pf = 0; pf <= (px == 2 ? 2 : 1); ++pf) {   // depth 2 only with 2 px per lane (registers)
             if (g_dist_prefetch >= 0 && g_dist_prefetch != pf) continue;
             for (int si = 1; si <= 4; si *= 2) {
                 if (forced != 0 && forced != si) continue;
-                const double c = px == 2 ? (pf ? tlp_cost<CT, 2, true>(a, si) : tlp_cost<CT, 2, false>(a, si))
-                                         : (pf ? tlp_cost<CT, 4, true>(a, si) : tlp_cost<CT, 4, false>(a, si));
+                double c;
+                if (px == 2) c = pf == 0 ? tlp_cost<CT, 2, 0>(a, si) : pf == 1 ? tlp_cost<CT, 2, 1>(a, si) : tlp_cost<CT, 2, 2>(a, si);
+                else c = pf == 0 ? tlp_cost<CT, 4, 0>(a, si) : tlp_cost<CT, 4, 1>(a, si);
                 if (c < best) { best = c; best_px = px; best_si = si; best_pf = pf; }
             }
         }
     }
-    if (best == 1e300) return -1;   // forced split 8: only the register-pipeline kernel has it
-    if (best_px == 2) return best_pf ? launch_distance_tlp<CT, 2, true>(a, best_si, st) : launch_distance_tlp<CT, 2, false>(a, best_si, st);
-    return best_pf ? launch_distance_tlp<CT, 4, true>(a, best_si, st) : launch_distance_tlp<CT, 4, false>(a, best_si, st);
+    if (best == 1e300) return -1;   // forced split 8 / unsupported combination: the register-pipeline kernel
+    if (best_px == 2) {
+        if (best_pf == 0) return launch_distance_tlp<CT, 2, 0>(a, best_si, st);
+        if (best_pf == 1) return launch_distance_tlp<CT, 2, 1>(a, best_si, st);
+        return launch_distance_tlp<CT, 2, 2>(a, best_si, st);
+    }
+    return best_pf ? launch_distance_tlp<CT, 4, 1>(a, best_si, st) : launch_distance_tlp<CT, 4, 0>(a, best_si, st);
 }
 
 static int g_dist_split = 0;  // tuning hook: 0 = automatic
@@ -470,7 +489,7 @@ extern "C" int tss_tune_distance_variant(int v) {
 
 extern "C" int tss_tune_distance_prefetch(int v) {
     int old = tss::g_dist_prefetch;
-    if (v >= -1 && v <= 1) tss::g_dist_prefetch = v;
+    if (v >= -1 && v <= 2) tss::g_dist_prefetch = v;
     return old;
 }
 

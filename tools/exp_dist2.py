@@ -25,9 +25,13 @@ def run(N, C, K, h, w, copies, V, S):
     mb = 4 * N * K * h * w / 1e6
     print("V=%d S=%d N=%d C=%d K=%d %dx%d: %.1f us  %.0f GB/s" % (V, S, N, C, K, h, w, t, mb / t * 1e3), flush=True)
 
-for V in (0, 1):
-    run(16, 13, 256, 81, 241, 3, V, 0)
-    run(2, 19, 2048, 129, 257, 2, V, 0)
-    run(8, 19, 2048, 129, 257, 2, V, 0)
-    run(4, 19, 256, 129, 257, 3, V, 0)
-    run(4, 13, 256, 81, 241, 3, V, 0)
+for PFD in (2, -1):
+    lib().tss_tune_distance_prefetch(PFD)
+    for V, Ss in (((2, (1, 2, 4)), (0, (0,))) if PFD == 2 else ((0, (0,)),)):
+        for S in Ss:
+            print("prefetch", PFD, end=" ")
+            run(16, 13, 256, 81, 241, 3, V, S)
+            print("prefetch", PFD, end=" ")
+            run(2, 19, 2048, 129, 257, 2, V, S)
+            print("prefetch", PFD, end=" ")
+            run(8, 19, 2048, 129, 257, 2, V, S)
