@@ -318,6 +318,23 @@ def run_b200(args):
         scratch = meter.hist.clone()
         sharding.all_reduce_confusion(scratch, meter.bad.clone())
         fence()
+        # ... and keep replaying in chunks of 12 steps until two consecutive chunks agree within 10 % on the slowest
+        # rank (the decision is all-reduced: every rank replays the same number of steps), at most 40 chunks
+        prev = None
+        for _ in range(40):
+            c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            c0.record()
+            for i in range(12):
+                step(i)
+            c1.record()
+            torch.cuda.synchronize()
+            tchunk = torch.tensor([c0.elapsed_time(c1)], device=dev)
+            dist.all_reduce(tchunk, op=dist.ReduceOp.MAX)
+            cur = float(tchunk.item())
+            if prev is not None and abs(cur - prev) <= 0.1 * min(cur, prev):
+                break
+            prev = cur
+        fence()
     for i in range(max(args.warmup, 3)):
         step(i)
     fence()
