@@ -1,32 +1,37 @@
 #!/usr/bin/env python
 """bench.py -- pseudo-labelled px/s of the self-training label path (BASELINE.json metric).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--config cfg1|cfg2|cfg3|cfg4|cfg5]
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
 
-Workload (BASELINE.json configs[1], "cfg2"): one STEP = one batch of 16 synthetic Freiburg-shape frames
-(640x1920, 13 classes; DeepLabv2 1/8-stride(+1) logits [16,13,81,241] and 256-ch features
-[16,256,81,241]) through
+Default workload (BASELINE.json configs[1], "cfg2"): one STEP = one batch of 16 synthetic Freiburg-shape frames
+(640x1920, 13 classes; DeepLabv2 1/8-stride(+1) logits [16,13,81,241] and 256-ch features [16,256,81,241]) through
 
-    1. fused bilinear upsample -> softmax -> argmax/confidence -> fp16 cast -> class-wise threshold +
-       whitelist  (uint8 label, fp16 confidence, thresholded uint8 label at 640x1920),
-    2. argmax label + per-(image, class) segmented feature means + sequential prototype update,
-    3. confusion-matrix accumulation of the labels against a uint8 ground-truth map (mIoU at the end).
+    1. fused bilinear upsample -> softmax -> argmax/confidence -> fp16 cast -> class-wise threshold + whitelist
+       (uint8 label, fp16 confidence, thresholded uint8 label at 640x1920)            [XU / issue bound]
+    2. argmax label + per-(image, class) segmented feature sums                        [HBM bound]
+       -- 1 and 2 run AT THE SAME TIME on every SM (two capture streams, co-resident CTAs) --
+    3. confusion-matrix accumulation of the labels against a uint8 ground-truth map (mIoU at the end),
+    4. means + sequential prototype update (+ the exchange between GPUs) on a tail stream, beside the next step.
 
-value = frames * 640 * 1920 / device time, inputs resident in HBM.  Images shard across ranks (weak
-scaling: 16 frames per rank per step); the only collectives are the prototype partial ([13,256] fp32 +
-counts, once per step) and the [13,13] int64 confusion matrix (once, inside the timed region).
-e2e = the same step through b200seg.dropin with pinned HOST buffers, H2D + D2H inside the timed region.
+value = frames * 640 * 1920 / device time, inputs resident in HBM.  Images shard across ranks (weak scaling: 16
+frames per rank per step); the only collectives are the prototype mean vectors (the finalize kernel's own NVLink
+stores + one barrier, once per step) and the [13,13] int64 confusion matrix (once, inside the timed region).
+e2e = the same step through b200seg.pipeline.HostLabelPipeline with pinned HOST buffers, H2D + D2H inside the timed
+region.  The other BASELINE.json configurations run with --config (cfg1, cfg3, cfg4, cfg5); the default line also
+times the distance / rectify kernel and the CE + RCE kernels at their BASELINE shapes (aux_stages).
 """
 from __future__ import annotations
 
 import argparse
 import json
+import math
 import os
 import subprocess
 import sys
 import threading
 import time
+import types
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
@@ -37,24 +42,57 @@ import torch  # noqa: E402
 
 METRIC = "pseudo-labelled px/sec (+proto update, mIoU)"
 UNIT = "px/s"
-CFG = dict(frames=16, H=640, W=1920, h=81, w=241, C=13, K=256, thr=0.3, keep=(5, 11), ignore=12)
-N_SETS = 4  # rotating input sets: 4 x (116 MB in + 79 MB out) = 780 MB working set >> 126 MB L2
+N_SETS = 4  # rotating input sets (cfg2: 4 x (116 MB in + 79 MB out) = 780 MB working set >> 126 MB L2)
+
+CONFIGS = {
+    # BASELINE.json configs[0]: 4 frames 640x320 -> DeepLabv2 1/8(+1) maps 41x81; pseudo-label + prototypes + mIoU
+    "cfg1": dict(frames=4, H=320, W=640, h=41, w=81, C=13, K=256, thr=0.3, keep=(5, 11), ignore=12, kind="label_step",
+                 title="cfg1: 4 thermal frames 640x320, 13 classes (random-init DeepLabv2 shapes): pseudo-labels + "
+                       "256-ch prototype update + confusion matrix"),
+    # configs[1] -- the headline
+    "cfg2": dict(frames=16, H=640, W=1920, h=81, w=241, C=13, K=256, thr=0.3, keep=(5, 11), ignore=12, kind="label_step",
+                 title="cfg2: Freiburg 1920x640, 13 classes, batch 16/GPU: fused upsample/softmax/argmax/threshold "
+                       "pseudo-labels + 256-ch prototype update + confusion matrix"),
+    # configs[2]: Cityscapes shape, 2048-ch 1/8-stride features: prototype accumulation + distance-weighted labels
+    "cfg3": dict(frames=4, H=1024, W=2048, h=129, w=257, C=19, K=2048, ignore=255, kind="proto_distance",
+                 title="cfg3: Cityscapes 2048x1024, 19 classes, 2048-ch 1/8-stride features, 4 images/GPU/step: prototype "
+                       "accumulation + update, distance -> weights -> rectified labels (unit: feature px)"),
+    # configs[3]: full self-training round over 10k frames
+    "cfg4": dict(frames=16, H=320, W=640, h=41, w=81, C=13, K=256, thr=0.3, keep=(5, 11), ignore=12, kind="self_train_round",
+                 total_frames=10000,
+                 title="cfg4: self-training round over 10k synthetic 640x320 frames, 16 frames/GPU/step: pseudo-labels, "
+                       "prototype update (exchange), rectified labels from the 1/8 features, CE+RCE forward+backward at 1/4"),
+    # configs[4]: evaluation sweep over 50k label maps
+    "cfg5": dict(frames=1024, H=256, W=512, C=19, kind="eval_sweep", total_frames=50000,
+                 title="cfg5: confusion-matrix mIoU over 50k synthetic 19-class 256x512 uint8 label maps, 1024 maps/GPU/step"),
+}
+CFG = CONFIGS["cfg2"]   # tools/ import this
 
 
-def workload_name():
-    return ("cfg2: Freiburg 1920x640, 13 classes, batch %d/GPU: fused upsample/softmax/argmax/threshold "
-            "pseudo-labels + 256-ch prototype update + confusion matrix" % CFG["frames"])
+def workload_name(cfg=None):
+    return (cfg or CFG)["title"]
 
 
-def algorithmic_bytes():
+def algorithmic_bytes(cfg=None):
     """Compulsory HBM traffic of one step per stage; every input element read once,
     every output written once."""
-    c = CFG
-    n, P, px = c["frames"], c["h"] * c["w"], c["H"] * c["W"]
-    pl = 4 * c["C"] * P * n + n * px * (1 + 2 + 1)                  # logits in; label, conf16, label_thr out
+    c = cfg or CFG
+    n = c["frames"]
+    if c["kind"] == "eval_sweep":
+        return {"confusion": n * c["H"] * c["W"] * 2}
+    P, px = c["h"] * c["w"], c["H"] * c["W"]
     proto = n * P * (4 * c["K"] + 4 * c["C"]) + 4 * n * c["C"] * (c["K"] + 1)
+    if c["kind"] == "proto_distance":
+        dist = n * P * (4 * c["K"] + 4 * c["C"] + 1 + 8)        # feat + soft in, uint8 hard in, int64 label out
+        return {"prototype": proto, "distance_rectify": dist}
+    pl = 4 * c["C"] * P * n + n * px * (1 + 2 + 1)                  # logits in; label, conf16, label_thr out
     hist = n * px * 2                                               # uint8 pred + uint8 gt
-    return {"pseudo_label": pl, "prototype": proto, "confusion": hist}
+    out = {"pseudo_label": pl, "prototype": proto, "confusion": hist}
+    if c["kind"] == "self_train_round":
+        q = (c["H"] // 4) * (c["W"] // 4)
+        out["rectify_sampled"] = n * (P * 4 * c["K"] + q * (4 * c["C"] + 1 + 8))
+        out["ce_rce_fwd_bwd"] = n * q * ((4 * c["C"] + 8) * 2 + 4 * c["C"]) + n * q * 4 * c["C"] * 2   # + the upsample round trip
+    return out
 
 
 # ------------------------------------------------------------------------------------------------
@@ -96,12 +134,16 @@ class ClockSampler(threading.Thread):
 
 
 def ncu_traffic(stage: str):
-    """DRAM bytes per launch of a stage from the committed ncu --set full capture (profiles/r01_traffic.json), or None."""
-    try:
-        with open(os.path.join(ROOT, "profiles", "r01_traffic.json")) as fh:
-            return int(json.load(fh)[stage])
-    except (OSError, KeyError, ValueError):
-        return None
+    """Steady-state DRAM bytes per launch of a stage's dominant kernel from the committed ncu --set full capture
+    (profiles/r02_traffic.json: a LATE launch of a multi-launch run, so dirty output lines of earlier launches are
+    evicted inside the measured launch as they are in the timed loop), or None."""
+    for name in ("r02_traffic.json", "r01_traffic.json"):
+        try:
+            with open(os.path.join(ROOT, "profiles", name)) as fh:
+                return int(json.load(fh)[stage])
+        except (OSError, KeyError, ValueError):
+            continue
+    return None
 
 
 def measured_peak_gbs():
@@ -113,93 +155,345 @@ def measured_peak_gbs():
 
 
 # ------------------------------------------------------------------------------------------------
-# synthetic inputs (SURVEY.md section 8(d) cfg 2): logits 3*randn so that confidences straddle 0.3
-def make_inputs(device, seed: int, frames: int):
-    c = CFG
+# synthetic inputs: logits 3*randn so that confidences straddle 0.3
+def make_inputs(device, seed: int, frames: int, cfg=None):
+    c = cfg or CFG
     g = torch.Generator(device=device).manual_seed(seed)
+    if c["kind"] == "eval_sweep":
+        gt = torch.randint(0, c["C"] + 1, (frames, c["H"], c["W"]), generator=g, device=device, dtype=torch.int16)
+        gt = torch.where(torch.rand(gt.shape, generator=g, device=device) < 0.01, torch.full_like(gt, 255), gt)
+        same = torch.rand(gt.shape, generator=g, device=device) < 0.7
+        rnd = torch.randint(0, c["C"], gt.shape, generator=g, device=device, dtype=torch.int16)
+        pred = torch.where(same, gt.clamp(max=c["C"] - 1), rnd)
+        return pred.to(torch.uint8), gt.to(torch.uint8)
     logits = 3.0 * torch.randn(frames, c["C"], c["h"], c["w"], generator=g, device=device)
     feat = torch.randn(frames, c["K"], c["h"], c["w"], generator=g, device=device)
+    if c["kind"] == "proto_distance":
+        soft = torch.softmax(3.0 * torch.randn(frames, c["C"], c["h"], c["w"], generator=g, device=device), 1)
+        hard = torch.full((frames, 1, c["h"], c["w"]), 255, dtype=torch.uint8, device=device)
+        return logits, feat, soft, hard
     gt = torch.randint(0, c["C"], (frames, c["H"], c["W"]), generator=g, device=device, dtype=torch.int16).to(torch.uint8)
+    if c["kind"] == "self_train_round":
+        q = (c["H"] // 4, c["W"] // 4)
+        soft = torch.softmax(3.0 * torch.randn(frames, c["C"], *q, generator=g, device=device), 1)
+        hard = torch.where(torch.rand((frames, 1) + q, generator=g, device=device) < 0.2,
+                           torch.full((frames, 1) + q, 5, dtype=torch.int16, device=device),
+                           torch.full((frames, 1) + q, c["ignore"], dtype=torch.int16, device=device)).to(torch.uint8)
+        return logits, feat, gt, soft, hard
     return logits, feat, gt
 
 
+def deeplab_inputs(cfg, device):
+    """cfg1: out / feat of the reference's random-init DeepLabv2-ResNet101 (baseline/_ref/models, torch.manual_seed(0))
+    on 4 synthetic frames, or None when the reference tree is not there (the caller falls back to randn maps)."""
+    ref = load_reference()
+    if ref is None or not hasattr(ref, "models"):
+        return None
+    try:
+        torch.manual_seed(0)
+        net = ref.models.Deeplab(torch.nn.BatchNorm2d, num_classes=cfg["C"], num_channels=1, freeze_bn=False, get_feat=True)
+        net = net.to(device).eval()
+        g = torch.Generator().manual_seed(1234)
+        x = torch.rand(cfg["frames"], 1, cfg["H"], cfg["W"], generator=g).to(device)
+        with torch.no_grad():
+            out = net(x)
+        return out["out"].float().contiguous(), out["feat"].float().contiguous()
+    except Exception as e:  # noqa: BLE001
+        print("bench.py: DeepLab input generation failed (%s: %s); using randn maps" % (type(e).__name__, e), file=sys.stderr)
+        return None
+
+
 # ------------------------------------------------------------------------------------------------
-# CPU reference arm: the oracle (= the reference's own torch/numpy op sequence) on the host cores
-def cpu_step(O, logits, feat, gt, bank, hist):
-    """One step of the same workload on CPU tensors, as the reference computes it:
-    upsample -> softmax -> max (self_training.py:53-55 order + generate_pseudo_label.py:85), fp16/uint8
-    storage casts (:91,:94), threshold block (data/freiburg_dataset.py:115-123), calculate_mean_vector +
-    update_objective_SingleVector loop (cal_prototype.py:72-75), _fast_hist (utils/eval_tools.py:4-9)."""
-    c = CFG
-    conf, lab = O.pseudo_label_upsampled(logits, (c["H"], c["W"]))
-    lab_u8 = lab.numpy().astype(np.uint8)
-    conf16 = conf.numpy().astype(np.float16)
-    for i in range(lab_u8.shape[0]):
-        O.threshold_hard_label(lab_u8[i], conf16[i], c["thr"], c["ignore"], keep=c["keep"])
-    vectors, ids = O.class_mean_vectors(feat, logits, c["C"])
-    for t, v in zip(ids, vectors):
-        bank.update(t, v, "mean")
-    g = gt.numpy()
-    for i in range(lab_u8.shape[0]):
-        hist += O.fast_hist(lab_u8[i].reshape(-1), g[i].reshape(-1), c["C"])
+# The reference's own modules for the CPU arm: baseline/_ref/ (staged by __graft_entry__.build() from the unmodified
+# reference; pure Python, so it cannot be pip-installed -- no setup.py / pyproject).
+_REF = [False, None]
 
 
-def run_reference(args):
+def load_reference():
+    if _REF[0]:
+        return _REF[1]
+    _REF[0] = True
+    root = os.path.join(ROOT, "baseline", "_ref")
+    if not os.path.isfile(os.path.join(root, "self_training.py")):
+        return None
+    try:
+        import importlib
+        import scipy.signal
+        import scipy.signal.windows
+        if not hasattr(scipy.signal, "gaussian"):            # library drift, not arithmetic (SURVEY 8(c))
+            scipy.signal.gaussian = scipy.signal.windows.gaussian
+        if "visdom" not in sys.modules:
+            vis = types.ModuleType("visdom")
+            vis.Visdom = lambda *a, **k: None
+            sys.modules["visdom"] = vis
+        if "torchvision.models.utils" not in sys.modules:
+            import torch.hub
+            tvu = types.ModuleType("torchvision.models.utils")
+            tvu.load_state_dict_from_url = torch.hub.load_state_dict_from_url
+            sys.modules["torchvision.models.utils"] = tvu
+        sys.path.insert(0, root)
+        ns = types.SimpleNamespace()
+        import warnings
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            ns.cal_prototype = importlib.import_module("cal_prototype")
+            ns.self_training = importlib.import_module("self_training")
+            ns.eval_tools = importlib.import_module("utils.eval_tools")
+            ns.models = importlib.import_module("models")
+        _REF[1] = ns
+    except Exception as e:  # noqa: BLE001
+        print("bench.py: baseline/_ref present but not importable (%s: %s); CPU arm = oracle port" % (type(e).__name__, e),
+              file=sys.stderr)
+    return _REF[1]
+
+
+class CpuArm:
+    """One step of a workload on CPU tensors as the reference computes it.  With baseline/_ref the reference's OWN
+    functions run wherever the path is a function there (Class_Features.calculate_mean_vector +
+    update_objective_SingleVector cal_prototype.py:72-75, SelfTrain.feat_prototype_distance / get_prototype_weight /
+    rce / seg_loss / calculate_mean_vector, utils.eval_tools._fast_hist); the inline blocks of the scripts
+    (upsample -> softmax -> max generate_pseudo_label.py:83-85 / self_training.py:53-55, fp16 / uint8 storage casts
+    :91,:94, the threshold block data/freiburg_dataset.py:115-123, the rectify block self_training.py:103-112) are
+    the same torch / numpy calls in the same order (oracle/label_path.py, pinned to the reference by the goldens)."""
+
+    def __init__(self, cfg):
+        from oracle import label_path as O
+        self.O, self.cfg = O, cfg
+        self.ref = load_reference()
+        self.kind = "reference" if self.ref is not None else "port"
+        c = cfg
+        if c["kind"] == "eval_sweep":
+            self.hist = np.zeros((c["C"], c["C"]))
+            return
+        if self.ref is not None:
+            self.cf = self.ref.cal_prototype.Class_Features(torch.device("cpu"), numbers=c["C"])
+            if c["K"] != 256:
+                self.cf.objective_vectors = torch.zeros([c["C"], c["K"]])
+            a = types.SimpleNamespace(num_classes=c["C"], ignore_index=c["ignore"], proto_temperature=0.5, proto_momentum=1e-4,
+                                      rce_alpha=0.1, rce_beta=1.0)
+            self.st = self.ref.self_training.SelfTrain(a, None, None, None, torch.device("cpu"), None)
+            self.st.objective_vectors = torch.randn(c["C"], c["K"], generator=torch.Generator().manual_seed(5))
+        else:
+            self.bank = O.PrototypeBank(c["C"], c["K"])
+            self.protos = torch.randn(c["C"], c["K"], generator=torch.Generator().manual_seed(5))
+        self.hist = np.zeros((c["C"], c["C"]))
+
+    def fast_hist(self, pred, gt, C):
+        if self.ref is not None:
+            return self.ref.eval_tools._fast_hist(pred, gt, C)
+        return self.O.fast_hist(pred, gt, C)
+
+    def prototypes(self, feat, logits):
+        c = self.cfg
+        if self.ref is not None:
+            vectors, ids = self.cf.calculate_mean_vector(feat, logits)
+            for t in range(len(ids)):
+                self.cf.update_objective_SingleVector(ids[t], vectors[t].detach().cpu(), "mean")
+        else:
+            vectors, ids = self.O.class_mean_vectors(feat, logits, c["C"])
+            for t, v in zip(ids, vectors):
+                self.bank.update(t, v, "mean")
+
+    def label_step(self, logits, feat, gt):
+        O, c = self.O, self.cfg
+        conf, lab = O.pseudo_label_upsampled(logits, (c["H"], c["W"]))
+        lab_u8 = lab.numpy().astype(np.uint8)
+        conf16 = conf.numpy().astype(np.float16)
+        for i in range(lab_u8.shape[0]):
+            O.threshold_hard_label(lab_u8[i], conf16[i], c["thr"], c["ignore"], keep=c["keep"])
+        self.prototypes(feat, logits)
+        g = gt.numpy()
+        for i in range(lab_u8.shape[0]):
+            self.hist += self.fast_hist(lab_u8[i].reshape(-1).astype(np.int64), g[i].reshape(-1).astype(np.int64), c["C"])
+
+    def proto_distance(self, logits, feat, soft, hard):
+        O, c = self.O, self.cfg
+        self.prototypes(feat, logits)
+        if self.ref is not None:
+            d = self.st.feat_prototype_distance(feat)
+            near, _ = d.min(dim=1, keepdim=True)
+            w = torch.nn.functional.softmax(-(d - near) * 0.5, dim=1)       # get_prototype_weight :139-142 (no full2weak here)
+        else:
+            w = O.prototype_weight(feat, self.protos, 0.5)
+        O.rectify_labels(w, soft, hard.long(), 0.0, c["ignore"])
+
+    def self_train_round(self, logits, feat, gt, soft, hard):
+        O, c = self.O, self.cfg
+        self.label_step(logits, feat, gt)
+        q = (c["H"] // 4, c["W"] // 4)
+        fq = O.upsample_bilinear_ac(feat, q)                                  # self_training.py:69
+        if self.ref is not None:
+            d = self.st.feat_prototype_distance(fq)
+            near, _ = d.min(dim=1, keepdim=True)
+            w = torch.nn.functional.softmax(-(d - near) * 0.5, dim=1)
+        else:
+            w = O.prototype_weight(fq, self.protos, 0.5)
+        lab, _ = O.rectify_labels(w, soft, hard.long(), 0.0, c["ignore"])
+        x = O.upsample_bilinear_ac(logits, q).requires_grad_(True)
+        y = lab.reshape(lab.shape[0], *q)
+        if self.ref is not None:
+            loss = 0.1 * self.st.seg_loss(x, y) + 1.0 * self.st.rce(x, y.clone())
+        else:
+            loss = 0.1 * O.cross_entropy(x, y, c["ignore"]) + 1.0 * O.reverse_cross_entropy(x, y.clone(), c["C"], c["ignore"])
+        loss.backward()
+
+    def eval_sweep(self, pred, gt):
+        c = self.cfg
+        p, g = pred.numpy().astype(np.int64), gt.numpy().astype(np.int64)
+        for i in range(p.shape[0]):                                           # evaluate() :49-51
+            self.hist += self.fast_hist(p[i].flatten(), g[i].flatten(), c["C"])
+
+    def step(self, data):
+        getattr(self, self.cfg["kind"])(*data)
+
+    def miou(self):
+        return float(self.O.metrics_from_hist(self.hist, self.cfg["C"])[2]) if self.cfg["C"] in (13, 19) else float("nan")
+
+
+CPU_SAMPLE = {"label_step": 2, "proto_distance": 1, "self_train_round": 2, "eval_sweep": 64}   # frames per CPU step
+
+
+def run_reference(args, cfg):
     """--impl reference: rank 0 only, all host threads, each step a bounded sample of the workload."""
-    rank = int(os.environ.get("RANK", "0"))
-    if rank != 0:
+    if int(os.environ.get("RANK", "0")) != 0:
         return
-    from oracle import label_path as O
-
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    frames = 2  # of the 16-frame batch: ~1 s of CPU work per step
-    sets = [make_inputs("cpu", 1234 + s, frames) for s in range(2)]
-    bank = O.PrototypeBank(CFG["C"], CFG["K"])
-    hist = np.zeros((CFG["C"], CFG["C"]))
-    for i in range(args.warmup):
-        cpu_step(O, *sets[i % 2], bank, hist)
+    frames = min(CPU_SAMPLE[cfg["kind"]], cfg["frames"])
+    if cfg is CONFIGS["cfg1"]:
+        frames = cfg["frames"]
+    sets = [make_inputs("cpu", 1234 + s, frames, cfg) for s in range(2)]
+    arm = CpuArm(cfg)
+    steps = args.steps if args.steps is not None else 20
+    if cfg["kind"] == "proto_distance":
+        steps = min(steps, 4)                                                # ~15 s of CPU per Cityscapes image
+    for i in range(min(args.warmup, 2)):
+        arm.step(sets[i % 2])
     t0 = time.perf_counter()
-    for i in range(args.steps):
-        cpu_step(O, *sets[i % 2], bank, hist)
+    for i in range(steps):
+        arm.step(sets[i % 2])
     dt = time.perf_counter() - t0
-    miou = O.metrics_from_hist(hist, CFG["C"])[2]
-    px = frames * CFG["H"] * CFG["W"] * args.steps
+    px = frames * (cfg["h"] * cfg["w"] if cfg["kind"] == "proto_distance" else cfg["H"] * cfg["W"]) * steps
     val = px / dt
-    sample = "%d of %d frames per step (same shapes, same stages), %d steps" % (frames, CFG["frames"], args.steps)
+    sample = "%d of %d frames per step (same shapes, same stages), %d steps" % (frames, cfg["frames"], steps)
+    how = ("reference's own functions from baseline/_ref (Class_Features, SelfTrain.*, _fast_hist) + its inline blocks as the "
+           "same torch/numpy calls" if arm.kind == "reference" else "oracle port of the reference's torch/numpy op sequence")
     print(json.dumps({
-        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
+        "warmup": min(args.warmup, 2), "ms_per_step": 1e3 * dt / steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": workload_name(), "sample": sample, "miou": float(miou)},
-        "cpu_baseline": {"value": val, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port", "sample": sample},
+        "config": {"workload": workload_name(cfg), "sample": sample, "miou": arm.miou(), "how": how},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": torch.get_num_threads(), "kind": arm.kind, "sample": sample},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0}))
 
 
-def cpu_baseline(budget_s: float = 12.0):
-    """The oracle timed on this box's host cores on a bounded sample of the same workload (rank 0, N=1)."""
-    from oracle import label_path as O
-
+def cpu_baseline(cfg, budget_s: float = 12.0):
+    """The reference's CPU path timed on this box's host cores on a bounded sample of the same workload (rank 0, N=1)."""
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    frames = 2
-    data = make_inputs("cpu", 1234, frames)
-    bank = O.PrototypeBank(CFG["C"], CFG["K"])
-    hist = np.zeros((CFG["C"], CFG["C"]))
-    cpu_step(O, *data, bank, hist)  # warm-up
+    frames = min(CPU_SAMPLE[cfg["kind"]], cfg["frames"])
+    data = make_inputs("cpu", 1234, frames, cfg)
+    arm = CpuArm(cfg)
+    arm.step(data)  # warm-up
     reps, t0 = 0, time.perf_counter()
-    while reps < 3 or (time.perf_counter() - t0 < budget_s and reps < 50):
-        cpu_step(O, *data, bank, hist)
+    while reps < 2 or (time.perf_counter() - t0 < budget_s and reps < 50):
+        arm.step(data)
         reps += 1
     dt = time.perf_counter() - t0
-    return {"value": frames * CFG["H"] * CFG["W"] * reps / dt, "unit": UNIT, "cores": torch.get_num_threads(),
-            "kind": "port", "sample": "%d of %d frames per step x %d steps in %.1f s (oracle = the reference's own "
-            "torch/numpy op sequence, all host threads)" % (frames, CFG["frames"], reps, dt)}
+    px = frames * (cfg["h"] * cfg["w"] if cfg["kind"] == "proto_distance" else cfg["H"] * cfg["W"])
+    return {"value": px * reps / dt, "unit": UNIT, "cores": torch.get_num_threads(), "kind": arm.kind,
+            "sample": "%d of %d frames per step x %d steps in %.1f s (%s, all host threads)" % (
+                frames, cfg["frames"], reps, dt, "reference's own functions from baseline/_ref + its inline blocks"
+                if arm.kind == "reference" else "oracle = the reference's own torch/numpy op sequence")}
 
 
 # ------------------------------------------------------------------------------------------------
-def run_b200(args):
+def parity_check(cfg, ops, out, data):
+    """One frame of the step the bench is about to time, against the oracle (rank 0, before timing)."""
+    from oracle import label_path as O
+
+    res = {}
+    if cfg["kind"] == "eval_sweep":
+        pred, gt = data
+        h, bad = ops.confusion_matrix(pred[:8].reshape(-1), gt[:8].reshape(-1), cfg["C"])
+        ref = O.fast_hist(pred[:8].cpu().numpy().reshape(-1).astype(np.int64), gt[:8].cpu().numpy().reshape(-1).astype(np.int64), cfg["C"])
+        res["hist_exact"] = bool(np.array_equal(h.cpu().numpy(), ref)) and int(bad) == 0
+        return res
+    logits, feat = data[0][:1].cpu(), data[1][:1].cpu()
+    C = cfg["C"]
+    if "pl" in out:
+        pl = out["pl"]
+        up = O.upsample_bilinear_ac(logits, (cfg["H"], cfg["W"]))
+        prob = torch.softmax(up, 1)
+        conf_ref, lab_ref = prob.max(1)
+        top2 = prob.topk(2, dim=1)[0]
+        safe = ((top2[:, 0] - top2[:, 1]) > 1e-6)[0].numpy()
+        lab = pl.label[0].cpu().numpy()
+        res["label_mismatch_outside_1e-6_margin"] = int((lab[safe] != lab_ref[0].numpy()[safe]).sum())
+        same = lab == lab_ref[0].numpy()
+        c16 = pl.conf16[0].cpu().numpy().astype(np.float32)
+        res["conf_max_abs_err_fp16_stored"] = float(np.abs(c16 - conf_ref[0].numpy().astype(np.float16).astype(np.float32))[same].max())
+        gt0 = data[2][0].cpu().numpy().reshape(-1).astype(np.int64)
+        h, _ = ops.confusion_matrix(pl.label[0].reshape(-1), data[2][0].reshape(-1), C)
+        res["hist_exact"] = bool(np.array_equal(h.cpu().numpy(), O.fast_hist(lab.reshape(-1).astype(np.int64), gt0, C)))
+    if "means" in out:
+        m = out["means"]
+        vr, ir = O.class_mean_vectors(feat, logits, C)
+        valid = list(np.nonzero(m.valid[0].cpu().numpy())[0])
+        err = 0.0
+        for t, v in zip(ir, vr):
+            a, b = m.vectors[0, t].cpu().numpy().astype(np.float64), v.reshape(-1).numpy().astype(np.float64)
+            err = max(err, float(np.abs(a - b).max() / max(np.abs(b).max(), 1e-30)))
+        res["class_ids_equal"] = valid == ir
+        res["proto_mean_max_rel_err"] = err
+    if "dist_label" in out:
+        protos = out["protos"].cpu()
+        soft, hard = data[2][:1].cpu(), data[3][:1].cpu().long()
+        w_ref = O.prototype_weight(feat, protos, 0.5)
+        lab_ref, rect = O.rectify_labels(w_ref, soft, hard, 0.0, cfg["ignore"])
+        d_ref = O.prototype_distance(feat, protos)
+        bad = (out["dist_label"][:1].cpu() != lab_ref).numpy()
+        srt = np.sort(rect.numpy(), axis=1)
+        eta = 2 * 0.5 * 1e-5 * float(d_ref.max())
+        ok = (srt[:, -1:] - srt[:, -2:-1]) < 1e-6 + 2 * eta * srt[:, -1:]
+        res["rectified_label_mismatch_outside_margin"] = int((bad & ~ok).sum())
+        res["rectified_label_mismatch_total"] = int(bad.sum())
+    return res
+
+
+def parity_ok(res) -> bool:
+    return (res.get("label_mismatch_outside_1e-6_margin", 0) == 0 and res.get("hist_exact", True)
+            and res.get("class_ids_equal", True) and res.get("proto_mean_max_rel_err", 0.0) <= 1e-5
+            and res.get("conf_max_abs_err_fp16_stored", 0.0) <= 2.5e-4
+            and res.get("rectified_label_mismatch_outside_margin", 0) == 0)
+
+
+# ------------------------------------------------------------------------------------------------
+def bind_near_gpu(local_rank: int):
+    """Pin this rank's threads (and with them the first-touch placement of its pinned host buffers) to the host NUMA
+    node of its GPU when the box has more than one.  Returns a short description for the JSON line."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        bus = pynvml.nvmlDeviceGetPciInfo(pynvml.nvmlDeviceGetHandleByIndex(local_rank)).busId
+        bus = bus.decode() if isinstance(bus, bytes) else bus
+        node_file = "/sys/bus/pci/devices/%s/numa_node" % bus.lower()[-12:]
+        node = int(open(node_file).read().strip())
+        nodes = [d for d in os.listdir("/sys/devices/system/node") if d.startswith("node") and d[4:].isdigit()]
+        if node < 0 or len(nodes) < 2:
+            return "single host NUMA node (%d listed): nothing to bind" % len(nodes)
+        cpus = []
+        for part in open("/sys/devices/system/node/node%d/cpulist" % node).read().strip().split(","):
+            a, _, b = part.partition("-")
+            cpus += list(range(int(a), int(b or a) + 1))
+        os.sched_setaffinity(0, cpus)
+        return "bound to host NUMA node %d (%d cpus)" % (node, len(cpus))
+    except Exception as e:  # noqa: BLE001
+        return "not bound (%s)" % type(e).__name__
+
+
+def run_b200(args, cfg):
     import torch.distributed as dist
 
     from b200seg import dropin, ops, sharding
@@ -211,6 +505,7 @@ def run_b200(args):
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     ws = int(os.environ.get("WORLD_SIZE", "1"))
+    numa = bind_near_gpu(local_rank) if ws > 1 else "single rank"
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if ws > 1:
@@ -227,17 +522,38 @@ def run_b200(args):
             sys.stdout.flush()
             os.dup2(saved, 1)
             os.close(saved)
-    c = CFG
-    frames, C, size = c["frames"], c["C"], (c["H"], c["W"])
-    sets = [make_inputs(dev, 1234 + 1000 * rank + s, frames) for s in range(N_SETS)]
+    c = cfg
+    kind = c["kind"]
+    frames, C = c["frames"], c["C"]
+    size = (c["H"], c["W"])
+    steps = args.steps
+    if steps is None:
+        steps = 50 if "total_frames" not in c else max(3, math.ceil(c["total_frames"] / (frames * ws)))
+    warm = max(args.warmup, 3)
+    n_sets = N_SETS if kind != "eval_sweep" else 8
+    data_note = "synthetic"
+    sets = [make_inputs(dev, 1234 + 1000 * rank + s, frames, c) for s in range(n_sets)]
+    if c is CONFIGS["cfg1"]:
+        dl = deeplab_inputs(c, dev)
+        if dl is not None:   # the network's outputs on 4 synthetic frames (random-init weights, torch.manual_seed(0))
+            sets = [(dl[0], dl[1], s[2]) for s in sets]
+            data_note = "synthetic frames through the reference's random-init DeepLabv2-ResNet101 (baseline/_ref/models)"
+        else:
+            data_note = "synthetic maps of the DeepLabv2 output shapes (reference model code not staged)"
 
-    bank = sharding.ShardedPrototypes(C, c["K"], dev, ops.UPDATE_MEAN, True, 0.9999)
+    has_proto = kind != "eval_sweep"
+    bank = sharding.ShardedPrototypes(C, c.get("K", 32), dev, ops.UPDATE_MEAN, True, 0.9999) if has_proto else None
+    if kind in ("proto_distance", "self_train_round"):
+        bank.protos.copy_(torch.randn(C, c["K"], generator=torch.Generator().manual_seed(5)).to(dev))
+        bank.num.fill_(200.0)
+        bank.mode = ops.UPDATE_MOVING_AVERAGE            # self_training.py:125-126 (start_mean=False, m = 1e-4)
+        bank.start_mean, bank.momentum = False, 1e-4
     meter = dropin.ConfusionMeter(C, dev)
     # N > 1: the mean vectors are exchanged by the finalize kernel's own stores into every peer's gather buffer
     # (sharding.PeerGather, symmetric memory over NVLink); NCCL all_gather is the fallback when peer mapping is
     # not available.  All ranks must agree, so the outcome is all-reduced.
     gather, exchange = None, "none at N=1"
-    if ws > 1:
+    if ws > 1 and has_proto:
         ok = torch.ones(1, device=dev)
         if args.exchange == "peer":
             try:
@@ -252,90 +568,185 @@ def run_b200(args):
         if ok.item() == 0:
             gather = None
         exchange = ("finalize kernel stores its mean vectors into every rank's symmetric-memory gather buffer over NVLink, one barrier, "
-                    "sequential update kernel; all inside the step's CUDA graph" if gather is not None else
-                    "one NCCL all_gather of the mean vectors + sequential update kernel after the graph replay")
+                    "sequential update kernel; on the tail stream, beside the next step" if gather is not None else
+                    "one NCCL all_gather of the mean vectors + sequential update kernel on the tail stream")
 
-    def stage_pl(i):
-        return ops.pseudo_label(sets[i % N_SETS][0], size=size, thr=c["thr"], keep=c["keep"], ignore_index=c["ignore"])
+    side = torch.cuda.Stream(dev)    # capture fork: the HBM-bound accumulate kernel beside the XU-bound pseudo-label kernel
+    tail = torch.cuda.Stream(dev)    # finalize / exchange / update of step i beside the kernels of step i+1
+    identity_weak = None
+    if kind == "self_train_round":
+        q = (c["H"] // 4, c["W"] // 4)
+        identity_weak = {"RandomSized": [torch.full((frames,), 4 * q[0]), torch.full((frames,), 4 * q[1])],
+                         "RandomCrop": [torch.zeros(frames), torch.full((frames,), 4.0 * q[0]), torch.zeros(frames),
+                                        torch.full((frames,), 4.0 * q[1])],
+                         "RandomHorizontallyFlip": [False] * frames}
 
-    tail = torch.cuda.Stream(dev)   # the latency-bound end of the prototype stage runs beside the confusion kernel
+    # ---- stages
+    def stage_pl(i, sm_warps=0):
+        return ops.pseudo_label(sets[i % n_sets][0], size=size, thr=c["thr"], keep=c["keep"], ignore_index=c["ignore"],
+                                flags=ops.pl_flags(sm_warps=sm_warps))
 
-    def stage_proto(i, tail_stream=None):
-        logits, feat, _ = sets[i % N_SETS]
-        if ws == 1:
-            return ops.class_means(feat, logits, C, update=(bank.protos, bank.num, bank.mode, bank.start_mean, bank.momentum),
-                                   tail_stream=tail_stream)
-        if gather is not None:                      # slots alternate with i: see sharding.PeerGather
-            means = ops.class_means(feat, logits, C, scatter=gather.targets(i % 2), tail_stream=tail_stream)
-            with torch.cuda.stream(tail_stream if tail_stream is not None else torch.cuda.current_stream(dev)):
-                bank.update_from_peers(gather, i % 2)
-            return means
-        return ops.class_means(feat, logits, C)     # the exchange (bank.update_gathered) follows outside the graph
+    def stage_sums(i, consumer_warps=0):
+        return ops.class_sums(sets[i % n_sets][1], sets[i % n_sets][0], C, consumer_warps=consumer_warps)
 
     def stage_hist(i, pl):
-        ops.confusion_matrix(pl.label.reshape(-1), sets[i % N_SETS][2].reshape(-1), C, meter.hist, meter.bad)
+        ops.confusion_matrix(pl.label.reshape(-1), sets[i % n_sets][2].reshape(-1), C, meter.hist, meter.bad)
 
-    def local_step(i):
-        # pseudo-labels -> segmented sums -> { means + prototype update (+ exchange) on `tail` || confusion matrix }
-        use_tail = not args.no_overlap and (ws == 1 or gather is not None)   # the NCCL form exchanges after the replay
-        pl = stage_pl(i)
-        means = stage_proto(i, tail if use_tail else None)
-        stage_hist(i, pl)
-        if use_tail:
-            torch.cuda.current_stream(dev).wait_stream(tail)
-        return pl, means
+    def stage_tail(i, cs):
+        """means + validity + sequential update; at N > 1 the exchange in between (slots alternate with i)"""
+        if ws == 1:
+            return ops.class_finalize(cs, update=(bank.protos, bank.num, bank.mode, bank.start_mean, bank.momentum))
+        if gather is not None:
+            means = ops.class_finalize(cs, scatter=gather.targets(i % 2))
+            bank.update_from_peers(gather, i % 2)
+            return means
+        return ops.class_finalize(cs)          # NCCL form: bank.update_gathered(means) follows outside the graph
 
-    # One CUDA graph per resident input set: the step's launch sequence is fixed, so the host issues ONE
-    # replay per step (b200seg.graphs).  At N > 1 the prototype exchange follows the replay on the same stream:
-    # one all_gather of this rank's [16,13,256] mean vectors + the sequential update kernel over the gathered
-    # list (sharding.ShardedPrototypes.update_gathered: bit-identical banks on every rank).
-    # Tried and rejected: NCCL inside the captured graph (no gain, process-group teardown hung on this stack);
-    # the exchange on a side stream (its NCCL kernels only get SM slots between our full-machine kernels and
-    # fall behind: 0.40 ms/step against 0.29 serialised).
-    # (one warm-up call per graph: consecutive steps must alternate the gather slot)
-    step_graphs = [GraphedCall(lambda i=i: local_step(i), warmup=1) for i in range(N_SETS)]
-    launches_per_step = step_graphs[0].launches + (1 if ws > 1 and gather is None else 0)
+    def stage_distance(i):
+        logits, feat, soft, hard = sets[i % n_sets]
+        return ops.prototype_distance(feat, bank.protos, temperature=0.5, want_dist=False, want_weight=False, soft=soft,
+                                      hard=hard, train_thred=0.0, ignore_index=c["ignore"])[2]
 
-    def step(i):
-        pl, means = step_graphs[i % N_SETS].replay()
-        if ws > 1 and gather is None:
-            bank.update_gathered(means)
-        return pl
+    def stage_round_tail(i):
+        """cfg4: rectified labels from the 1/8 features (fused sampling), then CE + RCE forward and backward at 1/4"""
+        logits, feat, gt, soft, hard = sets[i % n_sets]
+        q = (c["H"] // 4, c["W"] // 4)
+        lab = ops.prototype_distance_sampled(feat, q, identity_weak, bank.protos, temperature=0.5, soft=soft, hard=hard,
+                                             train_thred=0.0, ignore_index=c["ignore"])[2]
+        x = ops.upsample_bilinear(logits, q).requires_grad_(True)
+        loss = ops.ce_rce(x, lab.reshape(frames, *q), c["ignore"], 0.1, 1.0)[0]
+        g, = torch.autograd.grad(loss, x)
+        return lab, loss, ops.upsample_bilinear_adjoint(g, (c["h"], c["w"]))
+
+    def main_step(i, mode):
+        """everything of step i that the NEXT step's kernels must not overtake; returns what the tail needs"""
+        cur = torch.cuda.current_stream(dev)
+        if kind == "eval_sweep":
+            pred, gt = sets[i % n_sets]
+            ops.confusion_matrix(pred.reshape(-1), gt.reshape(-1), C, meter.hist, meter.bad)
+            return None, None
+        if kind == "proto_distance":
+            cs = stage_sums(i)
+            lab = stage_distance(i)
+            return cs, lab
+        if mode == "coresident":
+            side.wait_stream(cur)
+            with torch.cuda.stream(side):
+                cs = stage_sums(i, 4)
+            pl = stage_pl(i, 12)
+            stage_hist(i, pl)
+            extra = stage_round_tail(i) if kind == "self_train_round" else None
+            cur.wait_stream(side)
+        else:
+            pl = stage_pl(i)
+            cs = stage_sums(i)
+            stage_hist(i, pl)
+            extra = stage_round_tail(i) if kind == "self_train_round" else None
+        return cs, (pl, extra)
+
+    def build_graphs(mode):
+        mains = [GraphedCall(lambda i=i: main_step(i, mode), warmup=1) for i in range(n_sets)]
+        tails = [GraphedCall(lambda i=i: stage_tail(i, mains[i].out[0]), warmup=1) for i in range(n_sets)] if has_proto else None
+        return mains, tails
+
+    ev_main = [torch.cuda.Event() for _ in range(n_sets)]
+    ev_tail = [torch.cuda.Event() for _ in range(n_sets)]
+    state = {"issued": 0}
+
+    def make_step(mains, tails):
+        def step(_i=None):
+            # the set (and with it the gather slot, set % 2) follows ONE running counter, whichever loop calls: consecutive
+            # steps always alternate the slot
+            i = state["issued"]
+            cur = torch.cuda.current_stream(dev)
+            s = i % n_sets
+            if tails is not None and state["issued"] >= n_sets:
+                cur.wait_event(ev_tail[s])              # the tail of step i - n_sets has read this set's sums / records
+            mains[s].replay()
+            if tails is not None:
+                ev_main[s].record(cur)
+                with torch.cuda.stream(tail):
+                    tail.wait_event(ev_main[s])
+                    means = tails[s].replay()
+                    if ws > 1 and gather is None:
+                        bank.update_gathered(means)
+                    ev_tail[s].record(tail)
+            state["issued"] += 1
+        return step
 
     def fence():
-        if ws > 1:
-            bank.join()
+        torch.cuda.current_stream(dev).wait_stream(tail)
         torch.cuda.synchronize()
         if ws > 1:
             dist.barrier()
             torch.cuda.synchronize()
 
+    def time_steps(step, n):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        fence()
+        e0.record()
+        for i in range(n):
+            step(i)
+        torch.cuda.current_stream(dev).wait_stream(tail)
+        e1.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if ws > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item()) / n
+
+    # ---- choose the step form: the co-resident form (pseudo-label on 12 warps/SM + accumulate on 5) against the serial
+    # one, each timed over a few untimed-region replays; every rank takes the same decision (all-reduced times)
+    modes = ["serial"] if kind in ("eval_sweep", "proto_distance") else (["coresident", "serial"] if args.overlap == "auto" else [args.overlap])
+    trial = {}
+    built = {}
+    for m in modes:
+        built[m] = build_graphs(m)
+        st = make_step(*built[m])
+        for i in range(2 * n_sets):      # consecutive steps must alternate the gather slot: always whole rounds of the sets
+            st(i)
+        trial[m] = time_steps(st, 3 * n_sets)
+    mode = min(trial, key=trial.get)
+    for m in list(built):
+        if m != mode:
+            del built[m]
+    mains, tails = built[mode]
+    step = make_step(mains, tails)
+    launches_per_step = mains[0].launches + (tails[0].launches if tails else 0) + (1 if ws > 1 and has_proto and gather is None else 0)
+
+    # ---- in-run parity: one frame of this very step against the oracle, before anything is timed
+    parity = None
+    if rank == 0 and not args.no_parity:
+        out = {}
+        if kind == "eval_sweep":
+            pass
+        elif kind == "proto_distance":
+            out["means"] = ops.class_finalize(stage_sums(0))
+            out["dist_label"], out["protos"] = stage_distance(0), bank.protos.clone()
+        else:
+            out["pl"] = stage_pl(0, 12 if mode == "coresident" else 0)
+            out["means"] = ops.class_finalize(stage_sums(0, 4 if mode == "coresident" else 0))
+        torch.cuda.synchronize()
+        parity = parity_check(c, ops, out, sets[0])
+        if not parity_ok(parity):
+            raise SystemExit("bench.py: the step's outputs do not match the oracle: %s" % json.dumps(parity))
+    if ws > 1:
+        fence()
+
     if ws > 1:
         # setup, not warm-up steps: the first multi-GPU replays also pay for peer mappings, NCCL channel set-up and
-        # rank skew (one first run at N=8 measured 0.87 ms/step against 0.24-0.26 on every later one); settle them
-        for i in range(24):
-            step(i)
+        # rank skew; keep replaying in chunks of 12 steps until two consecutive chunks agree within 10 % on the
+        # slowest rank (the decision is all-reduced: every rank replays the same number of steps), at most 40 chunks
+        prev = None
+        for _ in range(40):
+            cur_t = time_steps(step, 12)
+            if prev is not None and abs(cur_t - prev) <= 0.1 * min(cur_t, prev):
+                break
+            prev = cur_t
         scratch = meter.hist.clone()
         sharding.all_reduce_confusion(scratch, meter.bad.clone())
         fence()
-        # ... and keep replaying in chunks of 12 steps until two consecutive chunks agree within 10 % on the slowest
-        # rank (the decision is all-reduced: every rank replays the same number of steps), at most 40 chunks
-        prev = None
-        for _ in range(40):
-            c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            c0.record()
-            for i in range(12):
-                step(i)
-            c1.record()
-            torch.cuda.synchronize()
-            tchunk = torch.tensor([c0.elapsed_time(c1)], device=dev)
-            dist.all_reduce(tchunk, op=dist.ReduceOp.MAX)
-            cur = float(tchunk.item())
-            if prev is not None and abs(cur - prev) <= 0.1 * min(cur, prev):
-                break
-            prev = cur
-        fence()
-    for i in range(max(args.warmup, 3)):
+    for i in range(((warm + n_sets - 1) // n_sets) * n_sets):
         step(i)
     fence()
 
@@ -349,122 +760,317 @@ def run_b200(args):
     fence()
     t_wall0 = time.perf_counter()
     ev0.record()
-    for i in range(args.steps):
+    for i in range(steps):
         step(i)
-    if ws > 1:
-        bank.join()                 # the timed region ends when the last exchange has landed
+    torch.cuda.current_stream(dev).wait_stream(tail)    # the timed region ends when the last exchange / update has landed
     sharding.all_reduce_confusion(meter.hist, meter.bad)
     ev1.record()
     fence()
     t_wall1 = time.perf_counter()
-    launches = launches_per_step * args.steps
+    launches = launches_per_step * steps
     ms = torch.tensor([ev0.elapsed_time(ev1)], device=dev)
     if ws > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     ms = float(ms.item())
-    miou = dropin.metrics_from_hist(meter.result(), C)[2]
-    bank_spread = 0.0
-    if ws > 1:   # the replicated bank must be bit-identical on every rank (exact gathered update)
-        bank.join()
+    miou = float(dropin.metrics_from_hist(meter.result(), C)[2])
+
+    # ---- N > 1: the replicated bank must be bit-identical on every rank, and equal to what ONE process gets from the
+    # sequential update over all ranks' images in global order (rank 0 gathers two steps' inputs and recomputes)
+    bank_spread, bank_vs_seq = 0.0, None
+    if ws > 1 and has_proto:
         hi, lo = bank.protos.clone(), bank.protos.clone()
         dist.all_reduce(hi, op=dist.ReduceOp.MAX)
         dist.all_reduce(lo, op=dist.ReduceOp.MIN)
         bank_spread = float((hi - lo).abs().max().item())
+        bank.protos.zero_()
+        bank.num.zero_()
+        fence()
+        vsteps, base = 2, state["issued"]
+        for i in range(vsteps):
+            step(i)
+        fence()
+        ref_p, ref_n = torch.zeros_like(bank.protos), torch.zeros_like(bank.num)
+        for i in range(vsteps):
+            lg, ft = sets[(base + i) % n_sets][0], sets[(base + i) % n_sets][1]
+            all_lg = [torch.empty_like(lg) for _ in range(ws)] if rank == 0 else None
+            all_ft = [torch.empty_like(ft) for _ in range(ws)] if rank == 0 else None
+            dist.gather(lg, all_lg, dst=0)
+            dist.gather(ft, all_ft, dst=0)
+            if rank == 0:
+                seq = ops.class_means(torch.cat(all_ft), torch.cat(all_lg), C)
+                ops.prototype_update(ref_p, ref_n, seq, bank.mode, bank.start_mean, bank.momentum, bank.cap)
+                del all_lg, all_ft, seq
+        if rank == 0:
+            bank_vs_seq = float(((bank.protos - ref_p).abs().max() / ref_p.abs().max().clamp_min(1e-30)).item())
+            if not torch.equal(bank.num, ref_n) or bank_vs_seq > 1e-5:
+                raise SystemExit("bench.py: sharded prototype bank differs from the sequential update: rel %.3e" % bank_vs_seq)
+        fence()
 
     # ---- per-stage device time: one graph per (stage, input set), CUDA events around every replay -> roofline
-    pl_graphs = [GraphedCall(lambda i=i: stage_pl(i)) for i in range(N_SETS)]
-    proto_graphs = [GraphedCall(lambda i=i: stage_proto(i), warmup=1) for i in range(N_SETS)]
-    hist_graphs = [GraphedCall(lambda i=i: stage_hist(i, pl_graphs[i].out)) for i in range(N_SETS)]
-    stage_ms = {"pseudo_label": 0.0, "prototype": 0.0, "confusion": 0.0}
-    evs = []
-    fence()
-    for i in range(args.steps):
-        e = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
-        e[0].record()
-        pl_graphs[i % N_SETS].replay()
-        e[1].record()
-        proto_graphs[i % N_SETS].replay()
-        e[2].record()
-        hist_graphs[i % N_SETS].replay()
-        e[3].record()
-        evs.append(e)
-    fence()
-    for e in evs:
-        for j, k in enumerate(stage_ms):
-            stage_ms[k] += e[j].elapsed_time(e[j + 1]) / args.steps
-    if sampler:
-        clocks = sampler.finish(t_wall0, time.perf_counter())
-    del pl_graphs, proto_graphs, hist_graphs
+    stage_ms = {}
+    if kind == "eval_sweep":
+        stage_ms["confusion"] = ms / steps
+    else:
+        stage_defs = []
+        if kind != "proto_distance":
+            plg = [GraphedCall(lambda i=i: stage_pl(i)) for i in range(n_sets)]
+            stage_defs.append(("pseudo_label", plg))
+        prg = [GraphedCall(lambda i=i: ops.class_finalize(stage_sums(i), update=(bank.protos, bank.num, bank.mode, bank.start_mean,
+                                                                                 bank.momentum)), warmup=1) for i in range(n_sets)]
+        stage_defs.append(("prototype", prg))
+        if kind == "proto_distance":
+            stage_defs.append(("distance_rectify", [GraphedCall(lambda i=i: stage_distance(i)) for i in range(n_sets)]))
+        else:
+            stage_defs.append(("confusion", [GraphedCall(lambda i=i: stage_hist(i, plg[i].out)) for i in range(n_sets)]))
+        if kind == "self_train_round":
+            stage_defs.append(("rectify_ce_rce", [GraphedCall(lambda i=i: stage_round_tail(i)) for i in range(n_sets)]))
+        reps = min(steps, 50)
+        fence()
+        evs = []
+        for i in range(reps):
+            e = [torch.cuda.Event(enable_timing=True) for _ in range(len(stage_defs) + 1)]
+            e[0].record()
+            for j, (_, graphs) in enumerate(stage_defs):
+                graphs[i % n_sets].replay()
+                e[j + 1].record()
+            evs.append(e)
+        fence()
+        for j, (name, _) in enumerate(stage_defs):
+            stage_ms[name] = sum(e[j].elapsed_time(e[j + 1]) for e in evs) / reps
+        del stage_defs
+    aux = aux_stages(ops, dev, GraphedCall) if (c is CONFIGS["cfg2"] and rank == 0 and not args.no_aux) else None
+    if ws > 1:
+        fence()
+    clocks = sampler.finish(t_wall0, time.perf_counter()) if sampler else None
 
     # ---- end to end through the drop-in API: pinned host buffers, H2D + D2H inside the timed region
-    e2e = run_e2e(args, dev, rank, ws, dist, dropin, ops, sharding)
+    e2e = run_e2e(args, c, dev, rank, ws, dist, dropin, ops, sharding, steps, gather is not None, numa)
 
     if rank != 0:
         if ws > 1:
             dist.destroy_process_group()
         return
-    px_step = frames * c["H"] * c["W"] * ws
-    alg = algorithmic_bytes()
-    top = max(stage_ms, key=stage_ms.get)
+    unit_px = (c["h"] * c["w"] if kind == "proto_distance" else c["H"] * c["W"])
+    px_step = frames * unit_px * ws
+    alg = algorithmic_bytes(c)
     peak, peak_src = measured_peak_gbs()
-    achieved = alg[top] / (stage_ms[top] * 1e-3) / 1e9
+    top = max(stage_ms, key=stage_ms.get)
+    achieved = alg.get(top, 0) / (stage_ms[top] * 1e-3) / 1e9 if top in alg else None
+    step_bytes = sum(alg.values())
+    roof = {"bound": "xu" if top == "pseudo_label" else "hbm", "kernel": top, "achieved": achieved, "peak": peak, "unit": "GB/s",
+            "frac": (achieved / peak) if achieved else None, "traffic": ncu_traffic(top), "peak_source": peak_src,
+            "algorithmic_bytes_per_launch": alg.get(top),
+            "step": {"algorithmic_bytes": step_bytes, "achieved": step_bytes / (ms / steps * 1e-3) / 1e9,
+                     "frac": step_bytes / (ms / steps * 1e-3) / 1e9 / peak}}
+    if top == "pseudo_label":
+        # MUFU floor of the fused low-resolution form: C ex2 + 1 rcp per pixel at 16 lanes/clk/SM on 148 SMs at the sampled clock
+        mhz = (clocks or {}).get("sm_mhz") or 1965
+        floor_ms = frames * c["H"] * c["W"] * (C + 1) / (148 * 16 * mhz * 1e6) * 1e3
+        roof["xu_floor_ms"] = floor_ms
+        roof["xu_frac"] = floor_ms / stage_ms[top]
+        roof["note"] = ("the dominant stage (fused upsample->softmax->argmax->threshold from LOW-RES logits) is bound by MUFU.EX2 + "
+                        "issue slots, not HBM (`bound: xu`): frac = HBM fraction of its 4 B/px algorithmic traffic, xu_frac = time of "
+                        "C ex2 + 1 rcp per pixel at 16 lanes/clk/SM over measured time; in the timed step it shares the SMs with the "
+                        "HBM-bound accumulate kernel (roofline.step = whole step against HBM)")
     out = {
-        "metric": METRIC, "value": px_step * args.steps / (ms * 1e-3), "unit": UNIT, "n_gpus": ws, "steps": args.steps,
-        "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": workload_name(), "frames_per_gpu_per_step": frames, "logits": [frames, C, c["h"], c["w"]],
-                   "feat": [frames, c["K"], c["h"], c["w"]], "labels": [frames, c["H"], c["W"]],
-                   "l2": "inputs rotate over %d resident sets (780 MB working set > 126 MB L2)" % N_SETS,
-                   "launch": "one CUDA-graph replay per step (b200seg.graphs.GraphedCall), %d kernels per replay%s" % (
-                       launches_per_step, "" if (args.no_overlap or (ws > 1 and gather is None)) else "; the prototype finalize/update(/exchange) node runs beside the confusion node"),
-                   "parallelism": "image-sharded x%d; collectives: prototype means [16,13,256] fp32 per rank and step (%s), "
-                                  "confusion [13,13] int64 once" % (ws, exchange),
-                   "miou": float(miou), "bank_max_spread_over_ranks": bank_spread},
+        "metric": METRIC, "value": px_step * steps / (ms * 1e-3), "unit": UNIT, "n_gpus": ws, "steps": steps,
+        "warmup": warm, "ms_per_step": ms / steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u8" if kind == "eval_sweep" else "f32", "data": data_note,
+        "config": {"workload": workload_name(c), "frames_per_gpu_per_step": frames,
+                   "l2": "inputs rotate over %d resident sets (working set %d MB > 126 MB L2)" % (
+                       n_sets, n_sets * sum(t.numel() * t.element_size() for t in sets[0]) // 2 ** 20),
+                   "launch": "one CUDA-graph replay per step for the kernels (%s form: %s) + one for the prototype tail on its own "
+                             "stream, %d kernels per step" % (mode, {"coresident": "pseudo-label kernel on 12 warps/SM and accumulate "
+                             "kernel on 5 warps/SM resident together, forked capture streams", "serial": "one stream"}[mode],
+                             launches_per_step),
+                   "step_form_trials_ms": {k: round(v, 5) for k, v in trial.items()},
+                   "parallelism": "image-sharded x%d; collectives: prototype means [%d,%d,%s] fp32 per rank and step (%s), "
+                                  "confusion [%d,%d] int64 once" % (ws, frames, C, c.get("K", "-"), exchange, C, C),
+                   "miou": miou, "bank_max_spread_over_ranks": bank_spread, "bank_vs_sequential_rel": bank_vs_seq,
+                   "host_numa": numa},
+        "parity_checked": parity is not None, "parity": parity,
         "stages_ms": {k: round(v, 5) for k, v in stage_ms.items()},
-        "stages_gbs": {k: round(alg[k] / (stage_ms[k] * 1e-3) / 1e9, 1) for k in stage_ms},
-        "roofline": {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": ncu_traffic(top), "peak_source": peak_src,
-                     "algorithmic_bytes_per_launch": alg[top],
-                     "note": ("the dominant stage (fused upsample->softmax->argmax->threshold from LOW-RES logits) is bound by "
-                              "MUFU.EX2 + issue slots, not HBM: 13 ex2 + 1 rcp per pixel at 16 lanes/clk/SM = 59 us floor, "
-                              "ncu XU pipe 58 % / issue 56 % / DRAM 4 % (profiles/r01_ncu_full_summary.txt); the HBM-bound "
-                              "stages are in stages_gbs") if top == "pseudo_label" else ""},
+        "stages_gbs": {k: round(alg[k] / (stage_ms[k] * 1e-3) / 1e9, 1) for k in stage_ms if k in alg},
+        "roofline": roof,
         "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
-        "wall_ms_per_step": 1e3 * (t_wall1 - t_wall0) / args.steps,
+        "wall_ms_per_step": 1e3 * (t_wall1 - t_wall0) / steps,
     }
+    if aux:
+        out["aux_stages"] = aux
     if ws == 1 and not args.no_cpu_baseline:
-        out["cpu_baseline"] = cpu_baseline()
+        out["cpu_baseline"] = cpu_baseline(c)
     print(json.dumps(out))
     if ws > 1:
         dist.destroy_process_group()
 
 
-def run_e2e(args, dev, rank, ws, dist, dropin, ops, sharding):
-    """The same step through the public host-fed API (b200seg.pipeline.HostLabelPipeline): every step's
-    inputs come from pinned HOST memory (H2D inside the timed region), every step's thresholded labels and
-    fp16 confidences go back to pinned host memory (D2H inside the timed region)."""
+def aux_stages(ops, dev, GraphedCall):
+    """Driver-timed numbers for the kernels the cfg2 step does not contain (A7-A12, cfg5's histogram), at their BASELINE
+    shapes: device time between CUDA-graph replays over rotating inputs, algorithmic bytes, fraction of the HBM peak."""
+    peak, _ = measured_peak_gbs()
+    res = {}
+
+    def run(name, fn, sets, alg_bytes, reps=20):
+        graphs = [GraphedCall(lambda s=s: fn(*s)) for s in sets]
+        for i in range(3):
+            graphs[i % len(graphs)].replay()
+        torch.cuda.synchronize()
+        evs = [torch.cuda.Event(enable_timing=True) for _ in range(reps + 1)]
+        evs[0].record()
+        for i in range(reps):
+            graphs[i % len(graphs)].replay()
+            evs[i + 1].record()
+        torch.cuda.synchronize()
+        t = sorted(evs[i].elapsed_time(evs[i + 1]) for i in range(reps))[reps // 2]
+        res[name] = {"ms": round(t, 5), "algorithmic_MB": round(alg_bytes / 1e6, 1), "GBps": round(alg_bytes / (t * 1e-3) / 1e9, 1),
+                     "frac_of_hbm_peak": round(alg_bytes / (t * 1e-3) / 1e9 / peak, 4)}
+
+    g = torch.Generator(device=dev).manual_seed(77)
+    # cfg3: distance -> weights -> rectified labels, 2 and 8 Cityscapes images, K = 2048, C = 19
+    for n in (2, 8):
+        K, C, P = 2048, 19, 129 * 257
+        sets = []
+        for _ in range(2):
+            sets.append((torch.randn(n, K, 129, 257, generator=g, device=dev), torch.randn(C, K, generator=g, device=dev),
+                         torch.softmax(3 * torch.randn(n, C, 129, 257, generator=g, device=dev), 1),
+                         torch.full((n, 1, 129, 257), 255, dtype=torch.uint8, device=dev)))
+        run("distance_rectify_cfg3_k2048_%dimg" % n,
+            lambda f, p, s, h: ops.prototype_distance(f, p, 0.5, want_dist=False, soft=s, hard=h, train_thred=0.0, ignore_index=255),
+            sets, n * P * (4 * K + 4 * C + 1 + 8))
+        del sets
+    # CE + RCE forward / backward, 4 x 13 x 640 x 1920, int64 targets (what the reference passes)
+    n, C, P = 4, 13, 640 * 1920
+    sets = [(torch.randn(n, C, 640, 1920, generator=g, device=dev),
+             torch.randint(0, C, (n, 640, 1920), generator=g, device=dev, dtype=torch.int64)) for _ in range(2)]
+    run("ce_rce_fwd_4x13x640x1920", lambda x, y: ops.ce_rce(x, y, 255, 0.1, 1.0)[0], sets, n * P * (4 * C + 8))
+
+    def fwd_bwd(x, y):
+        xr = x.detach().requires_grad_(True)
+        return torch.autograd.grad(ops.ce_rce(xr, y, 255, 0.1, 1.0)[0], xr)[0]
+    run("ce_rce_fwd_bwd_4x13x640x1920", fwd_bwd, sets, n * P * (4 * C + 8) * 2 + n * P * 4 * C)
+    del sets
+    # cfg5: confusion matrix over 1024 uint8 maps 256 x 512, 19 classes
+    sets = [make_inputs(dev, 88 + s, 1024, CONFIGS["cfg5"]) for s in range(2)]
+    hist = torch.zeros(19, 19, dtype=torch.int64, device=dev)
+    bad = torch.zeros(1, dtype=torch.int64, device=dev)
+    run("confusion_cfg5_1024x256x512_u8", lambda p, t: ops.confusion_matrix(p.reshape(-1), t.reshape(-1), 19, hist, bad), sets,
+        1024 * 256 * 512 * 2)
+    return res
+
+
+def run_e2e(args, c, dev, rank, ws, dist, dropin, ops, sharding, steps, use_peer, numa):
+    """The same step through the public host-fed API: every step's inputs come from pinned HOST memory (H2D inside
+    the timed region), every step's results go back to pinned host memory (D2H inside the timed region).  At N > 1 the
+    step is the FULL step: the prototype exchange runs through sharding.PeerGather on the pipeline's tail stream."""
+    kind = c["kind"]
+    frames, C = c["frames"], c["C"]
+    steps = min(steps, 50)
+    if kind == "eval_sweep":
+        host = [tuple(t.pin_memory() for t in make_inputs("cpu", 4321 + 1000 * rank + s, frames, c)) for s in range(2)]
+        meter = dropin.ConfusionMeter(C, dev)
+        s_in = torch.cuda.Stream(dev)
+        slots = [tuple(torch.empty_like(t, device=dev) for t in host[0]) for _ in range(2)]
+        ready = [torch.cuda.Event() for _ in range(2)]
+        free = [torch.cuda.Event() for _ in range(2)]
+
+        def submit(i):
+            s = i % 2
+            cur = torch.cuda.current_stream(dev)
+            with torch.cuda.stream(s_in):
+                if i >= 2:
+                    s_in.wait_event(free[s])
+                for d, h in zip(slots[s], host[s]):
+                    d.copy_(h, non_blocking=True)
+                ready[s].record(s_in)
+            cur.wait_event(ready[s])
+            meter.add(slots[s][0], slots[s][1])
+            free[s].record(cur)
+
+        for i in range(3):
+            submit(i)
+        torch.cuda.synchronize()
+        if ws > 1:
+            dist.barrier()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record()
+        for i in range(steps):
+            submit(i)
+        sharding.all_reduce_confusion(meter.hist, meter.bad)
+        hist = meter.result()
+        ev1.record()
+        torch.cuda.synchronize()
+        ms = torch.tensor([ev0.elapsed_time(ev1)], device=dev)
+        if ws > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        ms = float(ms.item())
+        return {"value": frames * c["H"] * c["W"] * ws * steps / (ms * 1e-3), "unit": UNIT,
+                "h2d_bytes_per_step": int(sum(t.numel() * t.element_size() for t in host[0])),
+                "d2h_bytes_per_step": int(hist.nbytes // max(steps, 1)), "ms_per_step": ms / steps,
+                "api": "b200seg.dropin.ConfusionMeter.add on double-buffered device slots fed from pinned host label maps"}
+    if kind != "label_step":
+        return {"value": None, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0,
+                "note": "end-to-end arm is reported for the label-step configurations (cfg1, cfg2) and cfg5"}
     from b200seg.pipeline import HostLabelPipeline
 
-    c = CFG
-    frames, C, size = c["frames"], c["C"], (c["H"], c["W"])
+    size = (c["H"], c["W"])
     host = []
     for s in range(2):
-        lg, ft, gt = make_inputs("cpu", 4321 + 1000 * rank + s, frames)
+        lg, ft, gt = make_inputs("cpu", 4321 + 1000 * rank + s, frames, c)
         host.append((lg.pin_memory(), ft.pin_memory(), gt.pin_memory()))
-    # ws > 1: the sharded prototype exchange is exercised by the device arm; here the class means are the traffic
+    bank = gather = None
+    if ws > 1 and use_peer:
+        bank = sharding.ShardedPrototypes(C, c["K"], dev, ops.UPDATE_MEAN, True, 0.9999)
+        gather = sharding.PeerGather(frames, C, c["K"], dev)
     pipe = HostLabelPipeline(dev, C, c["K"], size, thr=c["thr"], keep=c["keep"], ignore_index=c["ignore"],
-                             update_prototypes=(ws == 1))
+                             update_prototypes=True, overlap=True, bank=bank, gather=gather)
+    full_step = ws == 1 or gather is not None   # without peer memory the e2e arm keeps the prototype update rank-local
 
-    for i in range(3):
+    for i in range(4):
         pipe.submit(*host[i % 2])
     pipe.join()
     torch.cuda.synchronize()
     if ws > 1:
         dist.barrier()
+
+    # bare-copy ceiling: the same bytes per step, no kernels -- what the host / PCIe side of this box can deliver to all
+    # ranks at once
+    s_in, s_out = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+    d_in = [torch.empty_like(t, device=dev) for t in host[0]]
+    d_lab = torch.empty((frames,) + size, dtype=torch.uint8, device=dev)
+    d_conf = torch.empty((frames,) + size, dtype=torch.float16, device=dev)
+
+    def bare(n):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        if ws > 1:
+            dist.barrier()
+        e0.record()
+        for i in range(n):
+            with torch.cuda.stream(s_in):
+                for d, h in zip(d_in, host[i % 2]):
+                    d.copy_(h, non_blocking=True)
+            with torch.cuda.stream(s_out):
+                pipe.out_label[i % 2].copy_(d_lab, non_blocking=True)
+                pipe.out_conf[i % 2].copy_(d_conf, non_blocking=True)
+        cur = torch.cuda.current_stream(dev)
+        cur.wait_stream(s_in)
+        cur.wait_stream(s_out)
+        e1.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if ws > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item()) / n
+
+    bare(3)
+    bare_ms = bare(10)
+
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize()
+    if ws > 1:
+        dist.barrier()
     ev0.record()
-    for i in range(args.steps):
+    for i in range(steps):
         pipe.submit(*host[i % 2])
     pipe.join()
     sharding.all_reduce_confusion(pipe.meter.hist, pipe.meter.bad)
@@ -475,28 +1081,39 @@ def run_e2e(args, dev, rank, ws, dist, dropin, ops, sharding):
     if ws > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     ms = float(ms.item())
-    return {"value": frames * c["H"] * c["W"] * ws * args.steps / (ms * 1e-3), "unit": UNIT,
-            "h2d_bytes_per_step": int(pipe.h2d_bytes), "d2h_bytes_per_step": int(pipe.d2h_bytes + hist.nbytes // max(args.steps, 1)),
-            "ms_per_step": ms / args.steps,
-            "api": "b200seg.pipeline.HostLabelPipeline.submit (dropin.pseudo_label_batch + Class_Features.update_from_batch "
-                   "+ ConfusionMeter.add; upload / kernels / download on three streams, two slots)"}
+    h2d = int(pipe.h2d_bytes)
+    return {"value": frames * c["H"] * c["W"] * ws * steps / (ms * 1e-3), "unit": UNIT,
+            "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": int(pipe.d2h_bytes + hist.nbytes // max(steps, 1)),
+            "ms_per_step": ms / steps,
+            "bare_copy_ms_per_step": bare_ms, "frac_of_bare_copy_ceiling": bare_ms / (ms / steps),
+            "h2d_GBps_aggregate": h2d * ws / (ms / steps * 1e-3) / 1e9, "host_numa": numa,
+            "full_step_at_every_n": bool(full_step),
+            "api": "b200seg.pipeline.HostLabelPipeline.submit (pseudo-label kernel beside ops.class_sums, ConfusionMeter.add, "
+                   "ops.class_finalize + prototype update%s on the tail stream; upload / kernels / tail / download on five "
+                   "streams, two slots)" % (" through sharding.PeerGather" if gather is not None else "")}
 
 
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--steps", type=int, default=None)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--config", default="cfg2", choices=sorted(CONFIGS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--no-overlap", action="store_true", help="keep the whole step on one stream (A/B of the tail overlap)")
+    ap.add_argument("--no-parity", action="store_true", help="skip the in-run oracle check of one frame")
+    ap.add_argument("--no-aux", action="store_true", help="skip the aux_stages timings of the default line")
+    ap.add_argument("--overlap", default="auto", choices=["auto", "coresident", "serial"],
+                    help="step form: pseudo-label and accumulate kernels resident together, one after the other, or the faster "
+                         "of the two measured before the timed region (default)")
     ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
                     help="N > 1 prototype exchange: peer-memory stores from the finalize kernel (default) or NCCL all_gather")
     args = ap.parse_args()
+    cfg = CONFIGS[args.config]
     if args.impl == "reference":
-        run_reference(args)
+        run_reference(args, cfg)
     else:
-        run_b200(args)
+        run_b200(args, cfg)
 
 
 if __name__ == "__main__":

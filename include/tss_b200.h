@@ -15,7 +15,9 @@
  *   - work is enqueued on `stream` (a cudaStream_t passed as void*) and returns at once;
  *   - return value: 0 on success, a TSS_E_* code for a rejected argument, or
  *     1000 + cudaError_t for a CUDA failure; tss_last_error_string() explains it
- *     (thread-local).  No C++ exceptions cross this boundary, no global mutable state.
+ *     (thread-local).  No C++ exceptions cross this boundary.  The library keeps no mutable state between
+ *     calls other than that message and an atomic launch counter (tss_launch_count): kernel variants are
+ *     selected per call (`variant` / `flags` / `form` arguments, 0 = automatic), never through globals;
  *   - num_classes is limited to TSS_MAX_CLASSES.
  */
 #ifndef TSS_B200_H_
@@ -46,14 +48,10 @@ extern "C" {
 
 int tss_version(void);
 const char* tss_last_error_string(void);
-/* number of kernels this library has launched in the calling process (bench "gpu_launches") */
+/* number of kernels this library has launched in the calling process (bench "gpu_launches"; atomic) */
 uint64_t tss_launch_count(void);
-/* tuning hooks (benchmarks only): set a kernel variant, return the previous one; -1 = query */
-int tss_tune_confusion_variant(int v);   /* 0 shared-memory atomics, 1 packed private counters (uint8) */
-int tss_tune_pl_force_tile(int v);       /* 1 = use the tiled kernel even when H==h and W==w */
-int tss_tune_distance_variant(int v);    /* 0 = automatic, 1 = 8-warp register-pipeline kernel, 2 / 4 = thread-level-parallel kernel, 2 / 4 px per lane */
-int tss_tune_distance_prefetch(int v);   /* -1 = automatic, 0 / 1 / 2 = register prefetch depth (4-channel groups) of the thread-level-parallel kernel */
-int tss_tune_distance_split(int v);      /* 0 = automatic, else the K split 1 | 2 | 4 | 8 of tss_proto_distance */
+/* sha256 of the sources this library was compiled from (the host mirror refuses a stale library) */
+const char* tss_source_digest(void);
 
 /* ---------------------------------------------------------------------------------------------
  * A14  confusion matrix -- replaces utils/eval_tools.py:4-9 (_fast_hist) and the per-image
@@ -62,9 +60,14 @@ int tss_tune_distance_split(int v);      /* 0 = automatic, else the K split 1 | 
  * counted pixel with pred outside [0, C) makes np.bincount / reshape raise (or silently alias another
  * bin); here such pixels are left out of hist and counted in *bad_keys (uint64, accumulated; may be
  * NULL), and the host mirror raises ValueError when it is non-zero.
- * pred/gt: n elements of `dtype` (TSS_U8 / TSS_I32 / TSS_I64). */
+ * pred/gt: n elements of `dtype` (TSS_U8 / TSS_I32 / TSS_I64).
+ * variant: TSS_HIST_AUTO, or force the warp-private shared-memory atomics kernel (TSS_HIST_ATOMIC) / the packed
+ * per-thread 8-bit counters kernel where it applies (TSS_HIST_PACKED); all give the same matrix. */
+#define TSS_HIST_AUTO 0
+#define TSS_HIST_ATOMIC 1
+#define TSS_HIST_PACKED 2
 int tss_confusion(const void* pred, const void* gt, int dtype, int64_t n, int num_classes,
-                  int64_t* hist, uint64_t* bad_keys, void* stream);
+                  int64_t* hist, uint64_t* bad_keys, int variant, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * A2   low-resolution softmax -- generate_pseudo_label.py:75 (soft branch) and the first softmax
@@ -90,7 +93,13 @@ int tss_softmax_nchw(const float* logits, float* probs, int64_t n_img, int num_c
  * round-to-nearest-even (:94), conf32_out fp32, label_thr_out [N,H,W] uint8 = the threshold block
  * data/freiburg_dataset.py:115-123 applied to (label, fp16 conf): ignore_index where
  * fp16(conf) <= fp16(thr_host[label]) or keep_host[label] == 0.  thr_host / keep_host: HOST arrays of
- * num_classes entries (NULL = no threshold / keep all). */
+ * num_classes entries (NULL = no threshold / keep all).
+ * flags: 0, or TSS_PL_FLAG_FORCE_TILE (use the shared-memory tile kernel even where a faster form applies: A/B
+ * of the kernels) | TSS_PL_FLAG_SM_WARPS(w) (size the one-wave grid of the register-resident kernel for w warps
+ * per SM instead of the whole register file, so that the HBM-bound accumulate kernel of the prototype stage can
+ * run on the same SMs at the same time: tss_proto_accumulate(consumer_warps = 4)). */
+#define TSS_PL_FLAG_FORCE_TILE 1
+#define TSS_PL_FLAG_SM_WARPS(w) (((w) & 0xff) << 8)
 #define TSS_PL_UP_SOFTMAX 0
 #define TSS_PL_UP_ARGMAX 1
 #define TSS_PL_PROB_UP 2
@@ -101,7 +110,7 @@ int tss_softmax_nchw(const float* logits, float* probs, int64_t n_img, int num_c
 int tss_pseudo_label(const float* src, const float* src_flip, int64_t n_img, int num_classes, int h, int w,
                      int H, int W, int mode, int flip, uint8_t* label_out, uint16_t* conf16_out,
                      float* conf32_out, uint8_t* label_thr_out, const float* thr_host,
-                     const uint8_t* keep_host, int ignore_index, void* stream);
+                     const uint8_t* keep_host, int ignore_index, int flags, void* stream);
 
 /* A1   plain bilinear upsample, align_corners=True: self_training.py:62,69-77 (soft labels, feat, out).
  * src [planes, h, w] -> dst [planes, H, W] fp32. */
@@ -135,13 +144,15 @@ int tss_gather_nearest_u8(const uint8_t* src, uint8_t* dst, int64_t planes, int 
  *   process_label :146-151 / :204-209) and gated by conf >= conf_thresh (use_conf_gate != 0,
  *   self_training.py:180-181).  Writes seg_label [N,P] uint8 (class whose sum the pixel joins, 255 =
  *   none) and, in `records` (tss_proto_records_bytes(N, P) bytes, 16-byte aligned), per tile of
- *   TSS_PROTO_TILE pixels: the pixel offsets sorted by class, the class segment boundaries (= the gated
- *   per-class counts, the divisor :128,:140 / :189,:198) and the ungated one-hot counts (the "< 10" rule
- *   :135 / :196).  No atomics, no zero-initialised buffers.  sums_to_zero (may be NULL): sums_elems floats
+ *   TSS_PROTO_TILE pixels: the pixel offsets sorted by class in groups of eight (class segments padded with the
+ *   offset of an always-zero slot), the gated per-class counts (the divisor :128,:140 / :189,:198) and the
+ *   ungated one-hot counts (the "< 10" rule :135 / :196).  No atomics, no zero-initialised buffers.
+ *   sums_to_zero (may be NULL): sums_elems floats
  *   zeroed by the same launch, so that tss_proto_accumulate(zero_sums = 0) can follow without a memset.
  * Step 2, tss_proto_accumulate: feat [N,K,P] fp32 (K % 32 == 0) streamed once through shared memory
  *   (bulk async copies + mbarrier ring); sums [N,C,K] fp32 are zeroed first when zero_sums != 0, then
- *   accumulated.
+ *   accumulated.  consumer_warps: 0 (= 16, the kernel owns the SM) | 4 | 8 | 16 -- with 4 the CTA is 160 threads
+ *   x 96 registers and shares every SM with the pseudo-label kernel (TSS_PL_FLAG_SM_WARPS(12)).
  * Step 3, tss_proto_finalize: count_all / count_gated [N,C] int32 (OUT, summed over the tile records);
  *   vectors [N,C,K] = sums / count_gated; valid [N,C] uint8 = count_gated > 0 && count_all >= min_pixels
  *   (the two `continue`s); vector_sum [N,C] fp32 (for the `vector.sum() == 0` skip of
@@ -150,13 +161,15 @@ int tss_gather_nearest_u8(const uint8_t* src, uint8_t* dst, int64_t planes, int 
  *   update of tss_proto_update below with them (cal_prototype.py:72-75: calculate_mean_vector followed by
  *   the update loop). */
 #define TSS_PROTO_TILE 512
+#define TSS_PROTO_RECORD_BYTES 1776 /* per tile: 768 uint16 offsets, 96 group classes, 2 x 32 counts, group count */
 size_t tss_proto_records_bytes(int64_t n_img, int64_t plane);
 int tss_proto_labels(const float* logits, const float* labels_val, int64_t n_img, int num_classes,
                      int64_t plane, int overflow_channel, int use_conf_gate, float conf_thresh,
                      uint8_t* seg_label, void* records, float* sums_to_zero, int64_t sums_elems,
                      void* stream);
 int tss_proto_accumulate(const float* feat, const void* records, int64_t n_img, int64_t channels,
-                         int64_t plane, int num_classes, float* sums, int zero_sums, void* stream);
+                         int64_t plane, int num_classes, float* sums, int zero_sums, int consumer_warps,
+                         void* stream);
 int tss_proto_finalize(const float* sums, const void* records, int64_t n_img, int num_classes,
                        int64_t channels, int64_t plane, int min_pixels, int32_t* count_all,
                        int32_t* count_gated, float* vectors, uint8_t* valid, float* vector_sum, void* stream);
@@ -207,15 +220,38 @@ int tss_proto_update_partial(const float* vectors, const uint8_t* valid, const f
  * A7/A8/A10  feature-to-prototype distance, soft weights, label rectification -- replaces
  * SelfTrain.feat_prototype_distance (self_training.py:160-165), get_prototype_weight :139-142 and
  * the rectify block :106-112.  feat [N,K,P] fp32 (K % 32 == 0), protos [C,K] fp32.
- *   dist_out   [N,C,P] fp32 or NULL : ||proto_c - feat||_2 (direct difference form, fp32)
+ *   dist_out   [N,C,P] fp32 or NULL : ||proto_c - feat||_2 in fp32 (see `form`)
  *   weight_out [N,C,P] fp32 or NULL : softmax_c(-(d - min_c d) * temperature)
  *   if soft != NULL: rect = weight * soft [N,C,P]; label = argmax_c rect; label = ignore_index where
  *   max_c(rect / sum_c rect) < train_thred; label = hard[px] where hard != NULL and
- *   hard[px] != ignore_index.  hard: [N,P] of hard_dtype; label_out [N,P] int64. */
+ *   hard[px] != ignore_index.  hard: [N,P] of hard_dtype; label_out [N,P] int64.
+ * form: 0 = automatic, else TSS_DIST_FORM(variant, prefetch, split, algo) --
+ *   variant  0 auto | 1 eight-warp register-pipeline kernel | 2 / 4 thread-level-parallel kernel, 2 / 4 px per lane
+ *   prefetch 0 auto | 1 + depth (0, 1, 2 four-channel groups) of the thread-level-parallel kernel
+ *   split    0 auto | K split 1, 2, 4 (8: register-pipeline kernel only)
+ *   algo     0 auto | TSS_DIST_DIRECT: sum (p - f)^2 as torch.norm does | TSS_DIST_EXPANDED: |f|^2 + |p|^2 - 2 f.p
+ *            (half the FP32 work) with every (pixel, class) whose d^2 < 0.5 (|f|^2 + |p|^2) -- the cancellation
+ *            region -- recomputed in the direct form; automatic = expanded for K >= 128. */
+#define TSS_DIST_DIRECT 1
+#define TSS_DIST_EXPANDED 2
+#define TSS_DIST_FORM(variant, prefetch_plus1, split, algo) \
+    (((variant) & 0xf) | (((prefetch_plus1) & 0xf) << 4) | (((split) & 0xf) << 8) | (((algo) & 0xf) << 12))
 int tss_proto_distance(const float* feat, const float* protos, int64_t n_img, int64_t channels,
                        int64_t plane, int num_classes, float temperature, float* dist_out,
                        float* weight_out, const float* soft, const void* hard, int hard_dtype,
-                       float train_thred, int ignore_index, int64_t* label_out, void* stream);
+                       float train_thred, int ignore_index, int64_t* label_out, int form, void* stream);
+
+/* A7-A10 from the network's own 1/8-stride features: the chain self_training.py:69 (bilinear
+ * align_corners=True interpolation of feat8 [N,K,h8,w8] to the quarter map [Hq,Wq]) -> :145-158 (full2weak: per image
+ * resize to (rh, rw), crop at (y0, x0), optional mirror; `params` as in tss_full2weak) -> :160-165, :139-142, :106-112
+ * evaluated per OUTPUT pixel [N, TH*TW] with the two ATen operation sequences reproduced on the fly: neither the
+ * [N,K,Hq,Wq] nor the [N,K,TH,TW] tensor is written.  Outputs / soft / hard / label as in tss_proto_distance
+ * (P = TH*TW); direct-difference form; channels % 4 == 0. */
+int tss_proto_distance_sampled(const float* feat8, const float* protos, int64_t n_img, int64_t channels, int h8,
+                               int w8, int Hq, int Wq, const int32_t* params, int TH, int TW, int num_classes,
+                               float temperature, float* dist_out, float* weight_out, const float* soft,
+                               const void* hard, int hard_dtype, float train_thred, int ignore_index,
+                               int64_t* label_out, void* stream);
 
 /* A9   full2weak -- SelfTrain.full2weak (self_training.py:145-158): per image bilinear
  * (align_corners=True) resize of feat [N,K,h,w] to (rh, rw), crop [y0:y0+TH, x0:x0+TW], optional mirror
@@ -234,10 +270,12 @@ int tss_one_hot_overflow(const float* label, int64_t n_img, int64_t plane, int n
 /* ---------------------------------------------------------------------------------------------
  * A11/A12  cross-entropy with ignore_index and reverse cross-entropy -- nn.CrossEntropyLoss
  * (self_training.py:27,57,114; utils/loss.py:145) and SelfTrain.rce (self_training.py:167-174).
- * logits [N,C,P] fp32, target [N,P] (target_dtype).  out_host-independent: results land in `out`
- * (DEVICE, 4 doubles): {sum_px ce, sum_px rce, valid pixel count, pixels whose label is outside
- * [0, C] and != ignore (the reference raises there)}.  The host mirror forms
- * ce = out[0]/out[2], rce = out[1]/(out[2] + 1e-6).  workspace: tss_loss_workspace_bytes(). */
+ * logits [N,C,P] fp32, target [N,P] (target_dtype).  Results land in `out` (DEVICE, 8 doubles, 5 used):
+ * {sum_px ce, sum_px rce, pixels with a label in [0, C) and != ignore, pixels whose label the reference raises
+ * on (outside [0, C], or == C without rce), pixels labelled exactly C with rce: one_hot(label, C+1)[:, :C]
+ * accepts them, their clamped one-hot row is all 1e-4, so they add -log(1e-4) sum_c clamp(p_c) to the rce sum and
+ * count in its mask, while CrossEntropyLoss has no term for them}.  The host mirror forms
+ * ce = out[0]/out[2], rce = out[1]/(out[2] + out[4] + 1e-6).  workspace: tss_loss_workspace_bytes(). */
 size_t tss_loss_workspace_bytes(void);
 int tss_ce_rce_fwd(const float* logits, const void* target, int target_dtype, int64_t n_img,
                    int num_classes, int64_t plane, int ignore_index, int with_rce, double* out,
@@ -263,7 +301,8 @@ int tss_ce_rce_bwd_mix(const float* logits, const void* target, int target_dtype
                        void* stream);
 
 /* A13  focal loss -- FocalLoss.forward (utils/loss.py:164-184): loss_px = -(1-pt)^gamma * alpha[y] *
- * log pt with pt detached; no ignore handling.  out (DEVICE, 2 doubles) = {sum loss, pixel count}.
+ * log pt with pt detached; no ignore handling.  out (DEVICE, 8 doubles) = {sum loss, pixel count, -, labels
+ * outside [0, C) (the reference's gather raises), -}.
  * alpha: DEVICE [C] fp32 or NULL.  bwd: grad = scale[0] * d(sum loss)/dx. */
 int tss_focal_fwd(const float* logits, const void* target, int target_dtype, int64_t n_img,
                   int num_classes, int64_t plane, float gamma, const float* alpha, double* out,

@@ -31,7 +31,7 @@ __all__ = [
     "resize_nearest_pil_np", "one_hot_with_overflow", "class_mean_vectors", "PrototypeBank",
     "closed_form_update", "full2weak", "prototype_distance", "prototype_weight", "rectify_labels",
     "cross_entropy", "reverse_cross_entropy", "semantic_consistency", "focal_loss", "fast_hist",
-    "evaluate",
+    "evaluate", "self_train_step",
 ]
 
 
@@ -342,6 +342,44 @@ def focal_loss(logits: torch.Tensor, target: torch.Tensor, gamma=0, alpha=None, 
         logpt = logpt * alpha.type_as(x).gather(0, t.view(-1))
     loss = -1 * (1 - pt) ** gamma * logpt
     return loss.mean() if size_average else loss.sum()
+
+
+# --------------------------------------------------------------------------- the whole step
+def self_train_step(net_src_out, net_ema_feat, net_ema_out, net_tgt_out, source_label, full_hw, lp_soft, lp_hard,
+                    weak_params, protos, num, num_classes=13, ignore_index=12, train_thred=0.0, temperature=0.5,
+                    rce_alpha=0.1, rce_beta=1.0, momentum=1e-4, scale_rate=4):
+    """SelfTrain.step (self_training.py:49-134) on RECORDED network outputs (the three forward passes are the
+    caller's): source CE (:51-58), soft-label upsample (:62), EMA maps to the quarter resolution (:66-72), target
+    logits upsample (:75), prototype weights (:82), rectify (:103-112), CE + RCE (:114-118), backward (:58,:120),
+    moving-average prototype update (:123-126).  Returns a dict with the losses, the rectified labels, the
+    gradients left on the raw logits and the bank after the update."""
+    src = net_src_out.detach().clone().requires_grad_(True)
+    tgt = net_tgt_out.detach().clone().requires_grad_(True)
+    H, W = source_label.shape[1], source_label.shape[2]
+    scaled = (int(H / scale_rate), int(W / scale_rate))
+    loss_source = cross_entropy(upsample_bilinear_ac(src, (H, W)), source_label, ignore_index)
+    loss_source.backward()
+    soft_up = upsample_bilinear_ac(lp_soft, scaled)
+    quarter = (int(full_hw[0] / 4), int(full_hw[1] / 4))
+    ema_feat = upsample_bilinear_ac(net_ema_feat, quarter)
+    ema_out = upsample_bilinear_ac(net_ema_out, quarter)
+    tgt_up = upsample_bilinear_ac(tgt, soft_up.shape[2:])
+    weights = prototype_weight(ema_feat, protos, temperature, weak_params)
+    hard = resize_nearest_torch(lp_hard, soft_up.shape[2:])
+    label, _ = rectify_labels(weights, soft_up, hard, train_thred, ignore_index)
+    b, _, hh, ww = soft_up.shape
+    lab = label.reshape(b, hh, ww)
+    loss_target = rce_alpha * cross_entropy(tgt_up, lab, ignore_index) + \
+        rce_beta * reverse_cross_entropy(tgt_up, lab.clone(), num_classes, ignore_index)
+    loss_target.backward()
+    bank = PrototypeBank(num_classes, protos.shape[1], momentum=momentum)
+    bank.vectors, bank.num = protos.clone(), num.clone()
+    vecs, ids = class_mean_vectors(ema_feat, ema_out, num_classes, overflow_channel=ignore_index, use_conf_mask=True)
+    for t, v in zip(ids, vecs):
+        bank.update(t, v, "moving_average", start_mean=False)
+    return {"loss_target": loss_target.detach(), "loss_source": loss_source.detach(), "rectified_label": lab,
+            "weights": weights, "soft_up": soft_up, "target_logits": tgt_up.detach(), "src_out_grad": src.grad,
+            "tgt_out_grad": tgt.grad, "protos_after": bank.vectors, "num_after": bank.num}
 
 
 # --------------------------------------------------------------------------- A14/A15 evaluation

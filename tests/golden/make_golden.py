@@ -154,7 +154,12 @@ class _TinyNet(torch.nn.Module):
 
     def forward(self, x):
         feat = self.f(x)
-        return {"feat": feat, "out": self.o(feat) * 4.0}
+        out = self.o(feat) * 4.0
+        if getattr(self, "record", None) is not None:      # what the label path receives from the network
+            if out.requires_grad:
+                out.retain_grad()
+            self.record.append((feat, out))
+        return {"feat": feat, "out": out}
 
 
 def _st_args(**kw):
@@ -234,6 +239,7 @@ def golden_self_train(ref, out):
             return w_
 
         obj4.get_prototype_weight = spy_w
+        seg.record, ema.record = [], []
         si = gi.step_inputs()
         src_img, src_lab, tgt_img, tgt_full, lp_soft, lp_hard = (torch.from_numpy(si[k]) for k in (
             "src_img", "src_lab", "tgt_img", "tgt_full", "lp_soft", "lp_hard"))
@@ -249,6 +255,17 @@ def golden_self_train(ref, out):
         out["step_%s_soft_up" % tag] = torch.nn.Upsample(size=(16, 32), mode="bilinear", align_corners=True)(lp_soft).numpy()
         out["step_%s_protos_after" % tag] = obj4.objective_vectors.numpy().copy()
         out["step_%s_num_after" % tag] = obj4.objective_vectors_num.numpy().copy()
+        # the network outputs the step consumed (source pass, EMA pass, target pass) and the gradients the two
+        # backward() calls left on the raw logits: a replay net feeds the CUDA path the identical tensors
+        (_, src_out), (_, tgt_out) = seg.record
+        (ema_feat, ema_out), = ema.record
+        out["step_%s_net_src_out" % tag] = src_out.detach().numpy().copy()
+        out["step_%s_net_src_out_grad" % tag] = src_out.grad.numpy().copy()
+        out["step_%s_net_tgt_out" % tag] = tgt_out.detach().numpy().copy()
+        out["step_%s_net_tgt_out_grad" % tag] = tgt_out.grad.numpy().copy()
+        out["step_%s_net_ema_feat" % tag] = ema_feat.detach().numpy().copy()
+        out["step_%s_net_ema_out" % tag] = ema_out.detach().numpy().copy()
+        seg.record = ema.record = None
 
 
 def golden_eval(ref, out):

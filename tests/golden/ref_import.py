@@ -1,9 +1,9 @@
-"""Import the *unmodified* reference from /root/reference on CPU (dev container only).
+"""Import the *unmodified* reference: from /root/reference (dev container) or, on the GPU box, from the
+git-ignored copy ``baseline/_ref/`` that ``__graft_entry__.build()`` stages there.
 
-The reference cannot travel to the GPU box, so this module is used by exactly two
-things: ``make_golden.py`` (which writes the committed ``*.npz`` fixtures) and the
-optional live cross-check in ``tests/test_oracle_vs_reference_live.py`` (skipped
-when /root/reference is absent).  Nothing in the product imports it.
+Used by ``make_golden.py`` (which writes the committed ``*.npz`` fixtures), by the live cross-check
+``tests/test_oracle_vs_reference_live.py``, by ``tests/test_gpu_reference_dropin.py`` (the reference's own modules
+with ``dropin.install()`` applied) and by ``bench.py --impl reference``.  Nothing in the product imports it.
 
 Three runtime shims repair library drift unrelated to the hot-path arithmetic
 (SURVEY.md section 8(c)); no reference file is edited or copied:
@@ -15,7 +15,17 @@ import os
 import sys
 import types
 
-REF_ROOT = os.environ.get("TSS_REFERENCE_ROOT", "/root/reference")
+_REPO = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+
+def _default_root() -> str:
+    for cand in (os.environ.get("TSS_REFERENCE_ROOT"), "/root/reference", os.path.join(_REPO, "baseline", "_ref")):
+        if cand and os.path.isfile(os.path.join(cand, "self_training.py")):
+            return cand
+    return "/root/reference"
+
+
+REF_ROOT = _default_root()
 
 
 def reference_available() -> bool:
@@ -44,7 +54,7 @@ def import_reference():
         sys.path.insert(0, REF_ROOT)
     ns = types.SimpleNamespace()
     import importlib
-    for name in ("utils.eval_tools", "utils.loss", "cal_prototype", "self_training",
-                 "generate_pseudo_label", "data.freiburg_dataset"):
+    for name in ("utils.eval_tools", "utils.loss", "utils", "data", "cal_prototype", "self_training",
+                 "generate_pseudo_label", "data.freiburg_dataset", "segmentation_evaluate"):
         ns.__dict__[name.replace(".", "_")] = importlib.import_module(name)
     return ns

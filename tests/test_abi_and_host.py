@@ -34,21 +34,21 @@ def test_library_exports_every_declared_symbol():
     assert handle.tss_version() == 100
     handle.tss_proto_records_bytes.restype = ctypes.c_size_t
     handle.tss_proto_records_bytes.argtypes = [ctypes.c_int64, ctypes.c_int64]
-    assert handle.tss_proto_records_bytes(2, 1000) == 2 * 2 * (512 * 2 + 128 + 64)
+    assert handle.tss_proto_records_bytes(2, 1000) == 2 * 2 * 1776   # TSS_PROTO_RECORD_BYTES
     assert handle.tss_proto_records_bytes(0, 1000) == 0
 
 
 def test_argument_rejection_needs_no_gpu():
     from b200seg import _lib
     L = _lib.lib()
-    assert L.tss_confusion(None, None, 0, 10, 13, None, None, None) == 1          # TSS_E_ARG: null hist
+    assert L.tss_confusion(None, None, 0, 10, 13, None, None, 0, None) == 1          # TSS_E_ARG: null hist
     assert b"null" in L.tss_last_error_string()
     buf = ctypes.create_string_buffer(64)
     p = ctypes.cast(buf, ctypes.c_void_p)
-    assert L.tss_confusion(p, p, 0, 10, 99, p, None, None) == 2                   # TSS_E_CLASSES
-    assert L.tss_confusion(p, p, 7, 10, 13, p, None, None) == 1                   # bad dtype
-    assert L.tss_proto_accumulate(p, p, 1, 33, 10, 13, p, 1, None) == 1              # channels % 32
-    assert L.tss_confusion(p, p, 0, 0, 13, p, None, None) == 0                    # empty input is a no-op
+    assert L.tss_confusion(p, p, 0, 10, 99, p, None, 0, None) == 2                   # TSS_E_CLASSES
+    assert L.tss_confusion(p, p, 7, 10, 13, p, None, 0, None) == 1                   # bad dtype
+    assert L.tss_proto_accumulate(p, p, 1, 33, 10, 13, p, 1, 0, None) == 1              # channels % 32
+    assert L.tss_confusion(p, p, 0, 0, 13, p, None, 0, None) == 0                    # empty input is a no-op
 
 
 def test_cpu_tensors_are_refused():

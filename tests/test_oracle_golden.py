@@ -140,6 +140,29 @@ def test_step_rectify_and_loss(golden, tag, train_thred):
     assert np.array_equal(loss.numpy(), golden["step_%s_loss_target" % tag])
 
 
+def _weak_params():
+    return {"RandomSized": [torch.tensor(v) for v in gi.WEAK_PARAMS["RandomSized"]],
+            "RandomCrop": [torch.tensor(v) for v in gi.WEAK_PARAMS["RandomCrop"]],
+            "RandomHorizontallyFlip": torch.tensor(gi.WEAK_PARAMS["RandomHorizontallyFlip"])}
+
+
+@pytest.mark.parametrize("tag,train_thred", [("t0", 0), ("t06", 0.6)])
+def test_whole_step_from_recorded_network_outputs(golden, tag, train_thred):
+    """SelfTrain.step() (self_training.py:49-134) restated on the network outputs the reference's step consumed:
+    both losses, the rectified labels, the gradients its two backward() calls left on the raw logits, and the
+    prototype bank after the moving-average update."""
+    si = gi.step_inputs()
+    g = lambda k: T(golden["step_%s_%s" % (tag, k)])
+    out = O.self_train_step(g("net_src_out"), g("net_ema_feat"), g("net_ema_out"), g("net_tgt_out"), T(si["src_lab"]),
+                            si["tgt_full"].shape[2:], T(si["lp_soft"]), T(si["lp_hard"]), _weak_params(),
+                            T(gi.selftrain_protos()), torch.zeros(13), train_thred=train_thred)
+    for k in ("loss_target", "loss_source", "rectified_label", "weights", "soft_up", "target_logits", "protos_after",
+              "num_after"):
+        assert np.array_equal(out[k].numpy(), golden["step_%s_%s" % (tag, k)]), k
+    assert np.array_equal(out["src_out_grad"].numpy(), golden["step_%s_net_src_out_grad" % tag])
+    assert np.array_equal(out["tgt_out_grad"].numpy(), golden["step_%s_net_tgt_out_grad" % tag])
+
+
 @pytest.mark.parametrize("c", [13, 19])
 def test_eval_tools(golden, c):
     pred, gt = gi.hist_inputs(seed=601 + c, c=c)

@@ -18,23 +18,19 @@ _SIGNATURES = {
     # name: (restype, [argtypes])
     "tss_version": (c_int, []),
     "tss_last_error_string": (C.c_char_p, []),
+    "tss_source_digest": (C.c_char_p, []),
     "tss_launch_count": (C.c_uint64, []),
-    "tss_tune_confusion_variant": (c_int, [c_int]),
-    "tss_tune_pl_force_tile": (c_int, [c_int]),
-    "tss_tune_distance_variant": (c_int, [c_int]),
-    "tss_tune_distance_prefetch": (c_int, [c_int]),
-    "tss_tune_distance_split": (c_int, [c_int]),
-    "tss_confusion": (c_int, [c_vp, c_vp, c_int, c_i64, c_int, c_vp, c_vp, c_vp]),
+    "tss_confusion": (c_int, [c_vp, c_vp, c_int, c_i64, c_int, c_vp, c_vp, c_int, c_vp]),
     "tss_softmax_nchw": (c_int, [c_vp, c_vp, c_i64, c_int, c_i64, c_vp]),
     "tss_pseudo_label": (c_int, [c_vp, c_vp, c_i64, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_vp, c_vp,
-                                 c_vp, c_vp, c_vp, c_vp, c_int, c_vp]),
+                                 c_vp, c_vp, c_vp, c_vp, c_int, c_int, c_vp]),
     "tss_upsample_bilinear": (c_int, [c_vp, c_vp, c_i64, c_int, c_int, c_int, c_int, c_vp]),
     "tss_upsample_bilinear_adjoint": (c_int, [c_vp, c_vp, c_i64, c_int, c_int, c_int, c_int, c_vp]),
     "tss_threshold_labels": (c_int, [c_vp, c_vp, c_i64, c_int, c_vp, c_vp, c_int, c_vp, c_vp]),
     "tss_gather_nearest_u8": (c_int, [c_vp, c_vp, c_i64, c_int, c_int, c_int, c_int, c_vp, c_vp, c_vp]),
     "tss_proto_records_bytes": (c_sz, [c_i64, c_i64]),
     "tss_proto_labels": (c_int, [c_vp, c_vp, c_i64, c_int, c_i64, c_int, c_int, c_f32, c_vp, c_vp, c_vp, c_i64, c_vp]),
-    "tss_proto_accumulate": (c_int, [c_vp, c_vp, c_i64, c_i64, c_i64, c_int, c_vp, c_int, c_vp]),
+    "tss_proto_accumulate": (c_int, [c_vp, c_vp, c_i64, c_i64, c_i64, c_int, c_vp, c_int, c_int, c_vp]),
     "tss_proto_finalize": (c_int, [c_vp, c_vp, c_i64, c_int, c_i64, c_i64, c_int, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "tss_proto_finalize_scatter": (c_int, [c_vp, c_vp, c_i64, c_int, c_i64, c_i64, c_int, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_int, c_vp]),
     "tss_proto_finalize_update": (c_int, [c_vp, c_vp, c_i64, c_int, c_i64, c_i64, c_int, c_vp, c_vp, c_vp, c_vp, c_vp,
@@ -43,7 +39,9 @@ _SIGNATURES = {
     "tss_proto_update_partial": (c_int, [c_vp, c_vp, c_vp, c_i64, c_int, c_i64, c_int, c_int, c_f64, c_f64, c_vp,
                                          c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "tss_proto_distance": (c_int, [c_vp, c_vp, c_i64, c_i64, c_i64, c_int, c_f32, c_vp, c_vp, c_vp, c_vp, c_int,
-                                   c_f32, c_int, c_vp, c_vp]),
+                                   c_f32, c_int, c_vp, c_int, c_vp]),
+    "tss_proto_distance_sampled": (c_int, [c_vp, c_vp, c_i64, c_i64, c_int, c_int, c_int, c_int, c_vp, c_int, c_int, c_int,
+                                           c_f32, c_vp, c_vp, c_vp, c_vp, c_int, c_f32, c_int, c_vp, c_vp]),
     "tss_full2weak": (c_int, [c_vp, c_i64, c_i64, c_int, c_int, c_vp, c_int, c_int, c_vp, c_vp]),
     "tss_one_hot_overflow": (c_int, [c_vp, c_i64, c_i64, c_int, c_int, c_vp, c_vp]),
     "tss_loss_workspace_bytes": (c_sz, []),
@@ -65,12 +63,15 @@ def library_path() -> str:
 
 
 def lib() -> C.CDLL:
-    """The loaded library (built on first use when nvcc is available; otherwise an error)."""
+    """The loaded library.  It is (re)built with nvcc when it is missing or was compiled from other sources than
+    the ones in csrc/ (the source digest is compiled into the library); without nvcc a stale or missing library
+    is an error -- kernels never run against old code silently, and there is no other code path to fall back to."""
     global _lib
     if _lib is None:
-        path = _build.LIB_PATH
-        if not os.path.exists(path):
-            path = _build.build()
+        try:
+            path = _build.ensure_current()
+        except RuntimeError as e:
+            raise TssError("libtss_b200.so is missing or stale and cannot be rebuilt: %s" % e) from e
         handle = C.CDLL(path)
         for name, (res, args) in _SIGNATURES.items():
             fn = getattr(handle, name)  # AttributeError if the .so does not export what the header declares

@@ -32,4 +32,11 @@ const char* tss_last_error_string(void) { return tss::g_err; }
 
 uint64_t tss_launch_count(void) { return tss::g_launches.load(std::memory_order_relaxed); }
 
+#ifndef TSS_SOURCE_DIGEST
+#define TSS_SOURCE_DIGEST ""
+#endif
+// the marker lets the host mirror read the digest from the FILE (a dlopen of a stale library would pin it in the process)
+static const char kSourceDigest[] = "TSS_SOURCE_DIGEST=" TSS_SOURCE_DIGEST;
+const char* tss_source_digest(void) { return kSourceDigest + 18; }
+
 }  // extern "C"

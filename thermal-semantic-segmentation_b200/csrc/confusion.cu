@@ -190,24 +190,17 @@ confusion_packed(const T* __restrict__ pred, const T* __restrict__ gt, int64_t n
     if (bad != nullptr && nbad) atomicAdd(bad, nbad);
 }
 
-static int g_hist_variant = 1;  // 0 = shared atomics only, 1 = packed private counters for uint8
-
 }  // namespace tss
 
-extern "C" int tss_tune_confusion_variant(int v) {
-    int old = tss::g_hist_variant;
-    if (v >= 0) tss::g_hist_variant = v;
-    return old;
-}
-
 extern "C" int tss_confusion(const void* pred, const void* gt, int dtype, int64_t n, int num_classes,
-                             int64_t* hist, uint64_t* bad_keys, void* stream) {
+                             int64_t* hist, uint64_t* bad_keys, int variant, void* stream) {
     using namespace tss;
     TSS_REQUIRE(hist != nullptr && n >= 0, TSS_E_ARG, "tss_confusion: null hist or negative n");
     TSS_REQUIRE(n == 0 || (pred != nullptr && gt != nullptr), TSS_E_ARG, "tss_confusion: null input");
     TSS_REQUIRE(num_classes >= 1 && num_classes <= TSS_MAX_CLASSES, TSS_E_CLASSES,
                 "tss_confusion: num_classes %d outside [1, %d]", num_classes, TSS_MAX_CLASSES);
     TSS_REQUIRE(dtype == TSS_U8 || dtype == TSS_I32 || dtype == TSS_I64, TSS_E_ARG, "tss_confusion: bad dtype %d", dtype);
+    TSS_REQUIRE(variant >= TSS_HIST_AUTO && variant <= TSS_HIST_PACKED, TSS_E_ARG, "tss_confusion: bad variant %d", variant);
     if (n == 0) return TSS_OK;
     cudaStream_t st = as_stream(stream);
     auto* h = reinterpret_cast<unsigned long long*>(hist);
@@ -220,7 +213,7 @@ extern "C" int tss_confusion(const void* pred, const void* gt, int dtype, int64_
         return static_cast<int>(need < cap ? (need < 1 ? 1 : need) : cap);
     };
     int64_t done = 0;
-    if (g_hist_variant == 1 && n >= 16 * 32 * kPackedIters &&
+    if (variant != TSS_HIST_ATOMIC && n >= 16 * 32 * kPackedIters &&
         (reinterpret_cast<uintptr_t>(pred) & 15) == 0 && (reinterpret_cast<uintptr_t>(gt) & 15) == 0) {
         const int CP = C + 1, bins = CP * CP, words = (bins + 3) / 4;
         const size_t sh = (static_cast<size_t>((bins + 31) & ~31) + static_cast<size_t>(kPackedWarps) * words * 32) * 4;

@@ -247,7 +247,35 @@ struct TlpCfg {
     static constexpr int kThreads = kWarps * 32;
 };
 
-template <int CT, int PX, int PF>
+// EXP (expanded form): the loop accumulates f.p (ONE packed FMA per pixel pair, channel and class instead of a
+// subtract + FMA) and |f|^2 once per pixel; d^2 = |f|^2 + |p|^2 - 2 f.p.  The expansion cancels when a feature
+// lies near a prototype, so every (pixel, class) whose d^2 comes out below kExpTheta (|f|^2 + |p|^2) is
+// recomputed in the reference's direct-difference form by the whole warp (exact_d2_pixel): the fp32
+// accumulation error of the three sums (about 1e-6 relative to |f|^2 + |p|^2, measured; 4e-6 at four sigma) then
+// stays below 1e-5 relative to d^2 everywhere else.
+constexpr float kExpTheta = 0.5f;
+
+template <int CT>
+__device__ __noinline__ void exact_d2_pixel(const DistArgs& a, int64_t n, int64_t p, unsigned mask, float (&out)[CT]) {
+    const int lane = threadIdx.x & 31;
+    float s[CT];
+#pragma unroll
+    for (int c = 0; c < CT; ++c) s[c] = 0.f;
+    const float* f = a.feat + n * a.K * a.P + p;
+    for (int64_t k = lane; k < a.K; k += 32) {   // lane = channel (mod 32): 32 rows of the pixel per step
+        const float x = __ldg(f + k * a.P);
+#pragma unroll
+        for (int c = 0; c < CT; ++c)
+            if ((mask >> c) & 1u) {
+                const float d = __fsub_rn(__ldg(a.protos + c * a.K + k), x);
+                s[c] = fmaf(d, d, s[c]);
+            }
+    }
+#pragma unroll
+    for (int c = 0; c < CT; ++c) out[c] = ((mask >> c) & 1u) ? warp_sum(s[c]) : 0.f;
+}
+
+template <int CT, int PX, int PF, bool EXP>
 __global__ void __launch_bounds__(TlpCfg<CT, PX, PF>::kThreads, 1) distance_tlp_kernel(const DistArgs a, int64_t units, int SI) {
     constexpr int W = TlpCfg<CT, PX, PF>::kWarps;
     constexpr int PP = PX / 2;
@@ -262,6 +290,19 @@ __global__ void __launch_bounds__(TlpCfg<CT, PX, PF>::kThreads, 1) distance_tlp_
     for (int i = tid; i < CT * K; i += TlpCfg<CT, PX, PF>::kThreads) {
         const int c = i / K, k = i - c * K;
         ps[c * PS + k + 4 * (k / KW)] = (c < a.C) ? a.protos[i] : 0.f;
+    }
+    float* pn = ps + CT * PS;   // [CT] |p_c|^2 (EXP), summed in fp64
+    if (EXP) {
+        for (int c = warp; c < CT; c += W) {
+            double sq = 0.0;
+            if (c < a.C)
+                for (int k = lane; k < K; k += 32) {
+                    const double v = static_cast<double>(a.protos[c * K + k]);
+                    sq += v * v;
+                }
+            sq = warp_sum_d(sq);
+            if (lane == 0) pn[c] = static_cast<float>(sq);
+        }
     }
     __syncthreads();
 
@@ -285,6 +326,9 @@ __global__ void __launch_bounds__(TlpCfg<CT, PX, PF>::kThreads, 1) distance_tlp_
         for (int c = 0; c < CT; ++c)
 #pragma unroll
             for (int h = 0; h < PP; ++h) acc[c][h] = 0ull;
+        f32x2 nrm[2][PP];   // EXP: |f|^2 in two interleaved chains per pixel pair
+#pragma unroll
+        for (int h = 0; h < PP; ++h) { nrm[0][h] = 0ull; nrm[1][h] = 0ull; }
 
         // PF = prefetch depth in 4-channel groups (0: loads of a group are issued when it is used)
         constexpr int DS = PF > 0 ? PF : 1;
@@ -336,6 +380,12 @@ __global__ void __launch_bounds__(TlpCfg<CT, PX, PF>::kThreads, 1) distance_tlp_
             for (int q = 0; q < 4; ++q)
 #pragma unroll
                 for (int h = 0; h < PP; ++h) xp[q][h] = pack2(x[q][2 * h], x[q][2 * h + 1]);
+            if (EXP) {
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+#pragma unroll
+                    for (int h = 0; h < PP; ++h) nrm[q & 1][h] = fma2(xp[q][h], xp[q][h], nrm[q & 1][h]);
+            }
 #pragma unroll
             for (int c = 0; c < CT; ++c) {
                 const float4 pr = *reinterpret_cast<const float4*>(pk + c * PS + kk);
@@ -345,31 +395,97 @@ __global__ void __launch_bounds__(TlpCfg<CT, PX, PF>::kThreads, 1) distance_tlp_
                     const f32x2 pb = pack2(pv[q], pv[q]);
 #pragma unroll
                     for (int h = 0; h < PP; ++h) {
-                        const f32x2 df = sub2(pb, xp[q][h]);
-                        acc[c][h] = fma2(df, df, acc[c][h]);
+                        if (EXP) {
+                            acc[c][h] = fma2(pb, xp[q][h], acc[c][h]);
+                        } else {
+                            const f32x2 df = sub2(pb, xp[q][h]);
+                            acc[c][h] = fma2(df, df, acc[c][h]);
+                        }
                     }
                 }
             }
           }
+        }
+        if (EXP) {
+#pragma unroll
+            for (int h = 0; h < PP; ++h) nrm[0][h] = add2(nrm[0][h], nrm[1][h]);
         }
         for (int o = 16; o >= L; o >>= 1) {  // partial sums of the SI parts (no iteration when SI == 1)
 #pragma unroll
             for (int c = 0; c < CT; ++c)
 #pragma unroll
                 for (int h = 0; h < PP; ++h) acc[c][h] = add2(acc[c][h], __shfl_xor_sync(0xffffffffu, acc[c][h], o));
-        }
+            if (EXP) {
 #pragma unroll
-        for (int i = 0; i < PX; ++i) {   // pixel i of the unit is finished by part i mod SI
-            const int64_t p = base + i * L;
-            if ((i & (SI - 1)) == part && p < P) {
-                float d[CT];
+                for (int h = 0; h < PP; ++h) nrm[0][h] = add2(nrm[0][h], __shfl_xor_sync(0xffffffffu, nrm[0][h], o));
+            }
+        }
+        if (!EXP) {
+#pragma unroll
+            for (int i = 0; i < PX; ++i) {   // pixel i of the unit is finished by part i mod SI
+                const int64_t p = base + i * L;
+                if ((i & (SI - 1)) == part && p < P) {
+                    float d[CT];
+#pragma unroll
+                    for (int c = 0; c < CT; ++c) {
+                        float lo, hi;
+                        unpack2(acc[c][i >> 1], lo, hi);
+                        d[c] = sqrtf((i & 1) ? hi : lo);
+                    }
+                    distance_epilogue<CT>(a, d, n, p);
+                }
+            }
+        } else {
+            // d^2 = |f|^2 + |p|^2 - 2 f.p per finishing pixel; pairs inside the cancellation region are flagged
+            float d2[PX][CT];
+            unsigned fl[PX];
+            unsigned any = 0;
+#pragma unroll
+            for (int i = 0; i < PX; ++i) {
+                const int64_t p = base + i * L;
+                const bool mine = (i & (SI - 1)) == part && p < P;
+                float flo, fhi;
+                unpack2(nrm[0][i >> 1], flo, fhi);
+                const float F = (i & 1) ? fhi : flo;
+                fl[i] = 0;
 #pragma unroll
                 for (int c = 0; c < CT; ++c) {
                     float lo, hi;
                     unpack2(acc[c][i >> 1], lo, hi);
-                    d[c] = sqrtf((i & 1) ? hi : lo);
+                    const float scale = F + pn[c];
+                    d2[i][c] = fmaf(-2.0f, (i & 1) ? hi : lo, scale);
+                    if (mine && c < a.C && d2[i][c] < kExpTheta * scale) fl[i] |= 1u << c;
                 }
-                distance_epilogue<CT>(a, d, n, p);
+                any |= fl[i];
+            }
+            if (__any_sync(0xffffffffu, any != 0)) {   // rare: the warp recomputes the flagged pairs exactly
+#pragma unroll
+                for (int i = 0; i < PX; ++i) {
+                    unsigned pend = __ballot_sync(0xffffffffu, fl[i] != 0);
+                    while (pend) {
+                        const int src = __ffs(pend) - 1;
+                        pend &= pend - 1;
+                        const unsigned m = __shfl_sync(0xffffffffu, fl[i], src);
+                        const int pp = __shfl_sync(0xffffffffu, static_cast<int>(base + i * L), src);
+                        float ex[CT];
+                        exact_d2_pixel<CT>(a, n, pp, m, ex);
+                        if (lane == src) {
+#pragma unroll
+                            for (int c = 0; c < CT; ++c)
+                                if ((m >> c) & 1u) d2[i][c] = ex[c];
+                        }
+                    }
+                }
+            }
+#pragma unroll
+            for (int i = 0; i < PX; ++i) {
+                const int64_t p = base + i * L;
+                if ((i & (SI - 1)) == part && p < P) {
+                    float d[CT];
+#pragma unroll
+                    for (int c = 0; c < CT; ++c) d[c] = sqrtf(fmaxf(d2[i][c], 0.f));
+                    distance_epilogue<CT>(a, d, n, p);
+                }
             }
         }
     }
@@ -391,41 +507,60 @@ static double tlp_cost(const DistArgs& a, int SI) {
     return rounds * (static_cast<double>(a.K) / SI + 16.0) * (W * PX * 32) * f;
 }
 
-template <int CT, int PX, int PF>
+template <int CT, int PX, int PF, bool EXP>
 static int launch_distance_tlp(DistArgs& a, int SI, cudaStream_t st) {
     constexpr int W = TlpCfg<CT, PX, PF>::kWarps;
-    const size_t smem = sizeof(float) * CT * static_cast<size_t>(a.K + 4 * SI);
+    const size_t smem = sizeof(float) * (CT * static_cast<size_t>(a.K + 4 * SI) + CT);
     const int unit_px = PX * 32 / SI;
     const int64_t units = a.N * ((a.P + unit_px - 1) / unit_px);
-    cudaError_t e = cudaFuncSetAttribute(distance_tlp_kernel<CT, PX, PF>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+    cudaError_t e = cudaFuncSetAttribute(distance_tlp_kernel<CT, PX, PF, EXP>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
     if (e != cudaSuccess) return cuda_status(e, "tss_proto_distance: smem attribute");
     const int64_t ctas = (units + W - 1) / W;
     const unsigned grid = static_cast<unsigned>(ctas < kNumSMs ? ctas : kNumSMs);
-    distance_tlp_kernel<CT, PX, PF><<<grid, TlpCfg<CT, PX, PF>::kThreads, smem, st>>>(a, units, SI);
+    distance_tlp_kernel<CT, PX, PF, EXP><<<grid, TlpCfg<CT, PX, PF>::kThreads, smem, st>>>(a, units, SI);
     TSS_LAUNCH_CHECK("tss_proto_distance(tlp)");
     return TSS_OK;
 }
 
-// tuning hooks: form 0 = automatic, 1 = 8-warp register-pipeline kernel, 2 / 4 = thread-level-parallel kernel with
-// 2 / 4 pixels per lane; split 0 = automatic, else the K split
-static int g_dist_variant = 0;
-static int g_dist_prefetch = -1;   // -1 = automatic, 0 / 1 / 2 = register prefetch depth in 4-channel groups
-int g_dist_split_value();
+// `form` of tss_proto_distance (0 = everything automatic), see include/tss_b200.h
+struct DistForm {
+    int variant;    // 0 automatic, 1 = 8-warp register-pipeline kernel, 2 / 4 = thread-level-parallel kernel with 2 / 4 px per lane
+    int prefetch;   // -1 automatic, 0 / 1 / 2 = register prefetch depth in 4-channel groups
+    int split;      // 0 automatic, else the K split
+    int algo;       // 0 automatic, 1 direct difference, 2 expanded with exact recomputation
+};
+static DistForm decode_form(int form) {
+    DistForm f;
+    f.variant = form & 0xf;
+    f.prefetch = ((form >> 4) & 0xf) - 1;
+    f.split = (form >> 8) & 0xf;
+    f.algo = (form >> 12) & 0xf;
+    return f;
+}
+
+template <int CT, bool EXP>
+static int launch_distance_tlp_form(DistArgs& a, int px, int pf, int si, cudaStream_t st) {
+    if (px == 2) {
+        if (pf == 0) return launch_distance_tlp<CT, 2, 0, EXP>(a, si, st);
+        if (pf == 1) return launch_distance_tlp<CT, 2, 1, EXP>(a, si, st);
+        return launch_distance_tlp<CT, 2, 2, EXP>(a, si, st);
+    }
+    return pf ? launch_distance_tlp<CT, 4, 1, EXP>(a, si, st) : launch_distance_tlp<CT, 4, 0, EXP>(a, si, st);
+}
 
 // returns TSS_OK after a launch, or -1 when the thread-level-parallel form does not apply
 template <int CT>
-static int launch_distance_auto(DistArgs& a, cudaStream_t st) {
-    if (g_dist_variant == 1) return -1;
-    if (sizeof(float) * CT * static_cast<size_t>(a.K + 16) > 226 * 1024) return -1;   // prototypes must be resident
-    const int forced = g_dist_split_value();
+static int launch_distance_auto(DistArgs& a, const DistForm& fm, cudaStream_t st) {
+    if (fm.variant == 1) return -1;
+    if (sizeof(float) * (CT * static_cast<size_t>(a.K + 16) + CT) > 226 * 1024) return -1;   // prototypes must be resident
     int best_px = 2, best_si = 1, best_pf = 0;
     double best = 1e300;
     for (int px = 2; px <= 4; px += 2) {
-        if (g_dist_variant != 0 && g_dist_variant != px) continue;
+        if (fm.variant != 0 && fm.variant != px) continue;
         for (int pf = 0; pf <= (px == 2 ? 2 : 1); ++pf) {   // depth 2 only with 2 px per lane (registers)
-            if (g_dist_prefetch >= 0 && g_dist_prefetch != pf) continue;
+            if (fm.prefetch >= 0 && fm.prefetch != pf) continue;
             for (int si = 1; si <= 4; si *= 2) {
-                if (forced != 0 && forced != si) continue;
+                if (fm.split != 0 && fm.split != si) continue;
                 double c;
                 if (px == 2) c = pf == 0 ? tlp_cost<CT, 2, 0>(a, si) : pf == 1 ? tlp_cost<CT, 2, 1>(a, si) : tlp_cost<CT, 2, 2>(a, si);
                 else c = pf == 0 ? tlp_cost<CT, 4, 0>(a, si) : tlp_cost<CT, 4, 1>(a, si);
@@ -434,21 +569,17 @@ static int launch_distance_auto(DistArgs& a, cudaStream_t st) {
         }
     }
     if (best == 1e300) return -1;   // forced split 8 / unsupported combination: the register-pipeline kernel
-    if (best_px == 2) {
-        if (best_pf == 0) return launch_distance_tlp<CT, 2, 0>(a, best_si, st);
-        if (best_pf == 1) return launch_distance_tlp<CT, 2, 1>(a, best_si, st);
-        return launch_distance_tlp<CT, 2, 2>(a, best_si, st);
-    }
-    return best_pf ? launch_distance_tlp<CT, 4, 1>(a, best_si, st) : launch_distance_tlp<CT, 4, 0>(a, best_si, st);
+    // expanded form: half the FP32 work; worth it once the K loop dominates the per-unit overhead
+    const bool expanded = fm.algo == 2 || (fm.algo == 0 && a.K >= 128);
+    return expanded ? launch_distance_tlp_form<CT, true>(a, best_px, best_pf, best_si, st)
+                    : launch_distance_tlp_form<CT, false>(a, best_px, best_pf, best_si, st);
 }
 
-static int g_dist_split = 0;  // tuning hook: 0 = automatic
-int g_dist_split_value() { return g_dist_split; }
-
 template <int CT>
-static int launch_distance(DistArgs& a, cudaStream_t st) {
+static int launch_distance(DistArgs& a, int form, cudaStream_t st) {
+    const DistForm fm = decode_form(form);
     {
-        const int r = launch_distance_auto<CT>(a, st);
+        const int r = launch_distance_auto<CT>(a, fm, st);
         if (r != -1) return r;
     }
     // whole prototype matrix resident when it fits; else the largest K chunk 32*g (g | K/32, g <= 16)
@@ -470,7 +601,7 @@ static int launch_distance(DistArgs& a, cudaStream_t st) {
     const int64_t groups = a.N * ((a.P + kDWarpPx - 1) / kDWarpPx);
     int S = 1;
     while (S < 8 && groups * S < 6ll * kNumSMs * kDWarps) S *= 2;
-    if (g_dist_split > 0) S = g_dist_split;
+    if (fm.split > 0) S = fm.split;
     const int tile_px = kDWarpPx * (kDWarps / S);
     const int64_t tiles = a.N * ((a.P + tile_px - 1) / tile_px);
     const unsigned grid = static_cast<unsigned>(tiles < kNumSMs ? tiles : kNumSMs);
@@ -479,33 +610,169 @@ static int launch_distance(DistArgs& a, cudaStream_t st) {
     return TSS_OK;
 }
 
+// ------------------------------------------------------------------------------------------------
+// Distance / weights / rectified labels straight from the network's 1/8-stride features: the
+// reference first interpolates feat to a quarter of the full image (self_training.py:69), then full2weak resizes
+// that map per image, crops and mirrors it (:145-158), and only then takes distances -- two materialised
+// K-channel tensors.  Here a thread owns one output pixel and evaluates BOTH bilinear stages on the fly, per
+// channel, with the same fp32 operation sequence as the two ATen calls (stage 1: four quarter-map values from four
+// source taps each; stage 2: the resized value from those four), then accumulates the direct-difference distances
+// to the C prototypes in shared memory.  HBM traffic: the 1/8-stride features once (4 K bytes per SOURCE pixel; the
+// 16 taps of a pixel hit L1/L2) + soft / hard / label per output pixel.
+struct SampleArgs {
+    const int32_t* params;   // [N,6] {rh, rw, y0, x0, flip, 0}
+    int h8, w8, Hq, Wq, TH, TW;
+};
+
+__device__ __forceinline__ void axis_tap(float scale, int dst, int n_in, int& i0, int& i1, float& l0, float& l1) {
+    const float s = __fmul_rn(scale, static_cast<float>(dst));   // ATen: src = scale * dst, all fp32
+    i0 = min(static_cast<int>(s), n_in - 1);
+    i1 = i0 + (i0 < n_in - 1 ? 1 : 0);
+    l1 = __fsub_rn(s, static_cast<float>(i0));
+    l0 = __fsub_rn(1.0f, l1);
+}
+__device__ __forceinline__ float axis_scale(int n_in, int n_out) {
+    return n_out > 1 ? static_cast<float>(n_in - 1) / static_cast<float>(n_out - 1) : 0.f;
+}
+
+constexpr int kSampThreads = 128;
+
+template <int CT>
+__global__ void __launch_bounds__(kSampThreads) distance_sampled_kernel(const DistArgs a, const SampleArgs sp) {
+    extern __shared__ __align__(16) float ps[];   // [CT][K + 4]
+    const int K = static_cast<int>(a.K), PS = K + 4;
+    for (int i = threadIdx.x; i < CT * K; i += kSampThreads) {
+        const int c = i / K, k = i - c * K;
+        ps[c * PS + k] = (c < a.C) ? a.protos[i] : 0.f;
+    }
+    __syncthreads();
+    const int64_t n = blockIdx.y;
+    const int p = blockIdx.x * kSampThreads + threadIdx.x;
+    if (p >= sp.TH * sp.TW) return;
+    const int y = p / sp.TW, x = p - y * sp.TW;
+    const int rh = sp.params[n * 6 + 0], rw = sp.params[n * 6 + 1], y0 = sp.params[n * 6 + 2], x0 = sp.params[n * 6 + 3];
+    const int flip = sp.params[n * 6 + 4];
+    // stage 2 (full2weak): taps of the resized-and-cropped pixel in the quarter map
+    int Y[2], X[2];
+    float ly0, ly1, lx0, lx1;
+    axis_tap(axis_scale(sp.Hq, rh), y0 + y, sp.Hq, Y[0], Y[1], ly0, ly1);
+    axis_tap(axis_scale(sp.Wq, rw), x0 + (flip ? sp.TW - 1 - x : x), sp.Wq, X[0], X[1], lx0, lx1);
+    // stage 1 (1/8 -> 1/4 interpolation): taps of those quarter-map points in the source map
+    const float s1y = axis_scale(sp.h8, sp.Hq), s1x = axis_scale(sp.w8, sp.Wq);
+    int off[2][2][2][2];   // [quarter row a][source row r][quarter col b][source col s]
+    float my0[2], my1[2], mx0[2], mx1[2];
+    {
+        int iy[2][2], jx[2][2];
+#pragma unroll
+        for (int t = 0; t < 2; ++t) {
+            axis_tap(s1y, Y[t], sp.h8, iy[t][0], iy[t][1], my0[t], my1[t]);
+            axis_tap(s1x, X[t], sp.w8, jx[t][0], jx[t][1], mx0[t], mx1[t]);
+        }
+#pragma unroll
+        for (int t = 0; t < 2; ++t)
+#pragma unroll
+            for (int r = 0; r < 2; ++r)
+#pragma unroll
+                for (int b = 0; b < 2; ++b)
+#pragma unroll
+                    for (int q = 0; q < 2; ++q) off[t][r][b][q] = iy[t][r] * sp.w8 + jx[b][q];
+    }
+    const int64_t plane8 = static_cast<int64_t>(sp.h8) * sp.w8;
+    const float* f = a.feat + n * a.K * plane8;
+    float acc[CT];
+#pragma unroll
+    for (int c = 0; c < CT; ++c) acc[c] = 0.f;
+    for (int k0 = 0; k0 < K; k0 += 4) {
+        float v[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const float* ch = f + (k0 + q) * plane8;
+            float Q[2][2];
+#pragma unroll
+            for (int t = 0; t < 2; ++t)
+#pragma unroll
+                for (int b = 0; b < 2; ++b) {
+                    const float top = fmaf(mx1[b], __ldg(ch + off[t][0][b][1]), __fmul_rn(mx0[b], __ldg(ch + off[t][0][b][0])));
+                    const float bot = fmaf(mx1[b], __ldg(ch + off[t][1][b][1]), __fmul_rn(mx0[b], __ldg(ch + off[t][1][b][0])));
+                    Q[t][b] = fmaf(my1[t], bot, __fmul_rn(my0[t], top));
+                }
+            const float top = fmaf(lx1, Q[0][1], __fmul_rn(lx0, Q[0][0]));
+            const float bot = fmaf(lx1, Q[1][1], __fmul_rn(lx0, Q[1][0]));
+            v[q] = fmaf(ly1, bot, __fmul_rn(ly0, top));
+        }
+#pragma unroll
+        for (int c = 0; c < CT; ++c) {
+            const float4 pr = *reinterpret_cast<const float4*>(ps + c * PS + k0);
+            float d;
+            d = __fsub_rn(pr.x, v[0]); acc[c] = fmaf(d, d, acc[c]);
+            d = __fsub_rn(pr.y, v[1]); acc[c] = fmaf(d, d, acc[c]);
+            d = __fsub_rn(pr.z, v[2]); acc[c] = fmaf(d, d, acc[c]);
+            d = __fsub_rn(pr.w, v[3]); acc[c] = fmaf(d, d, acc[c]);
+        }
+    }
+    float d[CT];
+#pragma unroll
+    for (int c = 0; c < CT; ++c) d[c] = sqrtf(acc[c]);
+    distance_epilogue<CT>(a, d, n, p);
+}
+
+template <int CT>
+static int launch_distance_sampled(const DistArgs& a, const SampleArgs& sp, cudaStream_t st) {
+    const size_t smem = sizeof(float) * CT * static_cast<size_t>(a.K + 4);
+    TSS_REQUIRE(smem <= 226 * 1024, TSS_E_ARG, "tss_proto_distance_sampled: %d x %lld prototypes do not fit shared memory", CT,
+                static_cast<long long>(a.K));
+    cudaError_t e = cudaFuncSetAttribute(distance_sampled_kernel<CT>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+    if (e != cudaSuccess) return cuda_status(e, "tss_proto_distance_sampled: smem attribute");
+    dim3 grid(static_cast<unsigned>((sp.TH * sp.TW + kSampThreads - 1) / kSampThreads), static_cast<unsigned>(a.N));
+    distance_sampled_kernel<CT><<<grid, kSampThreads, smem, st>>>(a, sp);
+    TSS_LAUNCH_CHECK("tss_proto_distance_sampled");
+    return TSS_OK;
+}
+
 }  // namespace tss
 
-extern "C" int tss_tune_distance_variant(int v) {
-    int old = tss::g_dist_variant;
-    if (v == 0 || v == 1 || v == 2 || v == 4) tss::g_dist_variant = v;
-    return old;
-}
-
-extern "C" int tss_tune_distance_prefetch(int v) {
-    int old = tss::g_dist_prefetch;
-    if (v >= -1 && v <= 2) tss::g_dist_prefetch = v;
-    return old;
-}
-
-extern "C" int tss_tune_distance_split(int v) {
-    int old = tss::g_dist_split;
-    if (v >= 0 && (v == 0 || v == 1 || v == 2 || v == 4 || v == 8)) tss::g_dist_split = v;
-    return old;
+extern "C" int tss_proto_distance_sampled(const float* feat8, const float* protos, int64_t n_img, int64_t channels, int h8,
+                                          int w8, int Hq, int Wq, const int32_t* params, int TH, int TW, int num_classes,
+                                          float temperature, float* dist_out, float* weight_out, const float* soft,
+                                          const void* hard, int hard_dtype, float train_thred, int ignore_index,
+                                          int64_t* label_out, void* stream) {
+    using namespace tss;
+    TSS_REQUIRE(feat8 && protos && params, TSS_E_ARG, "tss_proto_distance_sampled: null pointer");
+    TSS_REQUIRE(n_img >= 0 && n_img <= 65535 && channels > 0 && h8 > 0 && w8 > 0 && Hq > 0 && Wq > 0 && TH > 0 && TW > 0, TSS_E_ARG,
+                "tss_proto_distance_sampled: bad extents");
+    TSS_REQUIRE(channels % 4 == 0, TSS_E_ARG, "tss_proto_distance_sampled: channels (%lld) must be a multiple of 4", static_cast<long long>(channels));
+    TSS_REQUIRE(num_classes >= 1 && num_classes <= 20, TSS_E_CLASSES, "tss_proto_distance_sampled: num_classes %d outside [1, 20]", num_classes);
+    TSS_REQUIRE(dist_out || weight_out || (soft && label_out), TSS_E_ARG, "tss_proto_distance_sampled: no output requested");
+    TSS_REQUIRE(hard == nullptr || hard_dtype == TSS_U8 || hard_dtype == TSS_I32 || hard_dtype == TSS_I64, TSS_E_ARG, "tss_proto_distance_sampled: bad hard dtype");
+    if (n_img == 0) return TSS_OK;
+    DistArgs a;
+    a.feat = feat8; a.protos = protos; a.dist_out = dist_out; a.weight_out = weight_out; a.soft = soft;
+    a.hard = hard; a.label_out = label_out; a.N = n_img; a.K = channels; a.P = static_cast<int64_t>(TH) * TW; a.C = num_classes;
+    a.temperature = temperature; a.train_thred = train_thred; a.hard_dtype = hard_dtype; a.ignore = ignore_index;
+    a.KC = 0;
+    SampleArgs sp{params, h8, w8, Hq, Wq, TH, TW};
+    cudaStream_t st = as_stream(stream);
+    if (num_classes <= 4) return launch_distance_sampled<4>(a, sp, st);
+    if (num_classes <= 8) return launch_distance_sampled<8>(a, sp, st);
+    if (num_classes <= 13) return launch_distance_sampled<13>(a, sp, st);
+    if (num_classes <= 16) return launch_distance_sampled<16>(a, sp, st);
+    if (num_classes <= 19) return launch_distance_sampled<19>(a, sp, st);
+    return launch_distance_sampled<20>(a, sp, st);
 }
 
 extern "C" int tss_proto_distance(const float* feat, const float* protos, int64_t n_img, int64_t channels,
                                   int64_t plane, int num_classes, float temperature, float* dist_out,
                                   float* weight_out, const float* soft, const void* hard, int hard_dtype,
-                                  float train_thred, int ignore_index, int64_t* label_out, void* stream) {
+                                  float train_thred, int ignore_index, int64_t* label_out, int form, void* stream) {
     using namespace tss;
     TSS_REQUIRE(feat && protos, TSS_E_ARG, "tss_proto_distance: null pointer");
-    TSS_REQUIRE(n_img >= 0 && plane > 0 && channels > 0, TSS_E_ARG, "tss_proto_distance: bad extents");
+    TSS_REQUIRE(n_img >= 0 && plane > 0 && plane < (1ll << 31) && channels > 0, TSS_E_ARG, "tss_proto_distance: bad extents");
+    {
+        const DistForm fm = decode_form(form);
+        TSS_REQUIRE(form >= 0 && form < (1 << 16) && (fm.variant == 0 || fm.variant == 1 || fm.variant == 2 || fm.variant == 4) &&
+                    fm.prefetch <= 2 && (fm.split == 0 || fm.split == 1 || fm.split == 2 || fm.split == 4 || fm.split == 8) &&
+                    fm.algo <= 2, TSS_E_ARG, "tss_proto_distance: bad form 0x%x", form);
+    }
     TSS_REQUIRE(channels % 32 == 0, TSS_E_ARG, "tss_proto_distance: channels (%lld) must be a multiple of 32", static_cast<long long>(channels));
     TSS_REQUIRE(num_classes >= 1 && num_classes <= 20, TSS_E_CLASSES, "tss_proto_distance: num_classes %d outside [1, 20]", num_classes);
     TSS_REQUIRE(dist_out || weight_out || (soft && label_out), TSS_E_ARG, "tss_proto_distance: no output requested");
@@ -517,10 +784,10 @@ extern "C" int tss_proto_distance(const float* feat, const float* protos, int64_
     a.temperature = temperature; a.train_thred = train_thred; a.hard_dtype = hard_dtype; a.ignore = ignore_index;
     a.KC = 0;  // chosen per class-count specialisation in launch_distance
     cudaStream_t st = as_stream(stream);
-    if (num_classes <= 4) return launch_distance<4>(a, st);
-    if (num_classes <= 8) return launch_distance<8>(a, st);
-    if (num_classes <= 13) return launch_distance<13>(a, st);
-    if (num_classes <= 16) return launch_distance<16>(a, st);
-    if (num_classes <= 19) return launch_distance<19>(a, st);
-    return launch_distance<20>(a, st);
+    if (num_classes <= 4) return launch_distance<4>(a, form, st);
+    if (num_classes <= 8) return launch_distance<8>(a, form, st);
+    if (num_classes <= 13) return launch_distance<13>(a, form, st);
+    if (num_classes <= 16) return launch_distance<16>(a, form, st);
+    if (num_classes <= 19) return launch_distance<19>(a, form, st);
+    return launch_distance<20>(a, form, st);
 }

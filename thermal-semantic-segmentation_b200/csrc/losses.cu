@@ -53,19 +53,24 @@ struct PixelSoftmax {
 template <typename T>
 __device__ __forceinline__ long long target_at(const void* t, int64_t i) { return load_label<T>(t, i); }
 
-__device__ __forceinline__ void block_reduce4(double (&v)[4], double* out4) {
-    __shared__ double sh[4][kLossThreads / 32];
+// per-CTA partials: kAcc doubles per block (0 CE sum, 1 RCE sum, 2 pixels with a label in [0, C), 3 labels the
+// reference raises on, 4 pixels labelled exactly C -- one_hot(label, C+1)[:, :C] accepts those in SelfTrain.rce)
+constexpr int kAcc = 5;
+constexpr int kAccStride = 8;
+
+__device__ __forceinline__ void block_reduce(double (&v)[kAcc], double* out) {
+    __shared__ double sh[kAcc][kLossThreads / 32];
 #pragma unroll
-    for (int i = 0; i < 4; ++i) v[i] = warp_sum_d(v[i]);
+    for (int i = 0; i < kAcc; ++i) v[i] = warp_sum_d(v[i]);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (lane == 0)
 #pragma unroll
-        for (int i = 0; i < 4; ++i) sh[i][warp] = v[i];
+        for (int i = 0; i < kAcc; ++i) sh[i][warp] = v[i];
     __syncthreads();
-    if (threadIdx.x < 4) {
+    if (threadIdx.x < kAcc) {
         double t = 0.0;
         for (int w = 0; w < kLossThreads / 32; ++w) t += sh[threadIdx.x][w];
-        out4[threadIdx.x] = t;
+        out[threadIdx.x] = t;
     }
 }
 
@@ -79,19 +84,19 @@ struct LossMix {
 
 __global__ void __launch_bounds__(256) reduce_partials_kernel(const double* __restrict__ part, int blocks, double* __restrict__ out,
                                                               const LossMix mix = LossMix{nullptr, 0.f, 0.f, 0, 0}) {
-    __shared__ double sh[4][8];
-    double v[4] = {0, 0, 0, 0};
+    __shared__ double sh[kAcc][8];
+    double v[kAcc] = {0, 0, 0, 0, 0};
     for (int b = threadIdx.x; b < blocks; b += 256)
 #pragma unroll
-        for (int i = 0; i < 4; ++i) v[i] += part[b * 4 + i];
+        for (int i = 0; i < kAcc; ++i) v[i] += part[b * kAccStride + i];
 #pragma unroll
-    for (int i = 0; i < 4; ++i) v[i] = warp_sum_d(v[i]);
+    for (int i = 0; i < kAcc; ++i) v[i] = warp_sum_d(v[i]);
     if ((threadIdx.x & 31) == 0)
 #pragma unroll
-        for (int i = 0; i < 4; ++i) sh[i][threadIdx.x >> 5] = v[i];
+        for (int i = 0; i < kAcc; ++i) sh[i][threadIdx.x >> 5] = v[i];
     __syncthreads();
-    __shared__ double tot[4];
-    if (threadIdx.x < 4) {
+    __shared__ double tot[kAcc];
+    if (threadIdx.x < kAcc) {
         double t = 0.0;
         for (int w = 0; w < 8; ++w) t += sh[threadIdx.x][w];
         out[threadIdx.x] = t;
@@ -101,7 +106,7 @@ __global__ void __launch_bounds__(256) reduce_partials_kernel(const double* __re
     if (mix.losses != nullptr && threadIdx.x == 0) {
         const double valid = tot[2];
         const float ce = static_cast<float>(mix.ce_sum ? tot[0] : tot[0] / valid);   // mean: nan when nothing is valid, as torch
-        const float rce = static_cast<float>(tot[1] / (valid + 1e-6));
+        const float rce = static_cast<float>(tot[1] / (valid + tot[4] + 1e-6));      // the rce mask is label != ignore
         float t = __fmul_rn(mix.alpha, ce);
         if (mix.with_rce) t = __fadd_rn(t, __fmul_rn(mix.beta, rce));
         mix.losses[0] = t;
@@ -113,16 +118,22 @@ __global__ void __launch_bounds__(256) reduce_partials_kernel(const double* __re
 // -log(clamp(0, 1e-4, 1)) in fp32, as torch.log(torch.clamp(one_hot, min=1e-4)) yields off the label
 __device__ __forceinline__ float rce_log_floor() { return -logf(1e-4f); }
 
-// one pixel's CE / RCE terms from a finished PixelSoftmax (acc: 0 CE sum, 1 RCE sum, 2 valid, 3 bad labels)
+// one pixel's CE / RCE terms from a finished PixelSoftmax.  A label equal to C is out of bounds for CrossEntropyLoss
+// but inside one_hot(label, C+1): its clamped one-hot row is all 1e-4, so the pixel adds A * sum_c clamp(p_c) to the
+// RCE sum and counts in the RCE mask (self_training.py:169-173); it is tallied separately in acc[4].
 template <int CT, bool EXACT>
 __device__ __forceinline__ void ce_rce_pixel(const PixelSoftmax<CT, EXACT>& sm, long long y, int C, int ignore, int with_rce,
-                                             float A, double (&acc)[4]) {
+                                             float A, double (&acc)[kAcc]) {
     if (y == ignore) return;
-    if (y < 0 || y >= C) { acc[3] += 1.0; return; }
+    if (y < 0 || y > C || (y == C && !with_rce)) { acc[3] += 1.0; return; }
     const int Cc = EXACT ? CT : C;
-    // -log_softmax[y] = log(s) - (x_y - m)
-    acc[0] += static_cast<double>(sm.log_s() - (sm.xy - sm.m));
-    acc[2] += 1.0;
+    if (y < C) {
+        // -log_softmax[y] = log(s) - (x_y - m)
+        acc[0] += static_cast<double>(sm.log_s() - (sm.xy - sm.m));
+        acc[2] += 1.0;
+    } else {
+        acc[4] += 1.0;
+    }
     if (with_rce) {
         const float inv = sm.inv_s();
         float r = 0.f;
@@ -143,7 +154,7 @@ template <int CT, bool EXACT, typename T, bool VEC>
 __global__ void __launch_bounds__(kLossThreads)
 ce_rce_fwd_kernel(const float* __restrict__ logits, const void* __restrict__ target, int64_t N, int C, int64_t P,
                   int ignore, int with_rce, double* __restrict__ part) {
-    double acc[4] = {0, 0, 0, 0};
+    double acc[kAcc] = {0, 0, 0, 0, 0};
     const float A = rce_log_floor();
     const int64_t first = blockIdx.x * static_cast<int64_t>(kLossThreads) + threadIdx.x;
     const int64_t stride = static_cast<int64_t>(gridDim.x) * kLossThreads;
@@ -180,7 +191,7 @@ ce_rce_fwd_kernel(const float* __restrict__ logits, const void* __restrict__ tar
             ce_rce_pixel<CT, EXACT>(sm, y, C, ignore, with_rce, A, acc);
         }
     }
-    block_reduce4(acc, part + blockIdx.x * 4);
+    block_reduce(acc, part + blockIdx.x * kAccStride);
 }
 
 // upstream gradients {g_total, g_ce, g_rce} (DEVICE) + the forward's sums: the backward kernel forms its own scales
@@ -203,7 +214,7 @@ ce_rce_bwd_kernel(const float* __restrict__ logits, const void* __restrict__ tar
         const float grce = __fadd_rn(gm.with_rce ? __fmul_rn(gt, gm.beta) : 0.f, gm.grads[2]);
         const double valid = gm.fwd_out[2];
         ce_scale = static_cast<float>(gm.ce_sum ? static_cast<double>(gce) : static_cast<double>(gce) / valid);
-        rce_scale = static_cast<float>(static_cast<double>(grce) / (valid + 1e-6));
+        rce_scale = static_cast<float>(static_cast<double>(grce) / (valid + gm.fwd_out[4] + 1e-6));
     } else {
         ce_scale = scales[0];
         rce_scale = scales[1];
@@ -219,12 +230,13 @@ ce_rce_bwd_kernel(const float* __restrict__ logits, const void* __restrict__ tar
         float* g = grad + w.n * C * P + w.p;
         PixelSoftmax<CT, EXACT> sm;
         sm.load(logits + w.n * C * P + w.p, C, P);   // together with the label (see the forward kernel)
-        if (y == ignore || y < 0 || y >= C) {
+        if (y == ignore || y < 0 || y > C || (y == C && rce_scale == 0.f)) {
 #pragma unroll
             for (int c = 0; c < CT; ++c)
                 if (c < Cc) g[c * P] = 0.f;
             continue;
         }
+        const float ces = y < C ? ce_scale : 0.f;   // a label equal to C carries only the RCE term (see ce_rce_pixel)
         const float inv = sm.inv_s();
         float S = 0.f;  // sum over j != y of [1e-7 <= p_j <= 1] p_j  (clamp passes gradient inside its range)
         int yi = static_cast<int>(y);
@@ -242,7 +254,7 @@ ce_rce_bwd_kernel(const float* __restrict__ logits, const void* __restrict__ tar
                 const float pc = sm.p[c];
                 const bool is_y = c == yi;
                 const float gate = (!is_y && pc >= 1e-7f && pc <= 1.0f) ? 1.f : 0.f;
-                g[c * P] = ce_scale * (pc - (is_y ? 1.f : 0.f)) + rs * pc * (gate - S);
+                g[c * P] = ces * (pc - (is_y ? 1.f : 0.f)) + rs * pc * (gate - S);
             }
     }
 }
@@ -259,7 +271,7 @@ template <int CT, bool EXACT, typename T>
 __global__ void __launch_bounds__(kLossThreads)
 focal_fwd_kernel(const float* __restrict__ logits, const void* __restrict__ target, int64_t N, int C, int64_t P,
                  float gamma, const float* __restrict__ alpha, double* __restrict__ part) {
-    double acc[4] = {0, 0, 0, 0};
+    double acc[kAcc] = {0, 0, 0, 0, 0};
     const int64_t total = N * P;
     const int Cc = EXACT ? CT : C;   // per-class guards fold at compile time when EXACT
     const int64_t first = blockIdx.x * static_cast<int64_t>(kLossThreads) + threadIdx.x;
@@ -276,7 +288,7 @@ focal_fwd_kernel(const float* __restrict__ logits, const void* __restrict__ targ
         acc[0] += static_cast<double>(-1.0f * focal_weight(pt, gamma) * logpt);
         acc[1] += 1.0;
     }
-    block_reduce4(acc, part + blockIdx.x * 4);
+    block_reduce(acc, part + blockIdx.x * kAccStride);
 }
 
 template <int CT, bool EXACT, typename T>
@@ -358,7 +370,7 @@ static int check_loss_args(const char* who, const void* logits, const void* targ
 
 }  // namespace tss
 
-extern "C" size_t tss_loss_workspace_bytes(void) { return static_cast<size_t>(tss::kLossMaxBlocks) * 4 * sizeof(double); }
+extern "C" size_t tss_loss_workspace_bytes(void) { return static_cast<size_t>(tss::kLossMaxBlocks) * tss::kAccStride * sizeof(double); }
 
 static int ce_rce_fwd_impl(const float* logits, const void* target, int target_dtype, int64_t n_img, int num_classes,
                            int64_t plane, int ignore_index, int with_rce, double* out, void* workspace, void* stream,

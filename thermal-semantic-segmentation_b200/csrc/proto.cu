@@ -6,36 +6,45 @@
 // and materialises a [K,h,w] product per (image, class); here feat is streamed ONCE:
 //
 //   proto_label_kernel   logits -> argmax label per pixel, class counts, and per 512-pixel tile a
-//                        class-sorted list of pixel offsets + class segment boundaries ("records").
+//                        class-sorted list of pixel offsets in GROUPS OF EIGHT: every class segment is padded
+//                        to a multiple of eight entries with the offset of a slot that always holds 0.0f, so a
+//                        group belongs to exactly one class and the accumulate kernel has no edge handling.
 //   proto_accum_kernel   persistent, one CTA per SM.  A producer warp stages tiles of 32 channel rows x
 //                        512 pixels into shared memory with 1-D bulk async copies (TMA engine, UBLKCP)
 //                        completing on an mbarrier ring; every lane copies the 16-byte-aligned superset
 //                        of its (misaligned) row, rows are skewed so that "lane = channel" reads are
-//                        bank-conflict free.  Eight consumer warps walk the tile's pixels in class-sorted
-//                        order: the pixel index is warp-uniform, each lane adds its channel's value to
-//                        ONE register accumulator per class segment -- no atomics, no select chains.
-//                        Global fp32 atomics happen once per class per (image, channel group) per CTA.
+//                        bank-conflict free.  NC consumer warps (16 when the kernel has the SM to itself, 4 when
+//                        it shares the SM with the pseudo-label kernel) each take a contiguous run of the tile's
+//                        groups: one 128-bit shared load brings eight pixel offsets (warp-uniform), eight
+//                        unconditional shared loads + an add tree, and the running sum goes to ONE register
+//                        accumulator per class when the class changes -- no atomics, no select chains.
+//                        Global fp32 reductions happen once per class per (image, channel group) per warp.
 #include "common.cuh"
 
 namespace tss {
 
 constexpr int kPT = TSS_PROTO_TILE;        // pixels per tile
 constexpr int kKT = 32;                    // channels per tile: one per lane
-constexpr int kConsumers = 16;             // consumer warps (each owns kPT/kConsumers sorted positions of a tile)
-constexpr int kAccThreads = (kConsumers + 1) * 32;
-constexpr int kRowStride = kPT + 36;       // floats; room for head misalignment (3) + 16 B round-up (3) + skew (28)
-constexpr int kRecBytes = kPT * 2 + 128 + 64;   // uint16 idx[kPT] + uint16 off[64] + uint16 call[32]
+constexpr int kRowStride = kPT + 40;       // floats; head misalignment (3) + 16 B round-up (3) + zero slots (4) + skew (28)
+constexpr int kPadOff = (kPT + 7) * 4;     // byte offset (from a lane's first pixel) of its always-zero slot: past every
+                                           // byte a bulk copy can write (<= 3 + 512 + 3 floats from the aligned start)
+constexpr int kIdxMax = kPT + 8 * TSS_MAX_CLASSES;   // sum_c roundup8(count_c) <= 512 + 7 C
+constexpr int kGroupsMax = kIdxMax / 8;
 constexpr int kStages = 3;
 
 static_assert(kRowStride % 4 == 0, "rows must start 16-byte aligned");
-static_assert(kRecBytes % 16 == 0, "records are bulk-copied");
 
 struct TileRecord {
-    uint16_t idx[kPT];   // BYTE offsets (4 x pixel index) of the tile's pixels sorted by class (bucket C = pixels that join no sum)
-    uint16_t off[64];    // off[c] = first sorted position of class c; off[c+1]-off[c] = gated count in the tile
-    uint16_t call[32];   // ungated one-hot count per class in the tile (the "< 10 pixels" rule)
+    uint16_t idx[kIdxMax];      // BYTE offsets (4 x pixel index, or kPadOff) of the tile's pixels, sorted by class
+    uint8_t gcls[kGroupsMax];   // class of every group of eight entries
+    uint16_t cnt[32];           // gated pixel count per class in the tile (the divisor)
+    uint16_t call[32];          // ungated one-hot count per class in the tile (the "< 10 pixels" rule)
+    uint16_t groups;            // groups in use
+    uint16_t pad_[7];
 };
-static_assert(sizeof(TileRecord) == kRecBytes, "record layout");
+constexpr int kRecBytes = sizeof(TileRecord);
+static_assert(kRecBytes % 16 == 0, "records are bulk-copied");
+static_assert(kRecBytes == TSS_PROTO_RECORD_BYTES, "header constant");
 
 // ------------------------------------------------------------------------------------------------
 template <int CT>
@@ -107,35 +116,44 @@ proto_label_kernel(const float* __restrict__ logits, const float* __restrict__ l
         }
     }
     __syncthreads();
-    // exclusive scan in (class, segment) order -> start of every (segment, class) run
+    // totals per bucket, then class segments padded to a multiple of eight entries (bucket C is not stored)
     if (tid <= C) {
         int tot = 0;
         for (int s = 0; s < 16; ++s) tot += wcnt[s][tid];
         boff[tid + 1] = tot;
     }
     __syncthreads();
+    __shared__ int pstart[TSS_MAX_CLASSES + 1];
     if (tid == 0) {
-        boff[0] = 0;
-        for (int b = 0; b <= C; ++b) boff[b + 1] += boff[b];
+        int run = 0;
+        for (int b = 0; b < C; ++b) {
+            pstart[b] = run;
+            run += (boff[b + 1] + 7) & ~7;
+        }
+        pstart[C] = run;
     }
     __syncthreads();
-    if (tid <= C) {
-        int run = boff[tid];
+    TileRecord* rec = records + n * tiles + tile;
+    if (tid < C) {
+        int run = pstart[tid];
         for (int s = 0; s < 16; ++s) {
             const int c = wcnt[s][tid];
             wcnt[s][tid] = run;
             run += c;
         }
+        for (; run < pstart[tid + 1]; ++run) rec->idx[run] = static_cast<uint16_t>(kPadOff);
+        for (int g = pstart[tid] >> 3; g < (pstart[tid + 1] >> 3); ++g) rec->gcls[g] = static_cast<uint8_t>(tid);
     }
     __syncthreads();
-    TileRecord* rec = records + n * tiles + tile;
 #pragma unroll
-    for (int r = 0; r < 2; ++r) rec->idx[wcnt[r * 8 + warp][bucket[r]] + rank[r]] = static_cast<uint16_t>((r * 256 + tid) * 4);
-    if (tid < 64) rec->off[tid] = static_cast<uint16_t>(tid <= C + 1 ? boff[tid] : kPT);
+    for (int r = 0; r < 2; ++r)
+        if (bucket[r] < C) rec->idx[wcnt[r * 8 + warp][bucket[r]] + rank[r]] = static_cast<uint16_t>((r * 256 + tid) * 4);
     if (tid < 32) {
-        const int g = tid < C ? boff[tid + 1] - boff[tid] : 0;  // gated count of this class in the tile
+        const int g = tid < C ? boff[tid + 1] : 0;  // gated count of this class in the tile
+        rec->cnt[tid] = static_cast<uint16_t>(g);
         rec->call[tid] = static_cast<uint16_t>(tid < C ? ((use_gate || labels_val != nullptr) ? call[tid] : g) : 0);
     }
+    if (tid == 0) rec->groups = static_cast<uint16_t>(pstart[C] >> 3);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -144,13 +162,9 @@ struct AccSmem {
     static constexpr int rows_bytes = kStages * kKT * kRowStride * 4;
     static constexpr int rec_off = rows_bytes;
     static constexpr int bar_off = rec_off + kStages * kRecBytes;
-    static constexpr int acc_off = bar_off + 2 * kStages * 8 + 16;          // [TSS_MAX_CLASSES][32] fp32
-    static constexpr int total = acc_off + TSS_MAX_CLASSES * 32 * 4;
+    static constexpr int total = bar_off + 2 * kStages * 8 + 16;
 };
-
-__device__ __forceinline__ void consumer_bar() {  // named barrier 1: the consumer warps only
-    asm volatile("bar.sync 1, %0;" ::"n"(kConsumers * 32) : "memory");
-}
+static_assert(AccSmem::total <= 227 * 1024, "accumulate kernel shared memory");
 
 __device__ __forceinline__ float lds_f32(uint32_t addr) {  // unconditional shared load (never sunk into a branch)
     float v;
@@ -167,7 +181,7 @@ __device__ __forceinline__ int row_skew_words(int lane) {
 }
 
 // racc[c] += t for a warp-uniform run-time class c: a switch (one indirect branch, no divergence) instead of a
-// chain of CT predicated adds -- the chain was ~40 of the ~170 instructions a class segment costs
+// chain of CT predicated adds
 template <int CT>
 __device__ __forceinline__ void add_to_class(float (&racc)[CT], int c, float t) {
 #define TSS_ACC_CASE(i) \
@@ -212,8 +226,17 @@ __device__ __forceinline__ void add_to_class(float (&racc)[CT], int c, float t) 
 #undef TSS_ACC_CASE
 }
 
-template <int CT>
-__global__ void __launch_bounds__(kAccThreads, 1)
+// NC = consumer warps.  The register cap is 96 per thread in every form (minBlocks is only the cap: shared memory
+// holds one CTA per SM), so that NC = 4 (160 threads, 15 K registers) fits beside three 4-warp CTAs of the
+// pseudo-label kernel on the same SM.
+template <int NC>
+struct AccCfg {
+    static constexpr int kThreads = (NC + 1) * 32;
+    static constexpr int kMinBlocks = 65536 / (kThreads * 96) < 1 ? 1 : 65536 / (kThreads * 96);
+};
+
+template <int CT, int NC>
+__global__ void __launch_bounds__(AccCfg<NC>::kThreads, AccCfg<NC>::kMinBlocks)
 proto_accum_kernel(const float* __restrict__ feat, const TileRecord* __restrict__ records, int64_t N, int64_t K,
                    int64_t P, int C, float* __restrict__ sums) {
     extern __shared__ __align__(128) unsigned char smem[];
@@ -221,9 +244,11 @@ proto_accum_kernel(const float* __restrict__ feat, const TileRecord* __restrict_
     unsigned char* recs = smem + AccSmem::rec_off;
     uint64_t* full = reinterpret_cast<uint64_t*>(smem + AccSmem::bar_off);
     uint64_t* empty = full + kStages;
-    float* acc = reinterpret_cast<float*>(smem + AccSmem::acc_off);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    for (int i = tid; i < TSS_MAX_CLASSES * 32; i += kAccThreads) acc[i] = 0.f;
+    // the always-zero slots (kPadOff) live in the staged rows: clear the whole row area once; bulk copies never
+    // reach those slots afterwards
+    for (int i = tid; i < AccSmem::rows_bytes / 16; i += AccCfg<NC>::kThreads)
+        reinterpret_cast<float4*>(rows)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     const int64_t T = (P + kPT - 1) / kPT;
     const int64_t KG = K / kKT;
     const int64_t jobs = N * KG * T;
@@ -231,14 +256,16 @@ proto_accum_kernel(const float* __restrict__ feat, const TileRecord* __restrict_
     if (tid == 0) {
         for (int s = 0; s < kStages; ++s) {
             mbar_init(&full[s], 32);
-            mbar_init(&empty[s], kConsumers);
+            mbar_init(&empty[s], NC);
         }
         mbar_fence_init();
     }
+    // generic-proxy stores (the zero fill) before async-proxy writes (bulk copies) to the same shared memory
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     __syncthreads();
     const int64_t total_elems = N * K * P;
 
-    if (warp == kConsumers) {
+    if (warp == NC) {
         // ===== producer warp: lane l stages channel row l of every tile job
         int stage = 0;
         uint32_t phase = 0;
@@ -271,23 +298,16 @@ proto_accum_kernel(const float* __restrict__ feat, const TileRecord* __restrict_
             if (++stage == kStages) { stage = 0; phase ^= 1u; }
         }
     } else {
-        // ===== consumer warps: class-sorted walk, lane = channel.  Warp w owns sorted positions
-        // [w*S, w*S+S) of every tile (S = kPT / kConsumers).  The class loop is unrolled so that every class
-        // has its own REGISTER accumulator; inside a class segment eight pixels are in flight at once (eight
-        // independent shared loads feeding a small add tree).  When the (image, channel group) changes, the
-        // warps fold their registers into the CTA's shared [C][32] accumulators, meet on a named barrier and
-        // emit ONE global atomic per class and channel.
+        // ===== consumer warps: class-sorted walk, lane = channel.  Warp w takes the contiguous run
+        // [G w / NC, G (w+1) / NC) of the tile's G groups; every class has its own REGISTER accumulator.  When the
+        // (image, channel group) changes, every warp adds its registers straight to the global sums with
+        // fire-and-forget reductions (RED.ADD.F32 resolves in L2, the SM does not wait).
         float racc[CT];
 #pragma unroll
         for (int c = 0; c < CT; ++c) racc[c] = 0.f;
         int stage = 0;
         uint32_t phase = 0;
         int64_t cur_unit = -1;
-        const int s0 = warp * (kPT / kConsumers), s1 = s0 + kPT / kConsumers;
-        // (image, channel group) finished: every warp adds its register accumulators straight to the global sums
-        // with fire-and-forget reductions (RED.ADD.F32 resolves in L2, the SM does not wait).  A CTA-level
-        // pre-reduction through shared-memory atomics costs more than it saves here: 16 warps x C ATOMS at
-        // ~64 cycles each serialise on the one shared-atomic unit (~7 us per flush).
         int64_t cur_n = 0, cur_kg = 0;
         auto flush = [&](int64_t n, int64_t kg) {
             float* out = sums + (n * C) * K + kg * kKT + lane;
@@ -317,46 +337,33 @@ proto_accum_kernel(const float* __restrict__ feat, const TileRecord* __restrict_
             const TileRecord* rec = reinterpret_cast<const TileRecord*>(recs + stage * kRecBytes);
             mbar_wait(&full[stage], phase);
 #ifndef TSS_PROTO_NOCONSUME
-            // Walk this warp's sorted positions [s0, s1) segment by segment.  Lane c holds class c's range
-            // [off[c], off[c+1]) of the tile; ONE ballot finds the class that owns the current position.  The
-            // loop body exists once in the instruction stream (an unrolled per-class copy thrashes the
-            // instruction cache at 19 classes); only the final "add the segment sum to class c's register
-            // accumulator" is an unrolled chain of predicated adds.
-            const int oa = rec->off[lane], ob = rec->off[lane + 1];  // off[] has 64 entries, non-decreasing
+            const int G = rec->groups;
+            const int g0 = (G * warp) / NC, g1 = (G * (warp + 1)) / NC;
             const uint32_t row_addr = smem_u32(row);
-            int pos = s0;
-            while (pos < s1) {  // warp-uniform
-                const unsigned int owner = __ballot_sync(0xffffffffu, oa <= pos && pos < ob);
-                const int c = __ffs(owner) - 1;
-                const int b = min(s1, __shfl_sync(0xffffffffu, ob, c));
-                if (c < C) {  // bucket C = pixels that join no sum
-                    float t0 = 0.f, t1 = 0.f;
-                    // aligned groups of eight sorted positions: ONE 128-bit shared load brings the eight pixel
-                    // indices; the eight feature loads are unconditional (every index of a record is a valid
-                    // offset into the staged row), the partial groups at the two ends of a segment select zeros
-                    for (int base = pos & ~7; base < b; base += 8) {
-                        const uint4 iq = *reinterpret_cast<const uint4*>(&rec->idx[base]);
-                        float v[8];
-                        v[0] = lds_f32(row_addr + (iq.x & 0xffffu));   // the record holds byte offsets
-                        v[1] = lds_f32(row_addr + (iq.x >> 16));
-                        v[2] = lds_f32(row_addr + (iq.y & 0xffffu));
-                        v[3] = lds_f32(row_addr + (iq.y >> 16));
-                        v[4] = lds_f32(row_addr + (iq.z & 0xffffu));
-                        v[5] = lds_f32(row_addr + (iq.z >> 16));
-                        v[6] = lds_f32(row_addr + (iq.w & 0xffffu));
-                        v[7] = lds_f32(row_addr + (iq.w >> 16));
-                        const int first = pos - base, last = b - base;  // valid q: first <= q < last
-                        if (first > 0 || last < 8) {
-#pragma unroll
-                            for (int q = 0; q < 8; ++q) v[q] = (q >= first && q < last) ? v[q] : 0.f;
-                        }
-                        t0 += (v[0] + v[1]) + (v[2] + v[3]);
-                        t1 += (v[4] + v[5]) + (v[6] + v[7]);
-                    }
-                    add_to_class<CT>(racc, c, t0 + t1);
+            int cur = -1;
+            float run = 0.f;
+            for (int g = g0; g < g1; ++g) {  // warp-uniform
+                const int c = rec->gcls[g];
+                if (c != cur) {
+                    if (cur >= 0) add_to_class<CT>(racc, cur, run);
+                    run = 0.f;
+                    cur = c;
                 }
-                pos = b;
+                // ONE 128-bit shared load brings the eight byte offsets; every offset of a record is a valid offset
+                // into the staged row (a pixel of the tile, or the zero slot)
+                const uint4 iq = *reinterpret_cast<const uint4*>(&rec->idx[8 * g]);
+                float v[8];
+                v[0] = lds_f32(row_addr + (iq.x & 0xffffu));
+                v[1] = lds_f32(row_addr + (iq.x >> 16));
+                v[2] = lds_f32(row_addr + (iq.y & 0xffffu));
+                v[3] = lds_f32(row_addr + (iq.y >> 16));
+                v[4] = lds_f32(row_addr + (iq.z & 0xffffu));
+                v[5] = lds_f32(row_addr + (iq.z >> 16));
+                v[6] = lds_f32(row_addr + (iq.w & 0xffffu));
+                v[7] = lds_f32(row_addr + (iq.w >> 16));
+                run += ((v[0] + v[1]) + (v[2] + v[3])) + ((v[4] + v[5]) + (v[6] + v[7]));
             }
+            if (cur >= 0) add_to_class<CT>(racc, cur, run);
 #endif
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty[stage]);
@@ -372,7 +379,7 @@ __device__ __forceinline__ void tile_counts(const TileRecord* __restrict__ rec, 
                                             int& gated, int& all) {
     int g = 0, a = 0;
     for (int64_t t = lane; t < tiles; t += 32) {
-        g += static_cast<int>(rec[t].off[c + 1]) - static_cast<int>(rec[t].off[c]);
+        g += rec[t].cnt[c];
         a += rec[t].call[c];
     }
     gated = __reduce_add_sync(0xffffffffu, g);
@@ -661,21 +668,31 @@ extern "C" int tss_proto_labels(const float* logits, const float* labels_val, in
 }
 
 namespace tss {
-template <int CT>
+template <int CT, int NC>
 static int launch_accum(const float* feat, const TileRecord* rec, int64_t N, int64_t K, int64_t P, int C, float* sums,
                         cudaStream_t st) {
-    cudaError_t e = cudaFuncSetAttribute(proto_accum_kernel<CT>, cudaFuncAttributeMaxDynamicSharedMemorySize, AccSmem::total);
+    cudaError_t e = cudaFuncSetAttribute(proto_accum_kernel<CT, NC>, cudaFuncAttributeMaxDynamicSharedMemorySize, AccSmem::total);
     if (e != cudaSuccess) return cuda_status(e, "tss_proto_accumulate: smem attribute");
     const int64_t jobs = N * (K / kKT) * ((P + kPT - 1) / kPT);
     const int grid = static_cast<int>(jobs < kNumSMs ? jobs : kNumSMs);
-    proto_accum_kernel<CT><<<grid, kAccThreads, AccSmem::total, st>>>(feat, rec, N, K, P, C, sums);
+    proto_accum_kernel<CT, NC><<<grid, AccCfg<NC>::kThreads, AccSmem::total, st>>>(feat, rec, N, K, P, C, sums);
     TSS_LAUNCH_CHECK("tss_proto_accumulate");
     return TSS_OK;
+}
+template <int CT>
+static int launch_accum_nc(int nc, const float* feat, const TileRecord* rec, int64_t N, int64_t K, int64_t P, int C, float* sums,
+                           cudaStream_t st) {
+    switch (nc) {
+        case 4: return launch_accum<CT, 4>(feat, rec, N, K, P, C, sums, st);
+        case 8: return launch_accum<CT, 8>(feat, rec, N, K, P, C, sums, st);
+        default: return launch_accum<CT, 16>(feat, rec, N, K, P, C, sums, st);
+    }
 }
 }  // namespace tss
 
 extern "C" int tss_proto_accumulate(const float* feat, const void* records, int64_t n_img, int64_t channels,
-                                    int64_t plane, int num_classes, float* sums, int zero_sums, void* stream) {
+                                    int64_t plane, int num_classes, float* sums, int zero_sums, int consumer_warps,
+                                    void* stream) {
     using namespace tss;
     TSS_REQUIRE(feat && records && sums, TSS_E_ARG, "tss_proto_accumulate: null pointer");
     TSS_REQUIRE(n_img >= 0 && plane > 0 && channels > 0, TSS_E_ARG, "tss_proto_accumulate: bad extents");
@@ -683,6 +700,8 @@ extern "C" int tss_proto_accumulate(const float* feat, const void* records, int6
     TSS_REQUIRE(num_classes >= 1 && num_classes <= TSS_MAX_CLASSES, TSS_E_CLASSES, "tss_proto_accumulate: num_classes %d", num_classes);
     TSS_REQUIRE((reinterpret_cast<uintptr_t>(feat) & 15) == 0 && (reinterpret_cast<uintptr_t>(records) & 15) == 0, TSS_E_ALIGN,
                 "tss_proto_accumulate: feat and records must be 16-byte aligned");
+    TSS_REQUIRE(consumer_warps == 0 || consumer_warps == 4 || consumer_warps == 8 || consumer_warps == 16, TSS_E_ARG,
+                "tss_proto_accumulate: consumer_warps must be 0 (default 16), 4, 8 or 16");
     if (n_img == 0) return TSS_OK;
     cudaStream_t st = as_stream(stream);
     if (zero_sums) {
@@ -690,9 +709,9 @@ extern "C" int tss_proto_accumulate(const float* feat, const void* records, int6
         if (e != cudaSuccess) return cuda_status(e, "tss_proto_accumulate: memset");
     }
     auto* rec = static_cast<const TileRecord*>(records);
-    if (num_classes <= 13) return launch_accum<13>(feat, rec, n_img, channels, plane, num_classes, sums, st);
-    if (num_classes <= 19) return launch_accum<19>(feat, rec, n_img, channels, plane, num_classes, sums, st);
-    return launch_accum<TSS_MAX_CLASSES>(feat, rec, n_img, channels, plane, num_classes, sums, st);
+    if (num_classes <= 13) return launch_accum_nc<13>(consumer_warps, feat, rec, n_img, channels, plane, num_classes, sums, st);
+    if (num_classes <= 19) return launch_accum_nc<19>(consumer_warps, feat, rec, n_img, channels, plane, num_classes, sums, st);
+    return launch_accum_nc<TSS_MAX_CLASSES>(consumer_warps, feat, rec, n_img, channels, plane, num_classes, sums, st);
 }
 
 extern "C" int tss_proto_finalize(const float* sums, const void* records, int64_t n_img, int num_classes,

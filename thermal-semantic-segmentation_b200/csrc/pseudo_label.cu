@@ -566,16 +566,16 @@ static int launch_direct(const PLArgs& a, int64_t n_img, cudaStream_t st) {
     return TSS_OK;
 }
 
-static int g_pl_force_tile = 0;
-
 template <int C, int MODE>
-static int launch_up(const PLArgs& a, int64_t n_img, cudaStream_t st) {
+static int launch_up(const PLArgs& a, int64_t n_img, int sm_warps, cudaStream_t st) {
     // One wave.  The kernel is compiled for a register cap that lets an SM hold UpCfg<C>::kWarpsPerSM warps;
-    // pick the warps per CTA that wastes the fewest column slots and keeps the SM fullest.
+    // pick the warps per CTA that wastes the fewest column slots and keeps the SM fullest.  sm_warps (0 = all)
+    // sizes the wave for fewer warps per SM, leaving registers for a co-resident kernel (the accumulate
+    // kernel of the prototype stage, which is HBM-bound while this one is XU/issue-bound).
     const int col_blocks = (a.W + kUpBlockPx - 1) / kUpBlockPx;
     int best_wpc = 8, best_cps = 2;
     double best_eff = -1.0;
-    constexpr int kW = UpCfg<C>::kWarpsPerSM;
+    const int kW = (sm_warps >= 4 && sm_warps < UpCfg<C>::kWarpsPerSM) ? sm_warps : UpCfg<C>::kWarpsPerSM;
     for (int wpc = 4; wpc <= kW; ++wpc) {
         const int cps = kW / wpc;                                  // CTAs per SM by registers
         const int gx = (col_blocks + wpc - 1) / wpc;
@@ -607,17 +607,13 @@ static int launch_up(const PLArgs& a, int64_t n_img, cudaStream_t st) {
 
 }  // namespace tss
 
-extern "C" int tss_tune_pl_force_tile(int v) {
-    int old = tss::g_pl_force_tile;
-    if (v >= 0) tss::g_pl_force_tile = v;
-    return old;
-}
-
 extern "C" int tss_pseudo_label(const float* src, const float* src_flip, int64_t n_img, int num_classes, int h, int w,
                                 int H, int W, int mode, int flip, uint8_t* label_out, uint16_t* conf16_out,
                                 float* conf32_out, uint8_t* label_thr_out, const float* thr_host,
-                                const uint8_t* keep_host, int ignore_index, void* stream) {
+                                const uint8_t* keep_host, int ignore_index, int flags, void* stream) {
     using namespace tss;
+    const int g_pl_force_tile = (flags & TSS_PL_FLAG_FORCE_TILE) ? 1 : 0;
+    const int sm_warps = (flags >> 8) & 0xff;
     TSS_REQUIRE(src != nullptr, TSS_E_ARG, "tss_pseudo_label: null src");
     TSS_REQUIRE(n_img >= 0 && h > 0 && w > 0 && H > 0 && W > 0, TSS_E_ARG, "tss_pseudo_label: bad extents");
     TSS_REQUIRE(n_img <= 65535, TSS_E_ARG, "tss_pseudo_label: at most 65535 images per call");
@@ -659,10 +655,10 @@ extern "C" int tss_pseudo_label(const float* src, const float* src_flip, int64_t
         (W % 2 == 0) && W >= 2 && al(label_out, 2) && al(conf16_out, 4) && al(conf32_out, 8) && al(label_thr_out, 2) &&
         (num_classes == 13 || num_classes == 19) && static_cast<int64_t>(num_classes) * h * w < (1ll << 30)) {
         if (num_classes == 13)
-            return mode == TSS_PL_UP_SOFTMAX ? launch_up<13, TSS_PL_UP_SOFTMAX>(a, n_img, st)
-                                             : launch_up<13, TSS_PL_UP_ARGMAX>(a, n_img, st);
-        return mode == TSS_PL_UP_SOFTMAX ? launch_up<19, TSS_PL_UP_SOFTMAX>(a, n_img, st)
-                                         : launch_up<19, TSS_PL_UP_ARGMAX>(a, n_img, st);
+            return mode == TSS_PL_UP_SOFTMAX ? launch_up<13, TSS_PL_UP_SOFTMAX>(a, n_img, sm_warps, st)
+                                             : launch_up<13, TSS_PL_UP_ARGMAX>(a, n_img, sm_warps, st);
+        return mode == TSS_PL_UP_SOFTMAX ? launch_up<19, TSS_PL_UP_SOFTMAX>(a, n_img, sm_warps, st)
+                                         : launch_up<19, TSS_PL_UP_ARGMAX>(a, n_img, sm_warps, st);
     }
 
     // tile height: the largest of {64,32,16,8} whose staged rows fit the shared-memory budget

@@ -7,14 +7,21 @@ device and there is no CPU path.
 
     cal_prototype.Class_Features              -> Class_Features
     self_training.SelfTrain (label methods)   -> SelfTrain
-    generate_pseudo_label.generate_pl :74-85  -> pseudo_label_batch / soft_label_batch
-    data/freiburg_dataset.py:115-125          -> threshold_block
+    generate_pseudo_label.generate_pl :60-96  -> generate_pl (pseudo_label_batch / soft_label_batch + formats)
+    data/freiburg_dataset.py:115-125          -> threshold_block, prepare_freiburg_labels (Freiburg ctor hook)
     utils.eval_tools._fast_hist / evaluate    -> _fast_hist / evaluate (+ ConfusionMeter, on-device)
     utils.loss.SemanticConsistency / FocalLoss-> SemanticConsistency / FocalLoss
-    segmentation_evaluate.seg_validate :38-44 -> validate_batch
+    segmentation_evaluate.seg_validate :24-80 -> seg_validate (validate_batch per batch)
+
+Label range checks: torch raises (CPU) or device-asserts (CUDA) on targets outside [0, C); the kernels count such
+pixels instead, which needs no host sync.  With ``STRICT_LABELS`` (env ``B200SEG_STRICT=1``) every loss call reads
+the counter back and raises like the reference; otherwise only ``SelfTrain.rce`` (whose reference form raises on
+the host, in ``one_hot``) does.  INTEGRATION.md section 1 lists the remaining deliberate differences.
 """
 from __future__ import annotations
 
+import copy
+import os
 from typing import Iterable, Optional, Sequence
 
 import numpy as np
@@ -23,8 +30,17 @@ import torch
 from . import ops
 
 __all__ = ["Class_Features", "SelfTrain", "pseudo_label_batch", "soft_label_batch", "threshold_block",
-           "_fast_hist", "evaluate", "metrics_from_hist", "ConfusionMeter", "validate_batch",
-           "SemanticConsistency", "FocalLoss", "install"]
+           "_fast_hist", "evaluate", "metrics_from_hist", "ConfusionMeter", "validate_batch", "seg_validate",
+           "generate_pl", "prepare_freiburg_labels", "SemanticConsistency", "FocalLoss", "install", "STRICT_LABELS"]
+
+STRICT_LABELS = os.environ.get("B200SEG_STRICT", "0") not in ("", "0")
+
+
+def _raise_if_bad_labels(bad: torch.Tensor, what: str) -> None:
+    """One device->host read of the kernel's out-of-range label counter (strict mode only)."""
+    n = int(bad.item())
+    if n:
+        raise IndexError("%s: %d target values are out of bounds (torch's CrossEntropyLoss raises here)" % (what, n))
 
 
 # ------------------------------------------------------------------------------------------------
@@ -100,16 +116,17 @@ def soft_label_batch(out: torch.Tensor) -> torch.Tensor:
 
 
 def pseudo_label_batch(out: torch.Tensor, flip_out: Optional[torch.Tensor] = None, size: Optional[Sequence[int]] = None,
-                       flip_dim: int = 1, thr=None, keep=None, ignore_index: int = 255):
+                       flip_dim: int = 1, thr=None, keep=None, ignore_index: int = 255, want_conf32: bool = False):
     """Hard branch of generate_pl.  Without ``flip_out``: Softmax(dim=1)(out).max(1) (:85) at the logits'
     resolution (or, with ``size``, after bilinear upsampling of the logits -- the fused headline path).
     With ``flip_out``: the flip branch as committed (:81-85) -- softmax, upsample, average with the flipped
     second pass (``flip_dim=1`` is what ``torch.fliplr`` does to NCHW, 3 is the width mirror), a second
     softmax, then max.  Returns ops.PseudoLabels (uint8 label, fp16 confidence as stored at :91,:94, and the
-    thresholded label of data/freiburg_dataset.py:115-123 when ``thr``/``keep`` are given)."""
+    thresholded label of data/freiburg_dataset.py:115-123 when ``thr``/``keep`` are given; the fp32 confidence
+    before the storage cast only with ``want_conf32``)."""
     if flip_out is None:
         return ops.pseudo_label(out, size=size, mode=ops.PL_UP_SOFTMAX, thr=thr, keep=keep, ignore_index=ignore_index,
-                                want_conf32=True)
+                                want_conf32=want_conf32)
     if size is None:
         raise ValueError("the flip branch upsamples to the image size: pass size=(H, W)")
     if flip_dim not in (1, 3):
@@ -117,7 +134,7 @@ def pseudo_label_batch(out: torch.Tensor, flip_out: Optional[torch.Tensor] = Non
     return ops.pseudo_label(ops.softmax_nchw(out), size=size, mode=ops.PL_PROB_UP_SOFTMAX,
                             src_flip=ops.softmax_nchw(flip_out),
                             flip=ops.FLIP_CLASS if flip_dim == 1 else ops.FLIP_WIDTH, thr=thr, keep=keep,
-                            ignore_index=ignore_index, want_conf32=True)
+                            ignore_index=ignore_index, want_conf32=want_conf32)
 
 
 def threshold_block(label: torch.Tensor, conf16: Optional[torch.Tensor], num_classes: int, threshold=0.3,
@@ -213,12 +230,18 @@ def evaluate(predictions, gts, num_classes, device="cuda"):
         raise ValueError("invalid dataset for evaluation.")
     m = ConfusionMeter(num_classes, device)
     if isinstance(predictions, (np.ndarray, torch.Tensor)) and isinstance(gts, (np.ndarray, torch.Tensor)) \
-            and tuple(predictions.shape) == tuple(gts.shape):
-        m.add(predictions, gts)           # one stacked array (what seg_validate passes): a single launch
+            and len(predictions) == len(gts) and _numel(predictions) == _numel(gts):
+        # one stacked array each -- what seg_validate passes: predictions [M,H,W], labels [M,H,W] or (after ToTensor)
+        # [M,1,H,W] (segmentation_evaluate.py:42-44,77-78); image-wise flatten order is the same: a single launch
+        m.add(predictions.reshape(-1), gts.reshape(-1))
     else:
         for lp, lt in zip(predictions, gts):
             m.add(lp, lt)
     return metrics_from_hist(m.result(), num_classes)
+
+
+def _numel(a) -> int:
+    return int(a.numel()) if isinstance(a, torch.Tensor) else int(a.size)
 
 
 def validate_batch(outputs: torch.Tensor, label: torch.Tensor, meter: ConfusionMeter, size=(256, 512),
@@ -231,6 +254,89 @@ def validate_batch(outputs: torch.Tensor, label: torch.Tensor, meter: ConfusionM
     if ignore_index is not None:
         loss = ops.cross_entropy(ops.upsample_bilinear(outputs, size), label, ignore_index)
     return pl.label, loss
+
+
+def seg_validate(args, sem_net, val_data, loss_func, device, vis=None, num_classes=13):
+    """segmentation_evaluate.seg_validate (:24-80) with the per-batch arithmetic on the device: upsample + argmax in
+    one kernel, the confusion matrix accumulated where the predictions are (no int64 D2H of every prediction, no
+    np.concatenate of the whole validation set), the loss accumulated on the device and read once at the end.
+    Returns (mean_iu, average loss, cls_iu) like the reference.  ``loss_func``: a mean-reduced unweighted
+    nn.CrossEntropyLoss / dropin._SegLoss runs in the fused CE kernel, anything else is called on the upsampled
+    logits as the reference does.  The prediction-saving branch (:55-75) is presentation and is not reproduced."""
+    print('validating...')
+    sem_net.eval()
+    dev = torch.device(device)
+    meter = ConfusionMeter(num_classes, dev)
+    loss_sum = torch.zeros((), dtype=torch.float64, device=dev)
+    count = 0
+    ignore = _ce_ignore_index(loss_func)
+    for item in val_data:
+        image = item['image'].to(dev)
+        label = item['label'].to(dev)
+        outputs = sem_net(image)['out']
+        n = image.size(0)
+        if ignore is not None:
+            _, loss = validate_batch(outputs, label, meter, size=(256, 512), ignore_index=ignore)
+        else:
+            validate_batch(outputs, label, meter, size=(256, 512))
+            loss = loss_func(ops.upsample_bilinear(outputs, (256, 512)), label)
+        loss_sum += loss.detach().double() * n          # AverageMeter.update(loss.item(), n) without the sync (:46)
+        count += n
+    hist = meter.result()
+    acc, acc_cls, mean_iu, fwavacc, cls_iu = metrics_from_hist(hist, num_classes)
+    return mean_iu, float(loss_sum.item()) / max(count, 1), cls_iu
+
+
+def _ce_ignore_index(loss_func) -> Optional[int]:
+    """ignore_index when ``loss_func`` is a plain mean cross-entropy the fused kernel reproduces, else None."""
+    if isinstance(loss_func, _SegLoss):
+        return loss_func.ignore_index
+    if isinstance(loss_func, torch.nn.CrossEntropyLoss) and loss_func.reduction == "mean" and loss_func.weight is None \
+            and getattr(loss_func, "label_smoothing", 0.0) == 0.0:
+        return int(loss_func.ignore_index)
+    return None
+
+
+# ------------------------------------------------------------------------------------------------
+# generate_pseudo_label.py:60-96 and data/freiburg_dataset.py:108-125
+def generate_pl(net, dataloader, device, args):
+    """generate_pseudo_label.generate_pl with the reference's signature and output directory
+    (``<root>/pseudo_labels/<pseudo_type>/<checkpoint>``); the arithmetic runs in the fused kernels and the files are
+    the reference's formats (formats.generate_pl)."""
+    from . import formats
+
+    save_dir = os.path.join(args.root, 'pseudo_labels', args.pseudo_type, args.checkpoint_name.replace('.pth', ''))
+    return formats.generate_pl(net, dataloader, device, save_dir, soft=bool(args.soft), flip=bool(getattr(args, "flip", False)))
+
+
+def prepare_freiburg_labels(args, image_names: Iterable[str], device="cuda", size_wh=(700, 320), batch: int = 64):
+    """The threshold block of Freiburg.__getitem__ (data/freiburg_dataset.py:112-125) for a whole pseudo-label
+    directory, on the device: every ``<name>.png`` + ``<name>_conf.npy`` under ``args.path_lp`` goes through
+    label[conf <= thr] = ignore (fp16 compare), the {5, 11} whitelist and the PIL-NEAREST resize to the 700x320 crop
+    the dataset uses, and is written as ``<name>.png`` into ``<path_lp>_b200thr``.  Returns a copy of ``args`` with
+    ``path_lp`` pointing there and ``threshold`` cleared, so that the unmodified ``__getitem__`` (which runs in
+    DataLoader workers, where CUDA is not available) loads the finished labels and skips its numpy block."""
+    from . import formats
+
+    out_dir = os.path.normpath(args.path_lp) + "_b200thr"
+    os.makedirs(out_dir, exist_ok=True)
+    names = [os.path.basename(n) for n in image_names]
+    by_shape = {}
+    for name in names:     # label files of one size go through the kernels together
+        lab, _ = formats.read_hard_files(args.path_lp, name, with_conf=False)
+        by_shape.setdefault(lab.shape, []).append(name)
+    for group in by_shape.values():
+        for i in range(0, len(group), batch):
+            part = group[i:i + batch]
+            out = formats.load_hard_batch(args.path_lp, part, args.num_classes if hasattr(args, "num_classes") else 13, device,
+                                          threshold=args.threshold, ignore_index=args.ignore_index, keep=(5, 11), size_wh=size_wh)
+            host = out.cpu().numpy()
+            for k, name in enumerate(part):
+                formats.Image.fromarray(host[k]).save(os.path.join(out_dir, name))
+    new_args = copy.copy(args)
+    new_args.path_lp = out_dir
+    new_args.threshold = None
+    return new_args
 
 
 # ------------------------------------------------------------------------------------------------
@@ -281,7 +387,10 @@ class _SegLoss:
         self.ignore_index = ignore_index
 
     def __call__(self, input, target):
-        return ops.cross_entropy(input, target, self.ignore_index)
+        loss, bad = ops.cross_entropy_checked(input, target, self.ignore_index)
+        if STRICT_LABELS:
+            _raise_if_bad_labels(bad, "seg_loss")
+        return loss
 
 
 class SelfTrain:
@@ -331,17 +440,22 @@ class SelfTrain:
 
     # -- A12
     def rce(self, prediction, label):
+        """SelfTrain.rce (:167-174).  one_hot(label, C+1) raises on the host for labels > C or < 0, and so does this
+        (one read of the kernel's counter); a label equal to C is accepted like there."""
         lab = label.to(self.device)
-        loss, _, rce, bad = ops.ce_rce(prediction, lab, self.args.ignore_index, 0.0, 1.0)
-        if int(bad.item()) != 0:  # one_hot(label, C+1) raises in the reference (self_training.py:171)
+        _, _, rce, bad, _ = ops.ce_rce(prediction, lab, self.args.ignore_index, 0.0, 1.0)
+        if int(bad.item()) != 0:
             raise RuntimeError("Class values must be smaller than num_classes.")
         return rce
 
     def target_loss(self, logits, label):
         """self_training.py:114-118 in one forward kernel: alpha*CE + beta*RCE (or CE alone)."""
         if getattr(self.args, "rce", False):
-            return ops.ce_rce(logits, label, self.args.ignore_index, self.args.rce_alpha, self.args.rce_beta)[0]
-        return ops.cross_entropy(logits, label, self.args.ignore_index)
+            total, _, _, bad, over = ops.ce_rce(logits, label, self.args.ignore_index, self.args.rce_alpha, self.args.rce_beta)
+            if STRICT_LABELS:
+                _raise_if_bad_labels(bad + over, "SelfTrain.step target loss")
+            return total
+        return self.seg_loss(logits, label)
 
     # -- A5/A6
     def class_means(self, feat_cls, outputs, labels=None, thresh=None) -> ops.ClassMeans:
@@ -387,28 +501,32 @@ class SelfTrain:
         else:
             threshold_arg = ops.upsample_bilinear(target_lp_hard.unsqueeze(1).float(), scaled_size).long()
 
-        ema_out = None
+        ema_out = ema_feat8 = quarter = None
         if a.ema:
             with torch.no_grad():
                 ema_out = self.ema_net(target_image_full)
             quarter = (int(target_image_full.shape[2] / 4), int(target_image_full.shape[3] / 4))
-            ema_out["feat"] = ops.upsample_bilinear(ema_out["feat"], quarter)
-            ema_out["out"] = ops.upsample_bilinear(ema_out["out"], quarter)
+            ema_feat8 = ema_out["feat"].detach()        # the network's own 1/8-stride features (:66-67)
 
         target_out = self.seg_net(target_image)
         target_out["out"] = _Upsample.apply(target_out["out"], tuple(threshold_arg.shape[2:]))
         batch, _, w, h = threshold_arg.shape
         if a.proto_rectify:
+            # :69 (interpolation to the quarter map) + :82,:136-165 (full2weak, distances, weights) + :103-112
+            # (rectify) in ONE kernel reading the 1/8-stride features: no [N,K,H/4,W/4] / [N,K,64,128] tensors
             hard_lp = ops.resize_nearest_u8(target_lp_hard.to(torch.uint8), tuple(threshold_arg.shape[2:]), rule="torch")
-            feat_weak = self.full2weak(ema_out["feat"], target_weak_params)
-            threshold_arg = self.rectify_labels(feat_weak, threshold_arg, hard_lp)
+            threshold_arg = ops.prototype_distance_sampled(
+                ema_feat8, quarter, target_weak_params, self._protos(), temperature=a.proto_temperature, soft=threshold_arg,
+                hard=hard_lp, train_thred=a.train_thred, ignore_index=a.ignore_index)[2]
 
         loss_target_pseudo = self.target_loss(target_out["out"], threshold_arg.reshape([batch, w, h]))
         loss_target_pseudo.backward()
         self.optimizer_seg.step()
 
         if a.moving_prototype:
-            self.update_prototypes(ema_out["feat"].detach(), ema_out["out"].detach(), start_mean=False)
+            # :124-126 takes the class means of the INTERPOLATED maps (:69-72): those two are materialised here
+            self.update_prototypes(ops.upsample_bilinear(ema_feat8, quarter),
+                                   ops.upsample_bilinear(ema_out["out"].detach(), quarter), start_mean=False)
 
         if a.ema:
             for param_q, param_k in zip(self.seg_net.parameters(), self.ema_net.parameters()):
@@ -434,20 +552,47 @@ class _Upsample(torch.autograd.Function):
 
 
 # ------------------------------------------------------------------------------------------------
+def _hook_freiburg(cls, device="cuda") -> None:
+    """Wrap data.freiburg_dataset.Freiburg.__init__: a self-training dataset with a confidence threshold gets its
+    stored pseudo-labels thresholded / whitelisted / resized on the device once (prepare_freiburg_labels), in the
+    process that builds the dataset; __getitem__ itself stays the reference's."""
+    if getattr(cls.__init__, "_b200seg_hooked", False):
+        return
+    original = cls.__init__
+
+    def __init__(self, args, *a, **kw):
+        original(self, args, *a, **kw)
+        if getattr(self, "self_train", False) and getattr(self, "with_label", False) \
+                and getattr(args, "proto_rectify", False) and getattr(args, "threshold", None):
+            self.args = prepare_freiburg_labels(args, self.data_list, device=device)
+
+    __init__._b200seg_hooked = True
+    cls.__init__ = __init__
+
+
 def install(reference_modules: dict) -> None:
     """Rebind the reference's names to this package.  ``reference_modules`` maps module
-    names ('cal_prototype', 'self_training', 'utils.eval_tools', 'utils.loss', 'segmentation_evaluate',
-    'segmentation_train', 'utils') to the imported reference modules; absent ones are skipped."""
+    names ('cal_prototype', 'self_training', 'self_train_main', 'generate_pseudo_label', 'segmentation_evaluate',
+    'segmentation_train', 'data', 'data.freiburg_dataset', 'utils', 'utils.eval_tools', 'utils.loss', 'train') to the
+    imported reference modules; absent ones are skipped."""
     def bind(mod, name, obj):
         m = reference_modules.get(mod)
         if m is not None and hasattr(m, name):
             setattr(m, name, obj)
 
     bind("cal_prototype", "Class_Features", Class_Features)
-    bind("self_training", "SelfTrain", SelfTrain)
+    for mod in ("self_training", "self_train_main"):
+        bind(mod, "SelfTrain", SelfTrain)
     for mod in ("utils.eval_tools", "utils", "segmentation_evaluate", "segmentation_train"):
         bind(mod, "evaluate", evaluate)
         bind(mod, "_fast_hist", _fast_hist)
     for mod in ("utils.loss", "utils", "train"):
         bind(mod, "SemanticConsistency", SemanticConsistency)
         bind(mod, "FocalLoss", FocalLoss)
+    bind("generate_pseudo_label", "generate_pl", generate_pl)                      # generate_pseudo_label.py:60-96
+    for mod in ("segmentation_evaluate", "segmentation_train", "self_train_main"):
+        bind(mod, "seg_validate", seg_validate)                                    # segmentation_evaluate.py:24-80
+    for mod in ("data.freiburg_dataset", "data"):                                  # data/freiburg_dataset.py:108-125
+        m = reference_modules.get(mod)
+        if m is not None and hasattr(m, "Freiburg"):
+            _hook_freiburg(m.Freiburg)

@@ -19,6 +19,19 @@ MAX_CLASSES = 32
 PL_UP_SOFTMAX, PL_UP_ARGMAX, PL_PROB_UP, PL_PROB_UP_SOFTMAX = 0, 1, 2, 3
 FLIP_NONE, FLIP_CLASS, FLIP_WIDTH = 0, 1, 2
 UPDATE_MEAN, UPDATE_MOVING_AVERAGE = 0, 1
+HIST_AUTO, HIST_ATOMIC, HIST_PACKED = 0, 1, 2
+PL_FLAG_FORCE_TILE = 1
+DIST_DIRECT, DIST_EXPANDED = 1, 2
+
+
+def pl_flags(force_tile: bool = False, sm_warps: int = 0) -> int:
+    """`flags` of tss_pseudo_label: A/B switch of the tile kernel, warps per SM of the register-resident kernel."""
+    return (PL_FLAG_FORCE_TILE if force_tile else 0) | ((int(sm_warps) & 0xff) << 8)
+
+
+def dist_form(variant: int = 0, prefetch: int = -1, split: int = 0, algo: int = 0) -> int:
+    """`form` of tss_proto_distance (TSS_DIST_FORM): 0 everywhere = automatic."""
+    return (variant & 0xf) | (((prefetch + 1) & 0xf) << 4) | ((split & 0xf) << 8) | ((algo & 0xf) << 12)
 _DT = {torch.uint8: 0, torch.int32: 1, torch.int64: 2}
 
 
@@ -49,7 +62,7 @@ def _label_tensor(t: torch.Tensor, name: str) -> torch.Tensor:
 
 # ------------------------------------------------------------------------------------------- A14
 def confusion_matrix(pred: torch.Tensor, gt: torch.Tensor, num_classes: int,
-                     hist: Optional[torch.Tensor] = None, bad: Optional[torch.Tensor] = None):
+                     hist: Optional[torch.Tensor] = None, bad: Optional[torch.Tensor] = None, variant: int = HIST_AUTO):
     """hist[C,C] int64 (+= when given), rows = ground truth.  Returns (hist, bad_keys) device tensors."""
     pred, gt = _label_tensor(pred, "pred"), _label_tensor(gt, "gt")
     if pred.dtype != gt.dtype:
@@ -61,7 +74,7 @@ def confusion_matrix(pred: torch.Tensor, gt: torch.Tensor, num_classes: int,
     if bad is None:
         bad = torch.zeros(1, dtype=torch.int64, device=pred.device)
     check(lib().tss_confusion(_ptr(pred), _ptr(gt), _DT[pred.dtype], pred.numel(), num_classes, _ptr(hist),
-                              _ptr(bad), _stream()), "tss_confusion")
+                              _ptr(bad), int(variant), _stream()), "tss_confusion")
     return hist, bad
 
 
@@ -106,7 +119,7 @@ class PseudoLabels:
 def pseudo_label(src: torch.Tensor, size: Optional[Sequence[int]] = None, mode: int = PL_UP_SOFTMAX,
                  src_flip: Optional[torch.Tensor] = None, flip: int = FLIP_NONE, thr=None, keep=None,
                  ignore_index: int = 255, want_label: bool = True, want_conf16: bool = True,
-                 want_conf32: bool = False, want_thr: Optional[bool] = None) -> PseudoLabels:
+                 want_conf32: bool = False, want_thr: Optional[bool] = None, flags: int = 0) -> PseudoLabels:
     """Fused upsample -> softmax -> argmax/confidence -> storage casts -> threshold (tss_pseudo_label)."""
     x = _dev(src, torch.float32, "src")
     if x.dim() != 4:
@@ -132,7 +145,7 @@ def pseudo_label(src: torch.Tensor, size: Optional[Sequence[int]] = None, mode: 
                                  _ptr(conf32), _ptr(label_thr),
                                  ctypes.cast(thr_arr, ctypes.c_void_p) if thr_arr is not None else None,
                                  ctypes.cast(keep_arr, ctypes.c_void_p) if keep_arr is not None else None,
-                                 int(ignore_index), _stream()), "tss_pseudo_label")
+                                 int(ignore_index), int(flags), _stream()), "tss_pseudo_label")
     return PseudoLabels(label, conf16, conf32, label_thr)
 
 
@@ -226,20 +239,21 @@ def _check_bank(protos: torch.Tensor, num: torch.Tensor, c: int, k: int) -> None
         raise ValueError("protos %s / num %s do not match [%d,%d]" % (tuple(protos.shape), tuple(num.shape), c, k))
 
 
-def class_means(feat: torch.Tensor, logits: torch.Tensor, num_classes: int, labels_val: Optional[torch.Tensor] = None,
-                overflow_channel: Optional[int] = None, conf_thresh: Optional[float] = None,
-                use_conf_gate: bool = False, min_pixels: int = 10, update=None, scatter=None,
-                tail_stream: Optional["torch.cuda.Stream"] = None) -> ClassMeans:
-    """A5 (three launches: labels -> segmented sums -> means).  ``update=(protos, num, mode, start_mean,
-    momentum[, cap])``: the sequential prototype update A6 runs inside the third launch
-    (tss_proto_finalize_update), as cal_prototype.py:72-75 / self_training.py:124-126 chain the two.
-    ``scatter=(vectors_out, sums_out, peer_ptrs, peer_sum_ptrs)`` (image-sharded batches, sharding.PeerGather): the
-    mean vectors / their sums are written into ``vectors_out`` [N,C,K] / ``sums_out`` [N,C] (this rank's slot of the
-    local gather buffer) and through every device pointer of ``peer_ptrs`` / ``peer_sum_ptrs`` (the same slot in
-    the other GPUs' buffers) by the third launch itself.
-    ``tail_stream``: issue the third launch (13 latency-bound CTAs at cfg2) on that stream, ordered after the first
-    two, so that independent work queued next on the current stream (the confusion matrix of the same step) runs
-    beside it; the caller joins (``current_stream().wait_stream(tail_stream)``) before reading the means or the bank."""
+@dataclass
+class ClassSums:
+    """Segmented sums of one batch before the mean / validity step (tss_proto_labels + tss_proto_accumulate)."""
+    sums: torch.Tensor         # [N,C,K] fp32
+    records: torch.Tensor      # per-tile records (class-sorted pixel lists, counts)
+    seg_label: torch.Tensor    # [N,P] uint8
+    plane: int
+
+
+def class_sums(feat: torch.Tensor, logits: torch.Tensor, num_classes: int, labels_val: Optional[torch.Tensor] = None,
+               overflow_channel: Optional[int] = None, conf_thresh: Optional[float] = None, use_conf_gate: bool = False,
+               consumer_warps: int = 0) -> ClassSums:
+    """First two launches of A5: per-pixel argmax labels + tile records, then ONE streaming pass over feat.
+    ``consumer_warps=4`` selects the 160-thread form of the accumulate kernel that shares every SM with the
+    pseudo-label kernel launched with ``flags=pl_flags(sm_warps=12)`` on another stream."""
     f = _dev(feat, torch.float32, "feat")
     x = _dev(logits, torch.float32, "logits")
     n, k = f.shape[0], f.shape[1]
@@ -261,17 +275,25 @@ def class_means(feat: torch.Tensor, logits: torch.Tensor, num_classes: int, labe
                              num_classes if overflow_channel is None else int(overflow_channel),
                              1 if use_conf_gate else 0, float(-1.0 if conf_thresh is None else conf_thresh),
                              _ptr(seg), _ptr(rec), _ptr(sums), sums.numel(), st), "tss_proto_labels")
-    check(L.tss_proto_accumulate(_ptr(f), _ptr(rec), n, k, plane, num_classes, _ptr(sums), 0, st), "tss_proto_accumulate")
+    check(L.tss_proto_accumulate(_ptr(f), _ptr(rec), n, k, plane, num_classes, _ptr(sums), 0, int(consumer_warps), st),
+          "tss_proto_accumulate")
+    return ClassSums(sums, rec, seg, plane)
+
+
+def class_finalize(cs: ClassSums, min_pixels: int = 10, update=None, scatter=None) -> ClassMeans:
+    """Third launch of A5 on the current stream: means, validity rules, and either the sequential prototype update
+    (``update=(protos, num, mode, start_mean, momentum[, cap])``, tss_proto_finalize_update) or the stores into every
+    rank's gather buffer (``scatter=(vectors_out, sums_out, peer_ptrs, peer_sum_ptrs)``, tss_proto_finalize_scatter)."""
+    sums, rec, plane = cs.sums, cs.records, cs.plane
+    n, num_classes, k = sums.shape
+    dev = sums.device
+    L = lib()
+    st = _stream()
     ca = torch.empty((n, num_classes), dtype=torch.int32, device=dev)
     cg = torch.empty((n, num_classes), dtype=torch.int32, device=dev)
     vec = torch.empty_like(sums)
     valid = torch.empty((n, num_classes), dtype=torch.uint8, device=dev)
     vsum = torch.empty((n, num_classes), dtype=torch.float32, device=dev)
-    if tail_stream is not None:
-        tail_stream.wait_stream(torch.cuda.current_stream(dev))
-        for t in (rec, sums, ca, cg, vec, valid, vsum):
-            t.record_stream(tail_stream)
-        st = tail_stream.cuda_stream
     if scatter is not None:
         if update is not None:
             raise ValueError("scatter and update are exclusive (the update follows the exchange)")
@@ -299,7 +321,30 @@ def class_means(feat: torch.Tensor, logits: torch.Tensor, num_classes: int, labe
         check(L.tss_proto_finalize_update(_ptr(sums), _ptr(rec), n, num_classes, k, plane, int(min_pixels), _ptr(ca),
                                           _ptr(cg), _ptr(vec), _ptr(valid), _ptr(vsum), _ptr(protos), _ptr(num), int(mode),
                                           1 if start_mean else 0, float(momentum), cap, st), "tss_proto_finalize_update")
-    return ClassMeans(vec, valid, vsum, ca, cg, seg, sums)
+    return ClassMeans(vec, valid, vsum, ca, cg, cs.seg_label, sums)
+
+
+def class_means(feat: torch.Tensor, logits: torch.Tensor, num_classes: int, labels_val: Optional[torch.Tensor] = None,
+                overflow_channel: Optional[int] = None, conf_thresh: Optional[float] = None,
+                use_conf_gate: bool = False, min_pixels: int = 10, update=None, scatter=None,
+                tail_stream: Optional["torch.cuda.Stream"] = None, consumer_warps: int = 0) -> ClassMeans:
+    """A5 (three launches: labels -> segmented sums -> means) = class_sums + class_finalize.  ``update`` /
+    ``scatter``: see class_finalize.  ``tail_stream``: issue the third launch (13 latency-bound CTAs at cfg2) on that
+    stream, ordered after the first two, so that independent work queued next on the current stream runs beside it;
+    the caller joins (``current_stream().wait_stream(tail_stream)``) before reading the means or the bank."""
+    cs = class_sums(feat, logits, num_classes, labels_val, overflow_channel, conf_thresh, use_conf_gate, consumer_warps)
+    if tail_stream is None:
+        return class_finalize(cs, min_pixels, update, scatter)
+    cur = torch.cuda.current_stream(cs.sums.device)
+    tail_stream.wait_stream(cur)
+    with torch.cuda.stream(tail_stream):
+        out = class_finalize(cs, min_pixels, update, scatter)
+    for t in (cs.records, cs.sums):                      # allocated under `cur`, read on the tail stream
+        t.record_stream(tail_stream)
+    for t in (out.vectors, out.valid, out.vector_sum, out.count_all, out.count_gated):
+        if scatter is None or t is not out.vectors:      # allocated under the tail stream, read by the caller on `cur`
+            t.record_stream(cur)
+    return out
 
 
 def prototype_update(protos: torch.Tensor, num: torch.Tensor, means: ClassMeans, mode: int, start_mean: bool,
@@ -412,7 +457,8 @@ def full2weak(feat: torch.Tensor, weak_params) -> torch.Tensor:
 # ------------------------------------------------------------------------------------------- A7/A8/A10
 def prototype_distance(feat: torch.Tensor, protos: torch.Tensor, temperature: float = 1.0, want_dist: bool = True,
                        want_weight: bool = False, soft: Optional[torch.Tensor] = None,
-                       hard: Optional[torch.Tensor] = None, train_thred: float = 0.0, ignore_index: int = 255):
+                       hard: Optional[torch.Tensor] = None, train_thred: float = 0.0, ignore_index: int = 255,
+                       form: int = 0):
     """Returns (dist [N,C,h,w] | None, weight [N,C,h,w] | None, label [N,1,h,w] int64 | None)."""
     f = _dev(feat, torch.float32, "feat")
     p = _dev(protos, torch.float32, "protos")
@@ -437,8 +483,53 @@ def prototype_distance(feat: torch.Tensor, protos: torch.Tensor, temperature: fl
                 raise ValueError("hard must have N*h*w elements")
             hd_dt = _DT[hd.dtype]
     check(lib().tss_proto_distance(_ptr(f), _ptr(p), n, k, plane, c, float(temperature), _ptr(dist), _ptr(wt), _ptr(sf),
-                                   _ptr(hd), hd_dt, float(train_thred), int(ignore_index), _ptr(lab), _stream()),
+                                   _ptr(hd), hd_dt, float(train_thred), int(ignore_index), _ptr(lab), int(form), _stream()),
           "tss_proto_distance")
+    return dist, wt, lab
+
+
+def prototype_distance_sampled(feat8: torch.Tensor, quarter_hw: Sequence[int], weak_params, protos: torch.Tensor,
+                               temperature: float = 1.0, want_dist: bool = False, want_weight: bool = False,
+                               soft: Optional[torch.Tensor] = None, hard: Optional[torch.Tensor] = None,
+                               train_thred: float = 0.0, ignore_index: int = 255):
+    """get_prototype_weight / the rectify block on the network's own 1/8-stride features: the interpolation to the
+    quarter map (self_training.py:69) and full2weak (:145-158) are evaluated inside the distance kernel
+    (tss_proto_distance_sampled).  Returns (dist, weight, label) at the weak view's [N, ., TH, TW]."""
+    f = _dev(feat8, torch.float32, "feat8")
+    p = _dev(protos, torch.float32, "protos")
+    n, k, h8, w8 = f.shape
+    c = p.shape[0]
+    if p.shape[1] != k:
+        raise ValueError("protos [C,%d] do not match feat channels %d" % (p.shape[1], k))
+    Hq, Wq = int(quarter_hw[0]), int(quarter_hw[1])
+    table, extents = weak_param_table(weak_params, n)
+    if len(set(extents)) != 1:
+        raise RuntimeError("full2weak: crops differ in size across the batch %s (torch.cat raises in the reference)"
+                           % sorted(set(extents)))
+    th, tw = extents[0]
+    if th <= 0 or tw <= 0:
+        raise RuntimeError("full2weak: empty crop %s" % (extents[0],))
+    if (table[:, 0] < 1).any() or (table[:, 1] < 1).any():
+        raise RuntimeError("full2weak: resized extent below 1")
+    dev = f.device
+    params = torch.from_numpy(table).to(dev)
+    dist = torch.empty((n, c, th, tw), dtype=torch.float32, device=dev) if want_dist else None
+    wt = torch.empty((n, c, th, tw), dtype=torch.float32, device=dev) if want_weight else None
+    sf = hd = lab = None
+    hd_dt = 0
+    if soft is not None:
+        sf = _dev(soft, torch.float32, "soft")
+        if sf.shape != (n, c, th, tw):
+            raise ValueError("soft %s must be [N,C,h,w] = %s" % (tuple(sf.shape), (n, c, th, tw)))
+        lab = torch.empty((n, 1, th, tw), dtype=torch.int64, device=dev)
+        if hard is not None:
+            hd = _label_tensor(hard, "hard")
+            if hd.numel() != n * th * tw:
+                raise ValueError("hard must have N*h*w elements")
+            hd_dt = _DT[hd.dtype]
+    check(lib().tss_proto_distance_sampled(_ptr(f), _ptr(p), n, k, h8, w8, Hq, Wq, _ptr(params), th, tw, c, float(temperature),
+                                           _ptr(dist), _ptr(wt), _ptr(sf), _ptr(hd), hd_dt, float(train_thred),
+                                           int(ignore_index), _ptr(lab), _stream()), "tss_proto_distance_sampled")
     return dist, wt, lab
 
 
@@ -458,7 +549,7 @@ class _CeRce(torch.autograd.Function):
         plane = x[0, 0].numel()
         if t.numel() != n * plane:
             raise ValueError("target must have N*H*W elements")
-        out = torch.empty(4, dtype=torch.float64, device=x.device)
+        out = torch.empty(8, dtype=torch.float64, device=x.device)
         losses = torch.empty(3, dtype=torch.float32, device=x.device)
         # ce = sum / valid (nan when nothing is valid, as torch), rce = sum / (valid + 1e-6), total = alpha ce + beta rce:
         # formed inside the reduction launch (tss_ce_rce_fwd_mix) instead of eight scalar torch kernels
@@ -467,10 +558,10 @@ class _CeRce(torch.autograd.Function):
                                        _ptr(_loss_workspace(x.device)), _stream()), "tss_ce_rce_fwd_mix")
         ctx.save_for_backward(x, t, out)
         ctx.meta = (int(ignore_index), float(alpha), float(beta), bool(with_rce), bool(ce_sum))
-        return losses[0], losses[1], losses[2], out[3]
+        return losses[0], losses[1], losses[2], out[3], out[4]
 
     @staticmethod
-    def backward(ctx, g_total, g_ce, g_rce, _g_bad):
+    def backward(ctx, g_total, g_ce, g_rce, _g_bad, _g_over):
         x, t, out = ctx.saved_tensors
         ignore_index, alpha, beta, with_rce, ce_sum = ctx.meta
         n, c = x.shape[0], x.shape[1]
@@ -491,8 +582,17 @@ def cross_entropy(logits, target, ignore_index: int = -100, reduction: str = "me
     return _CeRce.apply(logits, target, ignore_index, 1.0, 0.0, False, reduction == "sum")[0]
 
 
+def cross_entropy_checked(logits, target, ignore_index: int = -100, reduction: str = "mean"):
+    """(loss, bad_label_count): the count (device scalar) of targets outside [0, C) other than ignore_index, which
+    torch's CrossEntropyLoss refuses (IndexError on CPU, device assert on CUDA)."""
+    out = _CeRce.apply(logits, target, ignore_index, 1.0, 0.0, False, reduction == "sum")
+    return out[0], out[3]
+
+
 def ce_rce(logits, target, ignore_index: int, alpha: float, beta: float):
-    """(alpha*CE + beta*RCE, CE, RCE, bad_label_count) -- self_training.py:114-118."""
+    """(alpha*CE + beta*RCE, CE, RCE, bad_label_count, label_equals_C_count) -- self_training.py:114-118.  A
+    label equal to C passes SelfTrain.rce's one_hot(label, C+1) (it adds -log(1e-4) sum_c p_c and counts in the
+    mask) but is out of bounds for the CE term; it is reported in the last output, never folded into CE."""
     return _CeRce.apply(logits, target, ignore_index, alpha, beta, True)
 
 
@@ -510,7 +610,7 @@ class _Focal(torch.autograd.Function):
         if x.dim() == 2:  # [M, C] rows: treat as N=M images of one pixel
             plane = 1
         a = None if alpha is None else _dev(alpha, torch.float32, "alpha")
-        out = torch.empty(4, dtype=torch.float64, device=x.device)
+        out = torch.empty(8, dtype=torch.float64, device=x.device)
         check(lib().tss_focal_fwd(_ptr(x), _ptr(t), _DT[t.dtype], n, c, plane, float(gamma), _ptr(a), _ptr(out),
                                   _ptr(_loss_workspace(x.device)), _stream()), "tss_focal_fwd")
         ctx.save_for_backward(x, t, out, a if a is not None else torch.empty(0, device=x.device))

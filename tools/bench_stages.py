@@ -76,13 +76,14 @@ def g(seed):
     return torch.Generator(device=dev).manual_seed(seed)
 
 
-def stage_pl_low(reps, N, C, h, w, H, W, tag):
+def stage_pl_low(reps, N, C, h, w, H, W, tag, sm_warps=0):
     nb = 4 * N * C * h * w
     sets = [(3.0 * torch.randn(N, C, h, w, generator=g(s), device=dev),) for s in range(copies_for(nb + 4 * N * H * W))]
     thr, keep = 0.3, ((5, 11) if C == 13 else None)
-    fn = lambda x: ops.pseudo_label(x, size=(H, W), thr=thr, keep=keep, ignore_index=C - 1 if C == 13 else 255)
+    fn = lambda x: ops.pseudo_label(x, size=(H, W), thr=thr, keep=keep, ignore_index=C - 1 if C == 13 else 255,
+                                    flags=ops.pl_flags(sm_warps=sm_warps))
     med, mn = timed(fn, sets, reps)
-    report("pl_low_" + tag, [N, C, h, w, H, W], med, mn, nb + N * H * W * 4, N * H * W, 1,
+    report("pl_low_" + tag + ("_w%d" % sm_warps if sm_warps else ""), [N, C, h, w, H, W], med, mn, nb + N * H * W * 4, N * H * W, 1,
            "XU/issue-bound (C ex2 per px), not HBM: see DESIGN.md section 4")
 
 
@@ -94,7 +95,7 @@ def stage_pl_full(reps, N, C, H, W, tag):
     report("pl_full_" + tag, [N, C, H, W], med, mn, nb + N * H * W * 4, N * H * W, 1, "HBM-bound: (4C+4) B/px")
 
 
-def stage_proto(reps, N, C, K, h, w, tag):
+def stage_proto(reps, N, C, K, h, w, tag, consumer_warps=0, sums_only=False):
     nb = 4 * N * (K + C) * h * w
     sets = []
     for s in range(copies_for(nb)):
@@ -103,13 +104,43 @@ def stage_proto(reps, N, C, K, h, w, tag):
     num = torch.zeros(C, device=dev)
 
     def fn(feat, logits):
-        ops.class_means(feat, logits, C, update=(protos, num, ops.UPDATE_MEAN, True, 0.9999))
+        if sums_only:
+            return ops.class_sums(feat, logits, C, consumer_warps=consumer_warps)
+        return ops.class_means(feat, logits, C, update=(protos, num, ops.UPDATE_MEAN, True, 0.9999), consumer_warps=consumer_warps)
     med, mn = timed(fn, sets, reps)
-    report("proto_" + tag, [N, C, K, h, w], med, mn, nb + 4 * N * C * (K + 1), N * h * w, 5,
-           "labels + accumulate + finalize + sequential update")
+    report(("sums_" if sums_only else "proto_") + tag + ("_nc%d" % consumer_warps if consumer_warps else ""), [N, C, K, h, w], med, mn,
+           nb + 4 * N * C * (K + 1), N * h * w, 2 if sums_only else 3,
+           "labels + accumulate" if sums_only else "labels + accumulate + finalize/sequential update")
 
 
-def stage_dist(reps, N, C, K, h, w, tag, rectify):
+def stage_overlap(reps, pl_warps, nc):
+    """cfg2: the pseudo-label kernel (pl_warps per SM) and labels + accumulate (nc consumer warps) on two forked capture
+    streams -- both resident on every SM -- against the same two run one after the other."""
+    N, C, K, h, w, H, W = 16, 13, 256, 81, 241, 640, 1920
+    sets = []
+    for s in range(4):
+        sets.append((3.0 * torch.randn(N, C, h, w, generator=g(s), device=dev), torch.randn(N, K, h, w, generator=g(50 + s), device=dev)))
+    side = torch.cuda.Stream(dev)
+
+    def fn(logits, feat):
+        cur = torch.cuda.current_stream(dev)
+        if pl_warps:
+            side.wait_stream(cur)
+            with torch.cuda.stream(side):
+                cs = ops.class_sums(feat, logits, C, consumer_warps=nc)
+            pl = ops.pseudo_label(logits, size=(H, W), thr=0.3, keep=(5, 11), ignore_index=12, flags=ops.pl_flags(sm_warps=pl_warps))
+            cur.wait_stream(side)
+        else:
+            pl = ops.pseudo_label(logits, size=(H, W), thr=0.3, keep=(5, 11), ignore_index=12)
+            cs = ops.class_sums(feat, logits, C, consumer_warps=nc)
+        return pl, cs
+    med, mn = timed(fn, sets, reps)
+    alg = 4 * N * C * h * w + N * H * W * 4 + 4 * N * (K + C) * h * w
+    report("overlap_pl%d_nc%d" % (pl_warps, nc) if pl_warps else "serial_pl16_nc%d" % (nc or 16), [N, C, K, h, w, H, W], med, mn, alg,
+           N * H * W, 3, "pseudo-label + labels + accumulate (no finalize, no confusion)")
+
+
+def stage_dist(reps, N, C, K, h, w, tag, rectify, form=0):
     nb = 4 * N * K * h * w
     sets = []
     for s in range(copies_for(nb)):
@@ -120,13 +151,13 @@ def stage_dist(reps, N, C, K, h, w, tag, rectify):
     protos = torch.randn(C, K, generator=g(7), device=dev)
     if rectify:
         fn = lambda f, s, hd: ops.prototype_distance(f, protos, 0.5, want_dist=False, want_weight=True, soft=s, hard=hd,
-                                                     train_thred=0.0, ignore_index=255)
+                                                     train_thred=0.0, ignore_index=255, form=form)
         alg = nb + N * h * w * (4 * C + 4 * C + 1 + 8)
     else:
-        fn = lambda f, s, hd: ops.prototype_distance(f, protos, 0.5, want_dist=True, want_weight=False)
+        fn = lambda f, s, hd: ops.prototype_distance(f, protos, 0.5, want_dist=True, want_weight=False, form=form)
         alg = nb + N * h * w * 4 * C
     med, mn = timed(fn, sets, reps)
-    report(("dist_rectify_" if rectify else "dist_") + tag, [N, C, K, h, w], med, mn, alg, N * h * w, 1,
+    report(("dist_rectify_" if rectify else "dist_") + tag + ("_form%x" % form if form else ""), [N, C, K, h, w], med, mn, alg, N * h * w, 1,
            "feat read once; weights+rectified label fused" if rectify else "distance only")
 
 
@@ -139,11 +170,11 @@ def stage_loss(reps, N, C, H, W, tag):
         sets.append((x, y))
 
     def fwd(x, y):
-        return ops.ce_rce(x, y, 255, 0.1, 1.0)
+        return ops.ce_rce(x, y, 255, 0.1, 1.0)[0]
     med, mn = timed(fwd, sets, reps)
     report("ce_rce_fwd_" + tag, [N, C, H, W], med, mn, nb + 8 * N * H * W, N * H * W, 2, "ops.ce_rce: int64 targets as the reference; includes ~8 scalar torch kernels (mean, alpha/beta mix)")
 
-    out4 = torch.empty(4, dtype=torch.float64, device=dev)
+    out4 = torch.empty(8, dtype=torch.float64, device=dev)
     wsp = torch.empty(int(ops.lib().tss_loss_workspace_bytes()), dtype=torch.uint8, device=dev)
 
     def fwd_abi(x, y):   # the two forward launches alone (sums in fp64), without the scalar torch arithmetic of ops.ce_rce
@@ -199,6 +230,21 @@ STAGES = {
     "dist_rectify_cfg3": lambda r: stage_dist(r, 2, 19, 2048, 129, 257, "cfg3_k2048", True),
     "dist_rectify_k256": lambda r: stage_dist(r, 16, 13, 256, 81, 241, "cfg2_k256", True),
     "loss_cfg2": lambda r: stage_loss(r, 4, 13, 640, 1920, "4x13x640x1920"),
+    "dist_rectify_cfg3_direct": lambda r: stage_dist(r, 2, 19, 2048, 129, 257, "cfg3_k2048", True, ops.dist_form(algo=ops.DIST_DIRECT)),
+    "dist_rectify_cfg3_8img": lambda r: stage_dist(r, 8, 19, 2048, 129, 257, "cfg3_k2048_8img", True),
+    "dist_rectify_cfg3_8img_direct": lambda r: stage_dist(r, 8, 19, 2048, 129, 257, "cfg3_k2048_8img", True, ops.dist_form(algo=ops.DIST_DIRECT)),
+    "dist_rectify_k256_direct": lambda r: stage_dist(r, 16, 13, 256, 81, 241, "cfg2_k256", True, ops.dist_form(algo=ops.DIST_DIRECT)),
+    "pl_low_cfg2_w12": lambda r: stage_pl_low(r, 16, 13, 81, 241, 640, 1920, "cfg2", 12),
+    "pl_low_cfg2_w8": lambda r: stage_pl_low(r, 16, 13, 81, 241, 640, 1920, "cfg2", 8),
+    "sums_cfg2_nc16": lambda r: stage_proto(r, 16, 13, 256, 81, 241, "cfg2_k256", 16, True),
+    "sums_cfg2_nc8": lambda r: stage_proto(r, 16, 13, 256, 81, 241, "cfg2_k256", 8, True),
+    "sums_cfg2_nc4": lambda r: stage_proto(r, 16, 13, 256, 81, 241, "cfg2_k256", 4, True),
+    "sums_cfg3_nc4": lambda r: stage_proto(r, 2, 19, 2048, 129, 257, "cfg3_k2048", 4, True),
+    "serial_cfg2": lambda r: stage_overlap(r, 0, 0),
+    "overlap_cfg2_12_4": lambda r: stage_overlap(r, 12, 4),
+    "overlap_cfg2_8_8": lambda r: stage_overlap(r, 8, 8),
+    "overlap_cfg2_8_4": lambda r: stage_overlap(r, 8, 4),
+    "overlap_cfg2_16_4": lambda r: stage_overlap(r, 16, 4),
     "hist_u8": lambda r: stage_hist(r, 2000, 256, 512, 19, torch.uint8, "cfg5_u8_2000maps"),
     "hist_u8_c13": lambda r: stage_hist(r, 64, 640, 1920, 13, torch.uint8, "cfg2_u8_c13_64maps"),
     "hist_i64": lambda r: stage_hist(r, 500, 256, 512, 19, torch.int64, "cfg5_i64_500maps"),

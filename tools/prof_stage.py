@@ -1,5 +1,5 @@
 """Run one stage of the bench step a few times (for ncu / quick timing).  usage: prof_stage.py STAGE [reps]
-STAGE in pl | proto | hist | all (the bench step) | dist | ce | distce."""
+STAGE in pl | proto | hist | all (the bench step) | overlap (pseudo-label beside labels + accumulate) | dist | ce | distce."""
 import os
 import sys
 
@@ -41,6 +41,18 @@ for i in range(reps):
         def f():
             ops.class_means(feat, logits, c["C"], update=(protos, num, ops.UPDATE_MEAN, True, 0.9999))
         timed("proto", f)
+    if stage == "overlap":
+        side = torch.cuda.Stream(dev)
+
+        def f():
+            cur = torch.cuda.current_stream(dev)
+            side.wait_stream(cur)
+            with torch.cuda.stream(side):
+                ops.class_sums(feat, logits, c["C"], consumer_warps=4)
+            ops.pseudo_label(logits, size=(c["H"], c["W"]), thr=c["thr"], keep=c["keep"], ignore_index=c["ignore"],
+                             flags=ops.pl_flags(sm_warps=12))
+            cur.wait_stream(side)
+        timed("overlap", f)
     if stage in ("hist", "all"):
         timed("hist", lambda: ops.confusion_matrix(pl0.label.reshape(-1), gt.reshape(-1), c["C"], hist, bad))
 if stage in ("dist", "distce"):
