@@ -100,6 +100,10 @@ int tss_softmax_nchw(const float* logits, float* probs, int64_t n_img, int num_c
  * run on the same SMs at the same time: tss_proto_accumulate(consumer_warps = 4)). */
 #define TSS_PL_FLAG_FORCE_TILE 1
 #define TSS_PL_FLAG_SM_WARPS(w) (((w) & 0xff) << 8)
+/* co-resident scheduling: fixed CTA size in warps (3..8), and the number of waves the rows are cut into (1..15): many
+ * small CTAs let the block scheduler refill an SM with pseudo-label CTAs as the accumulate kernel's CTAs retire */
+#define TSS_PL_FLAG_CTA_WARPS(c) (((c) & 0xf) << 16)
+#define TSS_PL_FLAG_WAVES(n) (((n) & 0xf) << 20)
 #define TSS_PL_UP_SOFTMAX 0
 #define TSS_PL_UP_ARGMAX 1
 #define TSS_PL_PROB_UP 2
@@ -226,12 +230,13 @@ int tss_proto_update_partial(const float* vectors, const uint8_t* valid, const f
  *   max_c(rect / sum_c rect) < train_thred; label = hard[px] where hard != NULL and
  *   hard[px] != ignore_index.  hard: [N,P] of hard_dtype; label_out [N,P] int64.
  * form: 0 = automatic, else TSS_DIST_FORM(variant, prefetch, split, algo) --
- *   variant  0 auto | 1 eight-warp register-pipeline kernel | 2 / 4 thread-level-parallel kernel, 2 / 4 px per lane
+ *   variant  0 auto | 1 eight-warp register-pipeline kernel | 2 / 4 thread-level-parallel kernel, 2 / 4 px per lane |
+ *            8 streaming kernel (TMA bulk copies of feat tiles + prototype slices into a shared-memory ring; expanded form)
  *   prefetch 0 auto | 1 + depth (0, 1, 2 four-channel groups) of the thread-level-parallel kernel
  *   split    0 auto | K split 1, 2, 4 (8: register-pipeline kernel only)
  *   algo     0 auto | TSS_DIST_DIRECT: sum (p - f)^2 as torch.norm does | TSS_DIST_EXPANDED: |f|^2 + |p|^2 - 2 f.p
  *            (half the FP32 work) with every (pixel, class) whose d^2 < 0.5 (|f|^2 + |p|^2) -- the cancellation
- *            region -- recomputed in the direct form; automatic = expanded for K >= 128. */
+ *            region -- recomputed in the direct form; automatic = the streaming kernel (expanded) for K >= 64. */
 #define TSS_DIST_DIRECT 1
 #define TSS_DIST_EXPANDED 2
 #define TSS_DIST_FORM(variant, prefetch_plus1, split, algo) \

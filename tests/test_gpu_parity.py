@@ -351,10 +351,13 @@ def test_finalize_scatter_writes_every_destination(ops):
     extra_s = [torch.full((n, c), -7.0, device="cuda") for _ in range(3)]
     got = ops.class_means(feat, logits, c, scatter=(out, out_s, [e.data_ptr() for e in extra], [e.data_ptr() for e in extra_s]))
     assert got.vectors.data_ptr() == out.data_ptr()
-    for t in [out] + extra:
-        assert torch.equal(t, ref.vectors)
-    for t in [out_s] + extra_s:
-        assert torch.equal(t, ref.vector_sum)
+    for t in extra:                       # every destination of ONE launch holds the same bits
+        assert torch.equal(t, out)
+    for t in extra_s:
+        assert torch.equal(t, out_s)
+    # two runs of the accumulate kernel differ in the last bits (fp32 RED.ADD order is not fixed): 1e-6, not equality
+    close_vec(out.cpu().numpy(), ref.vectors.cpu().numpy(), rtol=2e-6)
+    close_vec(out_s.cpu().numpy(), ref.vector_sum.cpu().numpy(), rtol=2e-5)   # a sum over K of values of both signs
     assert torch.equal(got.valid, ref.valid) and torch.equal(got.count_gated, ref.count_gated)
 
 
@@ -416,7 +419,7 @@ def test_distance_expanded_form_near_prototypes(ops):
     feat[0, :, 0, 0] = protos[3]                                    # exactly on a prototype: distance 0
     d_ref = O.prototype_distance(T(feat), T(protos)).numpy()
     assert d_ref[0, 3, 0, 0] == 0.0 and d_ref.min() == 0.0 and (d_ref < 0.1).mean() > 0.01
-    for form in (ops.dist_form(algo=ops.DIST_EXPANDED), ops.dist_form(2, 1, 1, ops.DIST_EXPANDED),
+    for form in (ops.dist_form(8), ops.dist_form(algo=ops.DIST_EXPANDED), ops.dist_form(2, 1, 1, ops.DIST_EXPANDED),
                  ops.dist_form(4, 0, 2, ops.DIST_EXPANDED), ops.dist_form(2, 2, 4, ops.DIST_EXPANDED), 0):
         d, wgt, _ = ops.prototype_distance(G(feat), G(protos), temperature=0.5, want_dist=True, want_weight=True, form=form)
         np.testing.assert_allclose(d.cpu().numpy(), d_ref, rtol=RTOL, atol=1e-6, err_msg="form 0x%x" % form)
@@ -424,7 +427,7 @@ def test_distance_expanded_form_near_prototypes(ops):
         np.testing.assert_allclose(wgt.cpu().numpy(), w_ref, rtol=weight_rtol(d_ref, 0.5), atol=1e-30)
 
 
-@pytest.mark.parametrize("variant", [0, 1, 2, 4])
+@pytest.mark.parametrize("variant", [0, 1, 2, 4, 8])
 @pytest.mark.parametrize("split", [0, 1, 2, 4])
 def test_distance_kernel_forms_agree(ops, variant, split):
     """every kernel form / K split / algorithm behind tss_proto_distance gives the oracle's distances (ragged plane:

@@ -491,6 +491,201 @@ __global__ void __launch_bounds__(TlpCfg<CT, PX, PF>::kThreads, 1) distance_tlp_
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Streaming form (the default for K >= 64).  The thread-level-parallel kernels above are bound by the latency of their
+// own feature loads (ncu: 7 long-scoreboard stall cycles per issued instruction, DRAM 23 %, FMA pipe 35 %): with C
+// accumulator registers per pixel a warp can keep only a few KB in flight.  Here the loads are the TMA engine's:
+// persistent CTAs, one producer warp that streams (32 channels x 512 pixels) tiles of feat -- and the matching
+// [C, 32] slice of the prototypes -- into a 3-stage shared-memory ring with 1-D bulk copies completing on mbarriers
+// (200 KB in flight per SM), and eight consumer warps that own 64 pixels each (a lane owns pixels l and l + 32 as one
+// packed pair: conflict-free scalar shared loads whatever the rows' 4-byte misalignment).  Expanded form with exact
+// recomputation (see distance_tlp_kernel): 80 FFMA2 per 4 channels and 64 pixels, so a (tile, all K) unit costs the
+// FMA pipe ~86 us at C = 19, K = 2048 -- the same as the HBM time of its 4 MB.
+constexpr int kStTP = 512;                 // pixels per tile
+constexpr int kStKC = 32;                  // channels per stage
+constexpr int kStRS = kStTP + 8;           // row stride in floats: head misalignment (3) + 16-byte round-up (3)
+constexpr int kStStages = 3;
+constexpr int kStConsumers = 8;
+constexpr int kStThreads = (kStConsumers + 1) * 32;
+
+template <int CT>
+struct StreamSmem {
+    static constexpr int stage_floats = kStKC * kStRS + CT * kStKC;
+    static constexpr int bar_off = kStStages * stage_floats * 4;
+    static constexpr int pn_off = bar_off + 2 * kStStages * 8;
+    static constexpr int total = pn_off + CT * 4 + 16;
+};
+
+template <int CT>
+__global__ void __launch_bounds__(kStThreads, 1) distance_stream_kernel(const DistArgs a, int64_t units) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    float* ring = reinterpret_cast<float*>(smem_raw);
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + StreamSmem<CT>::bar_off);
+    uint64_t* empty = full + kStStages;
+    float* pn = reinterpret_cast<float*>(smem_raw + StreamSmem<CT>::pn_off);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int64_t P = a.P, K = a.K;
+    const int64_t T = (P + kStTP - 1) / kStTP;       // tiles per image
+    const int chunks = static_cast<int>(K / kStKC);   // stages per unit
+    if (tid == 0) {
+        for (int s = 0; s < kStStages; ++s) {
+            mbar_init(&full[s], 32);
+            mbar_init(&empty[s], kStConsumers);
+        }
+        mbar_fence_init();
+    }
+    // the zero rows of the prototype slices (classes C..CT-1) are written once; bulk copies only touch rows < C
+    for (int i = tid; i < kStStages * StreamSmem<CT>::stage_floats; i += kStThreads) ring[i] = 0.f;
+    for (int c = warp; c < CT; c += kStConsumers + 1) {   // |p_c|^2 in fp64
+        double sq = 0.0;
+        if (c < a.C)
+            for (int64_t k = lane; k < K; k += 32) {
+                const double v = static_cast<double>(a.protos[c * K + k]);
+                sq += v * v;
+            }
+        sq = warp_sum_d(sq);
+        if (lane == 0) pn[c] = static_cast<float>(sq);
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    __syncthreads();
+    const int64_t total_elems = a.N * K * P;
+
+    if (warp == kStConsumers) {
+        // ===== producer: lane l stages channel row k0 + l of the tile; lanes < C also stage the prototype slice of class l
+        int stage = 0;
+        uint32_t phase = 0;
+        for (int64_t u = blockIdx.x; u < units; u += gridDim.x) {
+            const int64_t n = u / T, p0 = (u - n * T) * kStTP;
+            const int len = static_cast<int>(min(static_cast<int64_t>(kStTP), P - p0));
+            for (int ch = 0; ch < chunks; ++ch) {
+                mbar_wait(&empty[stage], phase ^ 1u);
+                float* st = ring + stage * StreamSmem<CT>::stage_floats;
+                const int64_t e0 = (n * K + static_cast<int64_t>(ch) * kStKC + lane) * P + p0;
+                const int o = static_cast<int>(e0 & 3);
+                const int64_t ea = e0 - o;
+                uint32_t nbytes = static_cast<uint32_t>(((o + len) * 4 + 15) & ~15);
+                int patch = 0;
+                if ((ea + nbytes / 4) > total_elems) {  // never read past the end of the tensor
+                    nbytes = static_cast<uint32_t>((total_elems - ea) * 4) & ~15u;
+                    patch = (o + len) - static_cast<int>(nbytes / 4);
+                }
+                float* dst = st + lane * kStRS;
+                for (int i = 0; i < patch; ++i) dst[nbytes / 4 + i] = a.feat[ea + nbytes / 4 + i];
+                if (patch) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                const uint32_t pbytes = lane < a.C ? kStKC * 4 : 0;
+                mbar_arrive_expect_tx(&full[stage], nbytes + pbytes);
+                if (nbytes) bulk_g2s(dst, a.feat + ea, nbytes, &full[stage]);
+                if (pbytes) bulk_g2s(st + kStKC * kStRS + lane * kStKC, a.protos + lane * K + static_cast<int64_t>(ch) * kStKC, pbytes, &full[stage]);
+                if (++stage == kStStages) { stage = 0; phase ^= 1u; }
+            }
+        }
+    } else {
+        // ===== consumers: warp w owns pixels [64 w, 64 w + 64) of the tile, lane l the pair (64 w + l, 64 w + l + 32)
+        int stage = 0;
+        uint32_t phase = 0;
+        const int px0 = warp * 64 + lane;
+        for (int64_t u = blockIdx.x; u < units; u += gridDim.x) {
+            const int64_t n = u / T, p0 = (u - n * T) * kStTP;
+            f32x2 acc[CT];
+#pragma unroll
+            for (int c = 0; c < CT; ++c) acc[c] = 0ull;
+            f32x2 nrm0 = 0ull, nrm1 = 0ull;
+            const unsigned emod = static_cast<unsigned>((n * K * P + p0) & 3), pm = static_cast<unsigned>(P & 3);
+            for (int ch = 0; ch < chunks; ++ch) {
+                const float* st = ring + stage * StreamSmem<CT>::stage_floats;
+                const float* ps = st + kStKC * kStRS;
+                mbar_wait(&full[stage], phase);
+#pragma unroll 2
+                for (int g = 0; g < kStKC / 4; ++g) {
+                    f32x2 xp[4];
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const unsigned k = static_cast<unsigned>(ch * kStKC + g * 4 + q);
+                        const unsigned o = (emod + k * pm) & 3u;            // this row's head misalignment
+                        const float* row = st + (g * 4 + q) * kStRS + o + px0;
+                        xp[q] = pack2(row[0], row[32]);
+                    }
+                    nrm0 = fma2(xp[0], xp[0], nrm0);
+                    nrm1 = fma2(xp[1], xp[1], nrm1);
+                    nrm0 = fma2(xp[2], xp[2], nrm0);
+                    nrm1 = fma2(xp[3], xp[3], nrm1);
+#pragma unroll
+                    for (int c = 0; c < CT; ++c) {
+                        const float4 pr = *reinterpret_cast<const float4*>(ps + c * kStKC + g * 4);
+                        acc[c] = fma2(pack2(pr.x, pr.x), xp[0], acc[c]);
+                        acc[c] = fma2(pack2(pr.y, pr.y), xp[1], acc[c]);
+                        acc[c] = fma2(pack2(pr.z, pr.z), xp[2], acc[c]);
+                        acc[c] = fma2(pack2(pr.w, pr.w), xp[3], acc[c]);
+                    }
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&empty[stage]);
+                if (++stage == kStStages) { stage = 0; phase ^= 1u; }
+            }
+            // ---- unit finished: d^2 = |f|^2 + |p|^2 - 2 f.p, exact recomputation inside the cancellation region
+            float d2[2][CT];
+            unsigned fl[2];
+            float F[2];
+            unpack2(add2(nrm0, nrm1), F[0], F[1]);
+            unsigned any = 0;
+#pragma unroll
+            for (int i = 0; i < 2; ++i) {
+                const int64_t p = p0 + px0 + 32 * i;
+                fl[i] = 0;
+#pragma unroll
+                for (int c = 0; c < CT; ++c) {
+                    float lo, hi;
+                    unpack2(acc[c], lo, hi);
+                    const float scale = F[i] + pn[c];
+                    d2[i][c] = fmaf(-2.0f, i ? hi : lo, scale);
+                    if (p < P && c < a.C && d2[i][c] < kExpTheta * scale) fl[i] |= 1u << c;
+                }
+                any |= fl[i];
+            }
+            if (__any_sync(0xffffffffu, any != 0)) {
+#pragma unroll
+                for (int i = 0; i < 2; ++i) {
+                    unsigned pend = __ballot_sync(0xffffffffu, fl[i] != 0);
+                    while (pend) {
+                        const int src = __ffs(pend) - 1;
+                        pend &= pend - 1;
+                        const unsigned m = __shfl_sync(0xffffffffu, fl[i], src);
+                        const int pp = __shfl_sync(0xffffffffu, static_cast<int>(p0 + px0 + 32 * i), src);
+                        float ex[CT];
+                        exact_d2_pixel<CT>(a, n, pp, m, ex);
+                        if (lane == src) {
+#pragma unroll
+                            for (int c = 0; c < CT; ++c)
+                                if ((m >> c) & 1u) d2[i][c] = ex[c];
+                        }
+                    }
+                }
+            }
+#pragma unroll
+            for (int i = 0; i < 2; ++i) {
+                const int64_t p = p0 + px0 + 32 * i;
+                if (p < P) {
+                    float d[CT];
+#pragma unroll
+                    for (int c = 0; c < CT; ++c) d[c] = sqrtf(fmaxf(d2[i][c], 0.f));
+                    distance_epilogue<CT>(a, d, n, p);
+                }
+            }
+        }
+    }
+}
+
+template <int CT>
+static int launch_distance_stream(DistArgs& a, cudaStream_t st) {
+    cudaError_t e = cudaFuncSetAttribute(distance_stream_kernel<CT>, cudaFuncAttributeMaxDynamicSharedMemorySize, StreamSmem<CT>::total);
+    if (e != cudaSuccess) return cuda_status(e, "tss_proto_distance: smem attribute");
+    const int64_t units = a.N * ((a.P + kStTP - 1) / kStTP);
+    const unsigned grid = static_cast<unsigned>(units < kNumSMs ? units : kNumSMs);
+    distance_stream_kernel<CT><<<grid, kStThreads, StreamSmem<CT>::total, st>>>(a, units);
+    TSS_LAUNCH_CHECK("tss_proto_distance(stream)");
+    return TSS_OK;
+}
+
 // Relative cost of one (PX, SI) form on this problem: rounds of the persistent loop on the busiest warp x channel
 // steps per round (+ a per-unit constant) x pixels a round retires per SM x the measured per-pixel-channel cost of
 // the form (4 px per lane holds fewer warps: x1.05; 8-lane parts fetch 32-byte pieces of a row: x1.05).  B200
@@ -524,7 +719,7 @@ static int launch_distance_tlp(DistArgs& a, int SI, cudaStream_t st) {
 
 // `form` of tss_proto_distance (0 = everything automatic), see include/tss_b200.h
 struct DistForm {
-    int variant;    // 0 automatic, 1 = 8-warp register-pipeline kernel, 2 / 4 = thread-level-parallel kernel with 2 / 4 px per lane
+    int variant;    // 0 automatic, 1 = 8-warp register-pipeline kernel, 2 / 4 = thread-level-parallel kernel with 2 / 4 px per lane, 8 = streaming kernel
     int prefetch;   // -1 automatic, 0 / 1 / 2 = register prefetch depth in 4-channel groups
     int split;      // 0 automatic, else the K split
     int algo;       // 0 automatic, 1 direct difference, 2 expanded with exact recomputation
@@ -578,6 +773,9 @@ static int launch_distance_auto(DistArgs& a, const DistForm& fm, cudaStream_t st
 template <int CT>
 static int launch_distance(DistArgs& a, int form, cudaStream_t st) {
     const DistForm fm = decode_form(form);
+    const bool aligned = ((reinterpret_cast<uintptr_t>(a.feat) | reinterpret_cast<uintptr_t>(a.protos)) & 15) == 0;   // bulk copies
+    if (aligned && (fm.variant == 8 || (fm.variant == 0 && fm.algo != 1 && fm.prefetch < 0 && fm.split == 0 && a.K >= 64)))
+        return launch_distance_stream<CT>(a, st);
     {
         const int r = launch_distance_auto<CT>(a, fm, st);
         if (r != -1) return r;
@@ -769,7 +967,7 @@ extern "C" int tss_proto_distance(const float* feat, const float* protos, int64_
     TSS_REQUIRE(n_img >= 0 && plane > 0 && plane < (1ll << 31) && channels > 0, TSS_E_ARG, "tss_proto_distance: bad extents");
     {
         const DistForm fm = decode_form(form);
-        TSS_REQUIRE(form >= 0 && form < (1 << 16) && (fm.variant == 0 || fm.variant == 1 || fm.variant == 2 || fm.variant == 4) &&
+        TSS_REQUIRE(form >= 0 && form < (1 << 16) && (fm.variant == 0 || fm.variant == 1 || fm.variant == 2 || fm.variant == 4 || fm.variant == 8) &&
                     fm.prefetch <= 2 && (fm.split == 0 || fm.split == 1 || fm.split == 2 || fm.split == 4 || fm.split == 8) &&
                     fm.algo <= 2, TSS_E_ARG, "tss_proto_distance: bad form 0x%x", form);
     }

@@ -657,6 +657,11 @@ extern "C" int tss_proto_labels(const float* logits, const float* labels_val, in
     const int64_t tiles = (plane + kPT - 1) / kPT;
     dim3 grid(static_cast<unsigned>(tiles), static_cast<unsigned>(n_img));
     auto* rec = static_cast<TileRecord*>(records);
+    // the 228 KB shared-memory split of the accumulate kernel that follows: this kernel then runs beside it (and beside a
+    // co-resident pseudo-label kernel) on the same SMs instead of waiting for a reconfiguration
+    cudaFuncSetAttribute(proto_label_kernel<13>, cudaFuncAttributePreferredSharedMemoryCarveout, static_cast<int>(cudaSharedmemCarveoutMaxShared));
+    cudaFuncSetAttribute(proto_label_kernel<19>, cudaFuncAttributePreferredSharedMemoryCarveout, static_cast<int>(cudaSharedmemCarveoutMaxShared));
+    cudaFuncSetAttribute(proto_label_kernel<TSS_MAX_CLASSES>, cudaFuncAttributePreferredSharedMemoryCarveout, static_cast<int>(cudaSharedmemCarveoutMaxShared));
     if (num_classes <= 13)
         proto_label_kernel<13><<<grid, 256, 0, st>>>(logits, labels_val, num_classes, plane, overflow_channel, use_conf_gate, conf_thresh, seg_label, rec, sums_to_zero, sums_elems);
     else if (num_classes <= 19)
@@ -684,6 +689,7 @@ static int launch_accum_nc(int nc, const float* feat, const TileRecord* rec, int
                            cudaStream_t st) {
     switch (nc) {
         case 4: return launch_accum<CT, 4>(feat, rec, N, K, P, C, sums, st);
+        case 6: return launch_accum<CT, 6>(feat, rec, N, K, P, C, sums, st);
         case 8: return launch_accum<CT, 8>(feat, rec, N, K, P, C, sums, st);
         default: return launch_accum<CT, 16>(feat, rec, N, K, P, C, sums, st);
     }
@@ -700,8 +706,8 @@ extern "C" int tss_proto_accumulate(const float* feat, const void* records, int6
     TSS_REQUIRE(num_classes >= 1 && num_classes <= TSS_MAX_CLASSES, TSS_E_CLASSES, "tss_proto_accumulate: num_classes %d", num_classes);
     TSS_REQUIRE((reinterpret_cast<uintptr_t>(feat) & 15) == 0 && (reinterpret_cast<uintptr_t>(records) & 15) == 0, TSS_E_ALIGN,
                 "tss_proto_accumulate: feat and records must be 16-byte aligned");
-    TSS_REQUIRE(consumer_warps == 0 || consumer_warps == 4 || consumer_warps == 8 || consumer_warps == 16, TSS_E_ARG,
-                "tss_proto_accumulate: consumer_warps must be 0 (default 16), 4, 8 or 16");
+    TSS_REQUIRE(consumer_warps == 0 || consumer_warps == 4 || consumer_warps == 6 || consumer_warps == 8 || consumer_warps == 16, TSS_E_ARG,
+                "tss_proto_accumulate: consumer_warps must be 0 (default 16), 4, 6, 8 or 16");
     if (n_img == 0) return TSS_OK;
     cudaStream_t st = as_stream(stream);
     if (zero_sums) {

@@ -567,24 +567,29 @@ static int launch_direct(const PLArgs& a, int64_t n_img, cudaStream_t st) {
 }
 
 template <int C, int MODE>
-static int launch_up(const PLArgs& a, int64_t n_img, int sm_warps, cudaStream_t st) {
-    // One wave.  The kernel is compiled for a register cap that lets an SM hold UpCfg<C>::kWarpsPerSM warps;
-    // pick the warps per CTA that wastes the fewest column slots and keeps the SM fullest.  sm_warps (0 = all)
-    // sizes the wave for fewer warps per SM, leaving registers for a co-resident kernel (the accumulate
-    // kernel of the prototype stage, which is HBM-bound while this one is XU/issue-bound).
+static int launch_up(const PLArgs& a, int64_t n_img, int flags, cudaStream_t st) {
+    // The kernel is compiled for a register cap that lets an SM hold UpCfg<C>::kWarpsPerSM warps.  Default: ONE wave,
+    // with the warps per CTA that wastes the fewest column slots and keeps the SM fullest.
+    // flags (co-resident forms, see include/tss_b200.h): sm_warps sizes the wave for fewer warps per SM, leaving
+    // registers for a co-resident kernel (the accumulate kernel of the prototype stage, which is HBM-bound while this
+    // one is XU / issue bound); cta_warps fixes the CTA size and waves > 1 cuts the rows into that many times more
+    // segments than CTA slots, so that the block scheduler refills an SM with pseudo-label CTAs as the co-resident
+    // kernel's CTAs retire (a row segment still spans dozens of output rows: its two start-up row loads stay < 1 %).
+    const int sm_warps = (flags >> 8) & 0xff, cta_warps = (flags >> 16) & 0xf, waves = ((flags >> 20) & 0xf) ? ((flags >> 20) & 0xf) : 1;
     const int col_blocks = (a.W + kUpBlockPx - 1) / kUpBlockPx;
     int best_wpc = 8, best_cps = 2;
     double best_eff = -1.0;
-    const int kW = (sm_warps >= 4 && sm_warps < UpCfg<C>::kWarpsPerSM) ? sm_warps : UpCfg<C>::kWarpsPerSM;
-    for (int wpc = 4; wpc <= kW; ++wpc) {
+    const int kW = (sm_warps >= 3 && sm_warps < UpCfg<C>::kWarpsPerSM) ? sm_warps : UpCfg<C>::kWarpsPerSM;
+    for (int wpc = (cta_warps ? cta_warps : 4); wpc <= (cta_warps ? cta_warps : kW); ++wpc) {
         const int cps = kW / wpc;                                  // CTAs per SM by registers
+        if (cps < 1) break;
         const int gx = (col_blocks + wpc - 1) / wpc;
         const double eff = (static_cast<double>(col_blocks) / (gx * wpc)) * (cps * wpc / static_cast<double>(kW));
         if (eff > best_eff + 1e-9) { best_eff = eff; best_wpc = wpc; best_cps = cps; }
     }
     const int gx = (col_blocks + best_wpc - 1) / best_wpc;
     const int64_t total_rows = n_img * a.H;
-    int64_t segs = static_cast<int64_t>(kNumSMs) * best_cps / gx;  // CTA slots / CTAs per row segment
+    int64_t segs = static_cast<int64_t>(kNumSMs) * best_cps * waves / gx;  // CTA slots (x waves) / CTAs per row segment
     if (segs < 1) segs = 1;
     int64_t rps = (total_rows + segs - 1) / segs;
     if (rps < 1) rps = 1;
@@ -595,12 +600,24 @@ static int launch_up(const PLArgs& a, int64_t n_img, int sm_warps, cudaStream_t 
     const bool coop = (a.sx * 63.0f + 3.0f) < 32.0f;
     const bool pl_outs = MODE == TSS_PL_UP_SOFTMAX && a.label && a.conf16 && !a.conf32 && a.label_thr;
     const int block = best_wpc * 32, r = static_cast<int>(rps);
+    // Co-resident form: the accumulate kernel that shares the SMs needs the 228 KB shared-memory configuration, and an
+    // SM cannot hold CTAs of two kernels that ask for different L1 / shared splits -- so this kernel (which uses no
+    // shared memory) asks for the same split; on its own it keeps the default (largest L1).
+    const int carve = (sm_warps > 0 || cta_warps > 0) ? static_cast<int>(cudaSharedmemCarveoutMaxShared) : static_cast<int>(cudaSharedmemCarveoutDefault);
+    auto go = [&](auto kern) -> cudaError_t {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
+        if (e != cudaSuccess) return e;
+        kern<<<grid, block, 0, st>>>(a, total_rows, r, col_blocks);
+        return cudaSuccess;
+    };
+    cudaError_t e;
     if (coop && pl_outs)
-        pl_up_kernel<C, MODE, true, MODE == TSS_PL_UP_SOFTMAX ? kOutsPseudoLabel : kOutsRuntime><<<grid, block, 0, st>>>(a, total_rows, r, col_blocks);
+        e = go(pl_up_kernel<C, MODE, true, MODE == TSS_PL_UP_SOFTMAX ? kOutsPseudoLabel : kOutsRuntime>);
     else if (coop)
-        pl_up_kernel<C, MODE, true, kOutsRuntime><<<grid, block, 0, st>>>(a, total_rows, r, col_blocks);
+        e = go(pl_up_kernel<C, MODE, true, kOutsRuntime>);
     else
-        pl_up_kernel<C, MODE, false, kOutsRuntime><<<grid, block, 0, st>>>(a, total_rows, r, col_blocks);
+        e = go(pl_up_kernel<C, MODE, false, kOutsRuntime>);
+    if (e != cudaSuccess) return cuda_status(e, "tss_pseudo_label: carveout attribute");
     TSS_LAUNCH_CHECK("tss_pseudo_label(up)");
     return TSS_OK;
 }
@@ -614,6 +631,7 @@ extern "C" int tss_pseudo_label(const float* src, const float* src_flip, int64_t
     using namespace tss;
     const int g_pl_force_tile = (flags & TSS_PL_FLAG_FORCE_TILE) ? 1 : 0;
     const int sm_warps = (flags >> 8) & 0xff;
+    TSS_REQUIRE((flags >> 24) == 0 && flags >= 0, TSS_E_ARG, "tss_pseudo_label: bad flags 0x%x", flags);
     TSS_REQUIRE(src != nullptr, TSS_E_ARG, "tss_pseudo_label: null src");
     TSS_REQUIRE(n_img >= 0 && h > 0 && w > 0 && H > 0 && W > 0, TSS_E_ARG, "tss_pseudo_label: bad extents");
     TSS_REQUIRE(n_img <= 65535, TSS_E_ARG, "tss_pseudo_label: at most 65535 images per call");
@@ -655,10 +673,10 @@ extern "C" int tss_pseudo_label(const float* src, const float* src_flip, int64_t
         (W % 2 == 0) && W >= 2 && al(label_out, 2) && al(conf16_out, 4) && al(conf32_out, 8) && al(label_thr_out, 2) &&
         (num_classes == 13 || num_classes == 19) && static_cast<int64_t>(num_classes) * h * w < (1ll << 30)) {
         if (num_classes == 13)
-            return mode == TSS_PL_UP_SOFTMAX ? launch_up<13, TSS_PL_UP_SOFTMAX>(a, n_img, sm_warps, st)
-                                             : launch_up<13, TSS_PL_UP_ARGMAX>(a, n_img, sm_warps, st);
-        return mode == TSS_PL_UP_SOFTMAX ? launch_up<19, TSS_PL_UP_SOFTMAX>(a, n_img, sm_warps, st)
-                                         : launch_up<19, TSS_PL_UP_ARGMAX>(a, n_img, sm_warps, st);
+            return mode == TSS_PL_UP_SOFTMAX ? launch_up<13, TSS_PL_UP_SOFTMAX>(a, n_img, flags, st)
+                                             : launch_up<13, TSS_PL_UP_ARGMAX>(a, n_img, flags, st);
+        return mode == TSS_PL_UP_SOFTMAX ? launch_up<19, TSS_PL_UP_SOFTMAX>(a, n_img, flags, st)
+                                         : launch_up<19, TSS_PL_UP_ARGMAX>(a, n_img, flags, st);
     }
 
     // tile height: the largest of {64,32,16,8} whose staged rows fit the shared-memory budget

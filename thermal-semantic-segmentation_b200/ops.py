@@ -24,9 +24,17 @@ PL_FLAG_FORCE_TILE = 1
 DIST_DIRECT, DIST_EXPANDED = 1, 2
 
 
-def pl_flags(force_tile: bool = False, sm_warps: int = 0) -> int:
-    """`flags` of tss_pseudo_label: A/B switch of the tile kernel, warps per SM of the register-resident kernel."""
-    return (PL_FLAG_FORCE_TILE if force_tile else 0) | ((int(sm_warps) & 0xff) << 8)
+def pl_flags(force_tile: bool = False, sm_warps: int = 0, cta_warps: int = 0, waves: int = 0) -> int:
+    """`flags` of tss_pseudo_label: A/B switch of the tile kernel; warps per SM, warps per CTA and number of waves of
+    the register-resident kernel (co-resident forms)."""
+    return (PL_FLAG_FORCE_TILE if force_tile else 0) | ((int(sm_warps) & 0xff) << 8) | ((int(cta_warps) & 0xf) << 16) | \
+        ((int(waves) & 0xf) << 20)
+
+
+# The co-resident step form measured best on B200 at the cfg2 shape (profiles/r02_overlap_sweep.txt): pseudo-label kernel
+# in 3-warp CTAs, two waves, up to 15 warps per SM; accumulate kernel with 6 consumer warps on a high-priority stream
+CORESIDENT_PL_FLAGS = pl_flags(sm_warps=15, cta_warps=3, waves=2)
+CORESIDENT_CONSUMERS = 6
 
 
 def dist_form(variant: int = 0, prefetch: int = -1, split: int = 0, algo: int = 0) -> int:
@@ -250,10 +258,13 @@ class ClassSums:
 
 def class_sums(feat: torch.Tensor, logits: torch.Tensor, num_classes: int, labels_val: Optional[torch.Tensor] = None,
                overflow_channel: Optional[int] = None, conf_thresh: Optional[float] = None, use_conf_gate: bool = False,
-               consumer_warps: int = 0) -> ClassSums:
+               consumer_warps: int = 0, accumulate_stream: Optional["torch.cuda.Stream"] = None) -> ClassSums:
     """First two launches of A5: per-pixel argmax labels + tile records, then ONE streaming pass over feat.
-    ``consumer_warps=4`` selects the 160-thread form of the accumulate kernel that shares every SM with the
-    pseudo-label kernel launched with ``flags=pl_flags(sm_warps=12)`` on another stream."""
+    ``consumer_warps`` 4 / 6 / 8 select the smaller forms of the accumulate kernel that share every SM with the
+    pseudo-label kernel (``flags=pl_flags(...)``) running on another stream.  ``accumulate_stream``: the label kernel
+    runs on the current stream, the accumulate kernel on that stream (ordered after it); work queued next on the
+    current stream runs beside the accumulate kernel, and the caller joins
+    (``current_stream().wait_stream(accumulate_stream)``) before anything reads the sums."""
     f = _dev(feat, torch.float32, "feat")
     x = _dev(logits, torch.float32, "logits")
     n, k = f.shape[0], f.shape[1]
@@ -275,6 +286,11 @@ def class_sums(feat: torch.Tensor, logits: torch.Tensor, num_classes: int, label
                              num_classes if overflow_channel is None else int(overflow_channel),
                              1 if use_conf_gate else 0, float(-1.0 if conf_thresh is None else conf_thresh),
                              _ptr(seg), _ptr(rec), _ptr(sums), sums.numel(), st), "tss_proto_labels")
+    if accumulate_stream is not None:
+        accumulate_stream.wait_stream(torch.cuda.current_stream(dev))
+        st = accumulate_stream.cuda_stream
+        for t in (f, rec, sums):
+            t.record_stream(accumulate_stream)
     check(L.tss_proto_accumulate(_ptr(f), _ptr(rec), n, k, plane, num_classes, _ptr(sums), 0, int(consumer_warps), st),
           "tss_proto_accumulate")
     return ClassSums(sums, rec, seg, plane)

@@ -41,7 +41,7 @@ class HostLabelPipeline:
         self.features = dropin.Class_Features(self.dev, self.C, self.K)
         self.meter = dropin.ConfusionMeter(self.C, self.dev)
         self.s_in, self.s_out = torch.cuda.Stream(self.dev), torch.cuda.Stream(self.dev)
-        self.s_side, self.s_tail = torch.cuda.Stream(self.dev), torch.cuda.Stream(self.dev)
+        self.s_side, self.s_tail = torch.cuda.Stream(self.dev, priority=-1), torch.cuda.Stream(self.dev)
         self._in = [None] * self.SLOTS          # device input slots (allocated at first submit)
         self._ready = [torch.cuda.Event() for _ in range(self.SLOTS)]
         self._free = [torch.cuda.Event() for _ in range(self.SLOTS)]
@@ -79,17 +79,14 @@ class HostLabelPipeline:
             self._ready[s].record(self.s_in)
         cur.wait_event(self._ready[s])
         if self.overlap:
-            # pseudo-labels (XU / issue bound, 12 warps per SM) and the segmented sums (HBM bound, 5 warps per SM) at once
-            self.s_side.wait_stream(cur)
-            with torch.cuda.stream(self.s_side):
-                cs = ops.class_sums(d_feat, d_logits, self.C, overflow_channel=self.C, consumer_warps=4)
+            # pseudo-labels (XU / issue bound) and the segmented sums (HBM bound) on the same SMs at the same time
+            cs = ops.class_sums(d_feat, d_logits, self.C, overflow_channel=self.C, consumer_warps=ops.CORESIDENT_CONSUMERS,
+                                accumulate_stream=self.s_side)
             pl = ops.pseudo_label(d_logits, size=self.size, thr=self.thr, keep=self.keep, ignore_index=self.ignore,
-                                  flags=ops.pl_flags(sm_warps=12))
+                                  flags=ops.CORESIDENT_PL_FLAGS)
             if gt is not None:
                 self.meter.add(pl.label, d_gt)
             cur.wait_stream(self.s_side)
-            for t in (cs.sums, cs.records, cs.seg_label):
-                t.record_stream(cur)
         else:
             pl = dropin.pseudo_label_batch(d_logits, size=self.size, thr=self.thr, keep=self.keep, ignore_index=self.ignore)
             cs = ops.class_sums(d_feat, d_logits, self.C, overflow_channel=self.C)

@@ -76,15 +76,23 @@ def g(seed):
     return torch.Generator(device=dev).manual_seed(seed)
 
 
-def stage_pl_low(reps, N, C, h, w, H, W, tag, sm_warps=0):
+def stage_pl_low(reps, N, C, h, w, H, W, tag, sm_warps=0, cta_warps=0, waves=0):
     nb = 4 * N * C * h * w
     sets = [(3.0 * torch.randn(N, C, h, w, generator=g(s), device=dev),) for s in range(copies_for(nb + 4 * N * H * W))]
     thr, keep = 0.3, ((5, 11) if C == 13 else None)
     fn = lambda x: ops.pseudo_label(x, size=(H, W), thr=thr, keep=keep, ignore_index=C - 1 if C == 13 else 255,
-                                    flags=ops.pl_flags(sm_warps=sm_warps))
+                                    flags=ops.pl_flags(sm_warps=sm_warps, cta_warps=cta_warps, waves=waves))
     med, mn = timed(fn, sets, reps)
     report("pl_low_" + tag + ("_w%d" % sm_warps if sm_warps else ""), [N, C, h, w, H, W], med, mn, nb + N * H * W * 4, N * H * W, 1,
            "XU/issue-bound (C ex2 per px), not HBM: see DESIGN.md section 4")
+
+
+def stage_pl_argmax(reps, N, C, h, w, H, W, tag):
+    nb = 4 * N * C * h * w
+    sets = [(3.0 * torch.randn(N, C, h, w, generator=g(s), device=dev),) for s in range(copies_for(nb + 4 * N * H * W))]
+    fn = lambda x: ops.pseudo_label(x, size=(H, W), mode=ops.PL_UP_ARGMAX, want_conf16=False)
+    med, mn = timed(fn, sets, reps)
+    report("pl_argmax_" + tag, [N, C, h, w, H, W], med, mn, nb + N * H * W, N * H * W, 1, "upsample + argmax only (no exponentials)")
 
 
 def stage_pl_full(reps, N, C, H, W, tag):
@@ -113,22 +121,38 @@ def stage_proto(reps, N, C, K, h, w, tag, consumer_warps=0, sums_only=False):
            "labels + accumulate" if sums_only else "labels + accumulate + finalize/sequential update")
 
 
-def stage_overlap(reps, pl_warps, nc):
+def stage_overlap(reps, pl_warps, nc, cta_warps=0, waves=0, prio=False, label_first=False):
     """cfg2: the pseudo-label kernel (pl_warps per SM) and labels + accumulate (nc consumer warps) on two forked capture
     streams -- both resident on every SM -- against the same two run one after the other."""
     N, C, K, h, w, H, W = 16, 13, 256, 81, 241, 640, 1920
     sets = []
     for s in range(4):
         sets.append((3.0 * torch.randn(N, C, h, w, generator=g(s), device=dev), torch.randn(N, K, h, w, generator=g(50 + s), device=dev)))
-    side = torch.cuda.Stream(dev)
+    side = torch.cuda.Stream(dev, priority=-1) if prio else torch.cuda.Stream(dev)
 
     def fn(logits, feat):
         cur = torch.cuda.current_stream(dev)
         if pl_warps:
+            fl = ops.pl_flags(sm_warps=pl_warps, cta_warps=cta_warps, waves=waves)
+            if label_first:   # the label kernel alone first, then accumulate and pseudo-label become ready together
+                from b200seg.ops import _ptr, _stream, check, lib
+                import ctypes
+                n, k, plane = feat.shape[0], feat.shape[1], feat[0, 0].numel()
+                L = lib()
+                rec = torch.empty(int(L.tss_proto_records_bytes(n, plane)), dtype=torch.uint8, device=dev)
+                seg = torch.empty((n, plane), dtype=torch.uint8, device=dev)
+                sums = torch.empty((n, C, k), dtype=torch.float32, device=dev)
+                check(L.tss_proto_labels(_ptr(logits), None, n, C, plane, C, 0, -1.0, _ptr(seg), _ptr(rec), _ptr(sums), sums.numel(), _stream()), "labels")
+                side.wait_stream(cur)
+                with torch.cuda.stream(side):
+                    check(L.tss_proto_accumulate(_ptr(feat), _ptr(rec), n, k, plane, C, _ptr(sums), 0, nc, _stream()), "acc")
+                pl = ops.pseudo_label(logits, size=(H, W), thr=0.3, keep=(5, 11), ignore_index=12, flags=fl)
+                cur.wait_stream(side)
+                return pl, sums
             side.wait_stream(cur)
             with torch.cuda.stream(side):
                 cs = ops.class_sums(feat, logits, C, consumer_warps=nc)
-            pl = ops.pseudo_label(logits, size=(H, W), thr=0.3, keep=(5, 11), ignore_index=12, flags=ops.pl_flags(sm_warps=pl_warps))
+            pl = ops.pseudo_label(logits, size=(H, W), thr=0.3, keep=(5, 11), ignore_index=12, flags=fl)
             cur.wait_stream(side)
         else:
             pl = ops.pseudo_label(logits, size=(H, W), thr=0.3, keep=(5, 11), ignore_index=12)
@@ -136,7 +160,9 @@ def stage_overlap(reps, pl_warps, nc):
         return pl, cs
     med, mn = timed(fn, sets, reps)
     alg = 4 * N * C * h * w + N * H * W * 4 + 4 * N * (K + C) * h * w
-    report("overlap_pl%d_nc%d" % (pl_warps, nc) if pl_warps else "serial_pl16_nc%d" % (nc or 16), [N, C, K, h, w, H, W], med, mn, alg,
+    tag = "overlap_pl%d_nc%d" % (pl_warps, nc) + ("_cta%d_wv%d" % (cta_warps, waves) if cta_warps else "") + ("_prio" if prio else "") + \
+        ("_lf" if label_first else "")
+    report(tag if pl_warps else "serial_pl16_nc%d" % (nc or 16), [N, C, K, h, w, H, W], med, mn, alg,
            N * H * W, 3, "pseudo-label + labels + accumulate (no finalize, no confusion)")
 
 
@@ -219,7 +245,31 @@ def stage_hist(reps, n_maps, H, W, C, dtype, tag):
     report("hist_" + tag, [n_maps, H, W, C, str(dtype)], med, mn, 2 * n * es, n, 1, "%d B/px" % (2 * es))
 
 
+def stage_dist_sweep(reps, N, C, K, h, w, tag):
+    for algo in (ops.DIST_EXPANDED,):
+        for variant in (2, 4):
+            for pf in ((0, 1, 2) if variant == 2 else (0, 1)):
+                for split in (1, 2, 4):
+                    stage_dist(reps, N, C, K, h, w, tag, True, ops.dist_form(variant, pf, split, algo))
+
+
 STAGES = {
+    "dist_stream_cfg3": lambda r: stage_dist(r, 2, 19, 2048, 129, 257, "cfg3_2img", True, ops.dist_form(8)),
+    "dist_stream_cfg3_8": lambda r: stage_dist(r, 8, 19, 2048, 129, 257, "cfg3_8img", True, ops.dist_form(8)),
+    "dist_stream_cfg3_4": lambda r: stage_dist(r, 4, 19, 2048, 129, 257, "cfg3_4img", True, ops.dist_form(8)),
+    "dist_stream_k256": lambda r: stage_dist(r, 16, 13, 256, 81, 241, "k256", True, ops.dist_form(8)),
+    "dist_tlp_k256_best": lambda r: stage_dist(r, 16, 13, 256, 81, 241, "k256", True, ops.dist_form(2, 2, 1, 2)),
+    "ov_15_6_c3w2": lambda r: stage_overlap(r, 15, 6, 3, 2, False, False),
+    "ov_15_6_c3w2_p": lambda r: stage_overlap(r, 15, 6, 3, 2, True, False),
+    "ov_15_6_c3w3_plf": lambda r: stage_overlap(r, 15, 6, 3, 3, True, True),
+    "ov_15_6_c3w4_plf": lambda r: stage_overlap(r, 15, 6, 3, 4, True, True),
+    "ov_16_6_c4w2_plf": lambda r: stage_overlap(r, 16, 6, 4, 2, True, True),
+    "ov_15_6_c5w2_plf": lambda r: stage_overlap(r, 15, 6, 5, 2, True, True),
+    "ov_12_6_c3w2_plf": lambda r: stage_overlap(r, 12, 6, 3, 2, True, True),
+    "ov_15_6_c3w1_plf": lambda r: stage_overlap(r, 15, 6, 3, 1, True, True),
+    "dist_sweep_cfg3": lambda r: stage_dist_sweep(r, 2, 19, 2048, 129, 257, "cfg3_2img"),
+    "dist_sweep_cfg3_8": lambda r: stage_dist_sweep(r, 8, 19, 2048, 129, 257, "cfg3_8img"),
+    "dist_sweep_k256": lambda r: stage_dist_sweep(r, 16, 13, 256, 81, 241, "k256"),
     "pl_low_cfg2": lambda r: stage_pl_low(r, 16, 13, 81, 241, 640, 1920, "cfg2"),
     "pl_low_city": lambda r: stage_pl_low(r, 4, 19, 129, 257, 1024, 2048, "cityscapes19"),
     "pl_full_cfg2": lambda r: stage_pl_full(r, 16, 13, 640, 1920, "cfg2"),
@@ -242,6 +292,23 @@ STAGES = {
     "sums_cfg3_nc4": lambda r: stage_proto(r, 2, 19, 2048, 129, 257, "cfg3_k2048", 4, True),
     "serial_cfg2": lambda r: stage_overlap(r, 0, 0),
     "overlap_cfg2_12_4": lambda r: stage_overlap(r, 12, 4),
+    "ov_15_8_c3w2": lambda r: stage_overlap(r, 15, 8, 3, 2),
+    "ov_15_8_c3w2_p": lambda r: stage_overlap(r, 15, 8, 3, 2, True),
+    "ov_15_8_c3w2_plf": lambda r: stage_overlap(r, 15, 8, 3, 2, True, True),
+    "ov_15_8_c3w3_plf": lambda r: stage_overlap(r, 15, 8, 3, 3, True, True),
+    "ov_15_16_c3w2_plf": lambda r: stage_overlap(r, 15, 16, 3, 2, True, True),
+    "ov_15_6_c3w2_plf": lambda r: stage_overlap(r, 15, 6, 3, 2, True, True),
+    "ov_15_4_c3w2_plf": lambda r: stage_overlap(r, 15, 4, 3, 2, True, True),
+    "ov_15_8_c5w2_plf": lambda r: stage_overlap(r, 15, 8, 5, 2, True, True),
+    "ov_12_8_c6w2_plf": lambda r: stage_overlap(r, 12, 8, 6, 2, True, True),
+    "ov_12_6_plf": lambda r: stage_overlap(r, 12, 6, 0, 0, True, True),
+    "ov_12_6_p": lambda r: stage_overlap(r, 12, 6, 0, 0, True, False),
+    "pl_argmax_cfg2": lambda r: stage_pl_argmax(r, 16, 13, 81, 241, 640, 1920, "cfg2"),
+    "pl_c3w2": lambda r: stage_pl_low(r, 16, 13, 81, 241, 640, 1920, "cfg2_c3w2", 0, 3, 2),
+    "overlap_cfg2_10_6": lambda r: stage_overlap(r, 10, 6),
+    "overlap_cfg2_12_6": lambda r: stage_overlap(r, 12, 6),
+    "sums_cfg2_nc6": lambda r: stage_proto(r, 16, 13, 256, 81, 241, "cfg2_k256", 6, True),
+    "pl_low_cfg2_w10": lambda r: stage_pl_low(r, 16, 13, 81, 241, 640, 1920, "cfg2", 10),
     "overlap_cfg2_8_8": lambda r: stage_overlap(r, 8, 8),
     "overlap_cfg2_8_4": lambda r: stage_overlap(r, 8, 4),
     "overlap_cfg2_16_4": lambda r: stage_overlap(r, 16, 4),
