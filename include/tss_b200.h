@@ -232,7 +232,9 @@ int tss_proto_update_partial(const float* vectors, const uint8_t* valid, const f
  * form: 0 = automatic, else TSS_DIST_FORM(variant, prefetch, split, algo) --
  *   variant  0 auto | 1 eight-warp register-pipeline kernel | 2 / 4 thread-level-parallel kernel, 2 / 4 px per lane |
  *            8 streaming kernel (TMA bulk copies of feat tiles + prototype slices into a shared-memory ring; expanded form)
- *   prefetch 0 auto | 1 + depth (0, 1, 2 four-channel groups) of the thread-level-parallel kernel
+ *   prefetch 0 auto | 1 + depth (0, 1, 2 four-channel groups) of the thread-level-parallel kernel; with variant 8: the
+ *            tile shape of the streaming kernel (1: 512 px x 32 ch, 8 warps x 2 px; 2: 512 x 32, 4 warps x 4 px;
+ *            3: 1024 x 16, 8 warps x 4 px; 4: 1024 x 16, 16 warps x 2 px)
  *   split    0 auto | K split 1, 2, 4 (8: register-pipeline kernel only)
  *   algo     0 auto | TSS_DIST_DIRECT: sum (p - f)^2 as torch.norm does | TSS_DIST_EXPANDED: |f|^2 + |p|^2 - 2 f.p
  *            (half the FP32 work) with every (pixel, class) whose d^2 < 0.5 (|f|^2 + |p|^2) -- the cancellation

@@ -254,6 +254,9 @@ struct TlpCfg {
 // accumulation error of the three sums (about 1e-6 relative to |f|^2 + |p|^2, measured; 4e-6 at four sigma) then
 // stays below 1e-5 relative to d^2 everywhere else.
 constexpr float kExpTheta = 0.5f;
+#ifndef TSS_STREAM_AUTO_BIG
+#define TSS_STREAM_AUTO_BIG 1   // tile shape of the streaming kernel for large batches (set from the measured sweep)
+#endif
 
 template <int CT>
 __device__ __noinline__ void exact_d2_pixel(const DistArgs& a, int64_t n, int64_t p, unsigned mask, float (&out)[CT]) {
@@ -501,42 +504,44 @@ __global__ void __launch_bounds__(TlpCfg<CT, PX, PF>::kThreads, 1) distance_tlp_
 // packed pair: conflict-free scalar shared loads whatever the rows' 4-byte misalignment).  Expanded form with exact
 // recomputation (see distance_tlp_kernel): 80 FFMA2 per 4 channels and 64 pixels, so a (tile, all K) unit costs the
 // FMA pipe ~86 us at C = 19, K = 2048 -- the same as the HBM time of its 4 MB.
-constexpr int kStTP = 512;                 // pixels per tile
-constexpr int kStKC = 32;                  // channels per stage
-constexpr int kStRS = kStTP + 8;           // row stride in floats: head misalignment (3) + 16-byte round-up (3)
 constexpr int kStStages = 3;
-constexpr int kStConsumers = 8;
-constexpr int kStThreads = (kStConsumers + 1) * 32;
 
-template <int CT>
-struct StreamSmem {
-    static constexpr int stage_floats = kStKC * kStRS + CT * kStKC;
+// TP pixels per tile, KC channels per stage, NW consumer warps, PX pixels per lane (TP = 32 NW PX)
+template <int CT, int TP, int KC, int NW, int PX>
+struct StreamCfg {
+    static_assert(TP == 32 * NW * PX && KC % 4 == 0 && KC <= 32 && PX % 2 == 0, "stream tile shape");
+    static constexpr int kRS = TP + 8;                      // row stride in floats: head misalignment (3) + 16-byte round-up (3)
+    static constexpr int kThreads = (NW + 1) * 32;
+    static constexpr int stage_floats = KC * kRS + CT * KC;
     static constexpr int bar_off = kStStages * stage_floats * 4;
     static constexpr int pn_off = bar_off + 2 * kStStages * 8;
     static constexpr int total = pn_off + CT * 4 + 16;
+    static_assert((stage_floats * 4) % 16 == 0 && total <= 227 * 1024, "stream shared memory");
 };
 
-template <int CT>
-__global__ void __launch_bounds__(kStThreads, 1) distance_stream_kernel(const DistArgs a, int64_t units) {
+template <int CT, int TP, int KC, int NW, int PX>
+__global__ void __launch_bounds__(StreamCfg<CT, TP, KC, NW, PX>::kThreads, 1) distance_stream_kernel(const DistArgs a, int64_t units) {
+    using Cfg = StreamCfg<CT, TP, KC, NW, PX>;
+    constexpr int RS = Cfg::kRS, PP = PX / 2;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     float* ring = reinterpret_cast<float*>(smem_raw);
-    uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + StreamSmem<CT>::bar_off);
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + Cfg::bar_off);
     uint64_t* empty = full + kStStages;
-    float* pn = reinterpret_cast<float*>(smem_raw + StreamSmem<CT>::pn_off);
+    float* pn = reinterpret_cast<float*>(smem_raw + Cfg::pn_off);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int64_t P = a.P, K = a.K;
-    const int64_t T = (P + kStTP - 1) / kStTP;       // tiles per image
-    const int chunks = static_cast<int>(K / kStKC);   // stages per unit
+    const int64_t T = (P + TP - 1) / TP;             // tiles per image
+    const int chunks = static_cast<int>(K / KC);      // stages per unit
     if (tid == 0) {
         for (int s = 0; s < kStStages; ++s) {
             mbar_init(&full[s], 32);
-            mbar_init(&empty[s], kStConsumers);
+            mbar_init(&empty[s], NW);
         }
         mbar_fence_init();
     }
     // the zero rows of the prototype slices (classes C..CT-1) are written once; bulk copies only touch rows < C
-    for (int i = tid; i < kStStages * StreamSmem<CT>::stage_floats; i += kStThreads) ring[i] = 0.f;
-    for (int c = warp; c < CT; c += kStConsumers + 1) {   // |p_c|^2 in fp64
+    for (int i = tid; i < kStStages * Cfg::stage_floats; i += Cfg::kThreads) ring[i] = 0.f;
+    for (int c = warp; c < CT; c += NW + 1) {   // |p_c|^2 in fp64
         double sq = 0.0;
         if (c < a.C)
             for (int64_t k = lane; k < K; k += 32) {
@@ -550,72 +555,84 @@ __global__ void __launch_bounds__(kStThreads, 1) distance_stream_kernel(const Di
     __syncthreads();
     const int64_t total_elems = a.N * K * P;
 
-    if (warp == kStConsumers) {
-        // ===== producer: lane l stages channel row k0 + l of the tile; lanes < C also stage the prototype slice of class l
+    if (warp == NW) {
+        // ===== producer: lane l < KC stages channel row k0 + l of the tile; lanes < C also stage the prototype slice of class l
         int stage = 0;
         uint32_t phase = 0;
         for (int64_t u = blockIdx.x; u < units; u += gridDim.x) {
-            const int64_t n = u / T, p0 = (u - n * T) * kStTP;
-            const int len = static_cast<int>(min(static_cast<int64_t>(kStTP), P - p0));
+            const int64_t n = u / T, p0 = (u - n * T) * TP;
+            const int len = static_cast<int>(min(static_cast<int64_t>(TP), P - p0));
             for (int ch = 0; ch < chunks; ++ch) {
                 mbar_wait(&empty[stage], phase ^ 1u);
-                float* st = ring + stage * StreamSmem<CT>::stage_floats;
-                const int64_t e0 = (n * K + static_cast<int64_t>(ch) * kStKC + lane) * P + p0;
-                const int o = static_cast<int>(e0 & 3);
-                const int64_t ea = e0 - o;
-                uint32_t nbytes = static_cast<uint32_t>(((o + len) * 4 + 15) & ~15);
-                int patch = 0;
-                if ((ea + nbytes / 4) > total_elems) {  // never read past the end of the tensor
-                    nbytes = static_cast<uint32_t>((total_elems - ea) * 4) & ~15u;
-                    patch = (o + len) - static_cast<int>(nbytes / 4);
+                float* st = ring + stage * Cfg::stage_floats;
+                uint32_t nbytes = 0;
+                if (lane < KC) {
+                    const int64_t e0 = (n * K + static_cast<int64_t>(ch) * KC + lane) * P + p0;
+                    const int o = static_cast<int>(e0 & 3);
+                    const int64_t ea = e0 - o;
+                    nbytes = static_cast<uint32_t>(((o + len) * 4 + 15) & ~15);
+                    int patch = 0;
+                    if ((ea + nbytes / 4) > total_elems) {  // never read past the end of the tensor
+                        nbytes = static_cast<uint32_t>((total_elems - ea) * 4) & ~15u;
+                        patch = (o + len) - static_cast<int>(nbytes / 4);
+                    }
+                    float* dst = st + lane * RS;
+                    for (int i = 0; i < patch; ++i) dst[nbytes / 4 + i] = a.feat[ea + nbytes / 4 + i];
+                    if (patch) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                    const uint32_t pbytes = lane < a.C ? KC * 4 : 0;
+                    mbar_arrive_expect_tx(&full[stage], nbytes + pbytes);
+                    if (nbytes) bulk_g2s(dst, a.feat + ea, nbytes, &full[stage]);
+                } else {
+                    const uint32_t pbytes = lane < a.C ? KC * 4 : 0;
+                    mbar_arrive_expect_tx(&full[stage], pbytes);
                 }
-                float* dst = st + lane * kStRS;
-                for (int i = 0; i < patch; ++i) dst[nbytes / 4 + i] = a.feat[ea + nbytes / 4 + i];
-                if (patch) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                const uint32_t pbytes = lane < a.C ? kStKC * 4 : 0;
-                mbar_arrive_expect_tx(&full[stage], nbytes + pbytes);
-                if (nbytes) bulk_g2s(dst, a.feat + ea, nbytes, &full[stage]);
-                if (pbytes) bulk_g2s(st + kStKC * kStRS + lane * kStKC, a.protos + lane * K + static_cast<int64_t>(ch) * kStKC, pbytes, &full[stage]);
+                if (lane < a.C) bulk_g2s(st + KC * RS + lane * KC, a.protos + lane * K + static_cast<int64_t>(ch) * KC, KC * 4, &full[stage]);
                 if (++stage == kStStages) { stage = 0; phase ^= 1u; }
             }
         }
     } else {
-        // ===== consumers: warp w owns pixels [64 w, 64 w + 64) of the tile, lane l the pair (64 w + l, 64 w + l + 32)
+        // ===== consumers: warp w owns pixels [32 PX w, 32 PX (w + 1)) of the tile, lane l the pixels 32 PX w + l + 32 i
         int stage = 0;
         uint32_t phase = 0;
-        const int px0 = warp * 64 + lane;
+        const int px0 = warp * 32 * PX + lane;
         for (int64_t u = blockIdx.x; u < units; u += gridDim.x) {
-            const int64_t n = u / T, p0 = (u - n * T) * kStTP;
-            f32x2 acc[CT];
+            const int64_t n = u / T, p0 = (u - n * T) * TP;
+            f32x2 acc[CT][PP];
 #pragma unroll
-            for (int c = 0; c < CT; ++c) acc[c] = 0ull;
-            f32x2 nrm0 = 0ull, nrm1 = 0ull;
+            for (int c = 0; c < CT; ++c)
+#pragma unroll
+                for (int h = 0; h < PP; ++h) acc[c][h] = 0ull;
+            f32x2 nrm[2][PP];
+#pragma unroll
+            for (int h = 0; h < PP; ++h) { nrm[0][h] = 0ull; nrm[1][h] = 0ull; }
             const unsigned emod = static_cast<unsigned>((n * K * P + p0) & 3), pm = static_cast<unsigned>(P & 3);
             for (int ch = 0; ch < chunks; ++ch) {
-                const float* st = ring + stage * StreamSmem<CT>::stage_floats;
-                const float* ps = st + kStKC * kStRS;
+                const float* st = ring + stage * Cfg::stage_floats;
+                const float* ps = st + KC * RS;
                 mbar_wait(&full[stage], phase);
-#pragma unroll 2
-                for (int g = 0; g < kStKC / 4; ++g) {
-                    f32x2 xp[4];
+#pragma unroll(PX == 2 ? 2 : 1)
+                for (int g = 0; g < KC / 4; ++g) {
+                    f32x2 xp[4][PP];
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
-                        const unsigned k = static_cast<unsigned>(ch * kStKC + g * 4 + q);
+                        const unsigned k = static_cast<unsigned>(ch * KC + g * 4 + q);
                         const unsigned o = (emod + k * pm) & 3u;            // this row's head misalignment
-                        const float* row = st + (g * 4 + q) * kStRS + o + px0;
-                        xp[q] = pack2(row[0], row[32]);
+                        const float* row = st + (g * 4 + q) * RS + o + px0;
+#pragma unroll
+                        for (int h = 0; h < PP; ++h) xp[q][h] = pack2(row[64 * h], row[64 * h + 32]);
                     }
-                    nrm0 = fma2(xp[0], xp[0], nrm0);
-                    nrm1 = fma2(xp[1], xp[1], nrm1);
-                    nrm0 = fma2(xp[2], xp[2], nrm0);
-                    nrm1 = fma2(xp[3], xp[3], nrm1);
+#pragma unroll
+                    for (int q = 0; q < 4; ++q)
+#pragma unroll
+                        for (int h = 0; h < PP; ++h) nrm[q & 1][h] = fma2(xp[q][h], xp[q][h], nrm[q & 1][h]);
 #pragma unroll
                     for (int c = 0; c < CT; ++c) {
-                        const float4 pr = *reinterpret_cast<const float4*>(ps + c * kStKC + g * 4);
-                        acc[c] = fma2(pack2(pr.x, pr.x), xp[0], acc[c]);
-                        acc[c] = fma2(pack2(pr.y, pr.y), xp[1], acc[c]);
-                        acc[c] = fma2(pack2(pr.z, pr.z), xp[2], acc[c]);
-                        acc[c] = fma2(pack2(pr.w, pr.w), xp[3], acc[c]);
+                        const float4 pr = *reinterpret_cast<const float4*>(ps + c * KC + g * 4);
+                        const float pv[4] = {pr.x, pr.y, pr.z, pr.w};
+#pragma unroll
+                        for (int q = 0; q < 4; ++q)
+#pragma unroll
+                            for (int h = 0; h < PP; ++h) acc[c][h] = fma2(pack2(pv[q], pv[q]), xp[q][h], acc[c][h]);
                     }
                 }
                 __syncwarp();
@@ -623,28 +640,29 @@ __global__ void __launch_bounds__(kStThreads, 1) distance_stream_kernel(const Di
                 if (++stage == kStStages) { stage = 0; phase ^= 1u; }
             }
             // ---- unit finished: d^2 = |f|^2 + |p|^2 - 2 f.p, exact recomputation inside the cancellation region
-            float d2[2][CT];
-            unsigned fl[2];
-            float F[2];
-            unpack2(add2(nrm0, nrm1), F[0], F[1]);
+            float d2[PX][CT];
+            unsigned fl[PX];
             unsigned any = 0;
 #pragma unroll
-            for (int i = 0; i < 2; ++i) {
+            for (int i = 0; i < PX; ++i) {
                 const int64_t p = p0 + px0 + 32 * i;
+                float f0, f1;
+                unpack2(add2(nrm[0][i >> 1], nrm[1][i >> 1]), f0, f1);
+                const float F = (i & 1) ? f1 : f0;
                 fl[i] = 0;
 #pragma unroll
                 for (int c = 0; c < CT; ++c) {
                     float lo, hi;
-                    unpack2(acc[c], lo, hi);
-                    const float scale = F[i] + pn[c];
-                    d2[i][c] = fmaf(-2.0f, i ? hi : lo, scale);
+                    unpack2(acc[c][i >> 1], lo, hi);
+                    const float scale = F + pn[c];
+                    d2[i][c] = fmaf(-2.0f, (i & 1) ? hi : lo, scale);
                     if (p < P && c < a.C && d2[i][c] < kExpTheta * scale) fl[i] |= 1u << c;
                 }
                 any |= fl[i];
             }
             if (__any_sync(0xffffffffu, any != 0)) {
 #pragma unroll
-                for (int i = 0; i < 2; ++i) {
+                for (int i = 0; i < PX; ++i) {
                     unsigned pend = __ballot_sync(0xffffffffu, fl[i] != 0);
                     while (pend) {
                         const int src = __ffs(pend) - 1;
@@ -662,7 +680,7 @@ __global__ void __launch_bounds__(kStThreads, 1) distance_stream_kernel(const Di
                 }
             }
 #pragma unroll
-            for (int i = 0; i < 2; ++i) {
+            for (int i = 0; i < PX; ++i) {
                 const int64_t p = p0 + px0 + 32 * i;
                 if (p < P) {
                     float d[CT];
@@ -675,15 +693,34 @@ __global__ void __launch_bounds__(kStThreads, 1) distance_stream_kernel(const Di
     }
 }
 
-template <int CT>
-static int launch_distance_stream(DistArgs& a, cudaStream_t st) {
-    cudaError_t e = cudaFuncSetAttribute(distance_stream_kernel<CT>, cudaFuncAttributeMaxDynamicSharedMemorySize, StreamSmem<CT>::total);
+template <int CT, int TP, int KC, int NW, int PX>
+static int launch_distance_stream_cfg(DistArgs& a, cudaStream_t st) {
+    using Cfg = StreamCfg<CT, TP, KC, NW, PX>;
+    cudaError_t e = cudaFuncSetAttribute(distance_stream_kernel<CT, TP, KC, NW, PX>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::total);
     if (e != cudaSuccess) return cuda_status(e, "tss_proto_distance: smem attribute");
-    const int64_t units = a.N * ((a.P + kStTP - 1) / kStTP);
+    const int64_t units = a.N * ((a.P + TP - 1) / TP);
     const unsigned grid = static_cast<unsigned>(units < kNumSMs ? units : kNumSMs);
-    distance_stream_kernel<CT><<<grid, kStThreads, StreamSmem<CT>::total, st>>>(a, units);
+    distance_stream_kernel<CT, TP, KC, NW, PX><<<grid, Cfg::kThreads, Cfg::total, st>>>(a, units);
     TSS_LAUNCH_CHECK("tss_proto_distance(stream)");
     return TSS_OK;
+}
+
+// shape: 0 = automatic, 1 = 512 px x 32 ch, 8 warps x 2 px; 2 = 512 x 32, 4 warps x 4 px; 3 = 1024 x 16, 8 warps x 4 px;
+// 4 = 1024 x 16, 16 warps x 2 px
+template <int CT>
+static int launch_distance_stream(DistArgs& a, int shape, cudaStream_t st) {
+    if (shape == 0) {
+        // the 1024-pixel tiles (twice the warps or pixels per lane behind each prototype load) need enough tiles to fill
+        // the machine; small batches keep the 512-pixel tile
+        const int64_t big = a.N * ((a.P + 1023) / 1024);
+        shape = big >= (kNumSMs * 7) / 8 ? TSS_STREAM_AUTO_BIG : 1;
+    }
+    switch (shape) {
+        case 2: return launch_distance_stream_cfg<CT, 512, 32, 4, 4>(a, st);
+        case 3: return launch_distance_stream_cfg<CT, 1024, 16, 8, 4>(a, st);
+        case 4: return launch_distance_stream_cfg<CT, 1024, 16, 16, 2>(a, st);
+        default: return launch_distance_stream_cfg<CT, 512, 32, 8, 2>(a, st);
+    }
 }
 
 // Relative cost of one (PX, SI) form on this problem: rounds of the persistent loop on the busiest warp x channel
@@ -775,7 +812,7 @@ static int launch_distance(DistArgs& a, int form, cudaStream_t st) {
     const DistForm fm = decode_form(form);
     const bool aligned = ((reinterpret_cast<uintptr_t>(a.feat) | reinterpret_cast<uintptr_t>(a.protos)) & 15) == 0;   // bulk copies
     if (aligned && (fm.variant == 8 || (fm.variant == 0 && fm.algo != 1 && fm.prefetch < 0 && fm.split == 0 && a.K >= 64)))
-        return launch_distance_stream<CT>(a, st);
+        return launch_distance_stream<CT>(a, fm.variant == 8 ? fm.prefetch + 1 : 0, st);   // variant 8: `prefetch` selects the tile shape
     {
         const int r = launch_distance_auto<CT>(a, fm, st);
         if (r != -1) return r;

@@ -159,10 +159,19 @@ ce_rce_fwd_kernel(const float* __restrict__ logits, const void* __restrict__ tar
     const int64_t first = blockIdx.x * static_cast<int64_t>(kLossThreads) + threadIdx.x;
     const int64_t stride = static_cast<int64_t>(gridDim.x) * kLossThreads;
     if (VEC) {
+        // Four pixels per thread as two packed pairs (FFMA2 / FADD2 halve the issue slots of the exponent arguments and
+        // the sums).  The label's own logit is RE-LOADED from the line that has just streamed through L2 (one 4-byte
+        // load per pixel) instead of being picked out of the C registers with C compare + select pairs, and the RCE
+        // sum over c != y is the sum over all classes minus the label's term (the same ex2 of the same argument, so the
+        // difference carries only the rounding of the sum).  The per-pixel terms of the four pixels are added in fp32
+        // and enter the fp64 accumulators once per iteration.
+        const int Cc = EXACT ? CT : C;
         const int64_t Pq = P >> 2, total = N * Pq;
+        const f32x2 l2e = pack2(kLog2e, kLog2e);
         PixelWalk w(first, stride, Pq);
         for (int64_t q = first; q < total; q += stride, w.next()) {
-            const float* x = logits + w.n * C * P + 4 * w.p;
+            const float* x0 = logits + w.n * C * P + 4 * w.p;
+            const float* x = x0;
             float4 v[CT];
 #pragma unroll
             for (int c = 0; c < CT; ++c) {
@@ -172,14 +181,82 @@ ce_rce_fwd_kernel(const float* __restrict__ logits, const void* __restrict__ tar
             long long y[4];
 #pragma unroll
             for (int j = 0; j < 4; ++j) y[j] = target_at<T>(target, 4 * q + j);
+            // label classification (32-bit tests) and the reload of the label's logit
+            float xy[4];
+            bool in_range[4], over[4], bad[4];
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-                PixelSoftmax<CT, EXACT> sm;
-#pragma unroll
-                for (int c = 0; c < CT; ++c) sm.p[c] = j == 0 ? v[c].x : j == 1 ? v[c].y : j == 2 ? v[c].z : v[c].w;
-                sm.finish(C, static_cast<int>(y[j]));
-                ce_rce_pixel<CT, EXACT>(sm, y[j], C, ignore, with_rce, A, acc);
+                const bool ign = y[j] == ignore;
+                in_range[j] = !ign && static_cast<unsigned long long>(y[j]) < static_cast<unsigned long long>(C);
+                over[j] = !ign && y[j] == C && with_rce;
+                bad[j] = !ign && !in_range[j] && !over[j];
+                const int yc = in_range[j] ? static_cast<int>(y[j]) : 0;
+                xy[j] = __ldg(x0 + static_cast<int64_t>(yc) * P + j);
             }
+            float m[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) m[j] = -INFINITY;
+#pragma unroll
+            for (int c = 0; c < CT; ++c)
+                if (c < Cc) {
+                    m[0] = fmaxf(m[0], v[c].x); m[1] = fmaxf(m[1], v[c].y);
+                    m[2] = fmaxf(m[2], v[c].z); m[3] = fmaxf(m[3], v[c].w);
+                }
+            const f32x2 nm01 = pack2(-(m[0] * kLog2e), -(m[1] * kLog2e)), nm23 = pack2(-(m[2] * kLog2e), -(m[3] * kLog2e));
+            f32x2 s01 = 0ull, s23 = 0ull;
+            float e[CT][4];
+#pragma unroll
+            for (int c = 0; c < CT; ++c)
+                if (c < Cc) {
+                    float a0, a1, a2, a3;
+                    unpack2(fma2(pack2(v[c].x, v[c].y), l2e, nm01), a0, a1);
+                    unpack2(fma2(pack2(v[c].z, v[c].w), l2e, nm23), a2, a3);
+                    e[c][0] = ex2_approx(a0); e[c][1] = ex2_approx(a1); e[c][2] = ex2_approx(a2); e[c][3] = ex2_approx(a3);
+                    s01 = add2(s01, pack2(e[c][0], e[c][1]));
+                    s23 = add2(s23, pack2(e[c][2], e[c][3]));
+                }
+            float sv[4];
+            unpack2(s01, sv[0], sv[1]);
+            unpack2(s23, sv[2], sv[3]);
+            float rsum[4] = {0.f, 0.f, 0.f, 0.f};
+            if (with_rce) {
+                // sum_c clamp(p_c, 1e-7, 1) = inv * sum_c max(e_c, 1e-7 s)   (p_c <= 1 up to rounding: the upper clamp is
+                // a 1-ulp effect on a term of order one)
+                float t[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) t[j] = 1e-7f * sv[j];
+                f32x2 r01 = 0ull, r23 = 0ull;
+#pragma unroll
+                for (int c = 0; c < CT; ++c)
+                    if (c < Cc) {
+                        r01 = add2(r01, pack2(fmaxf(e[c][0], t[0]), fmaxf(e[c][1], t[1])));
+                        r23 = add2(r23, pack2(fmaxf(e[c][2], t[2]), fmaxf(e[c][3], t[3])));
+                    }
+                unpack2(r01, rsum[0], rsum[1]);
+                unpack2(r23, rsum[2], rsum[3]);
+            }
+            float ce4 = 0.f, rce4 = 0.f;
+            int nvalid = 0, nover = 0, nbad = 0;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                nbad += bad[j] ? 1 : 0;
+                if (in_range[j]) {
+                    ce4 += __logf(sv[j]) - (xy[j] - m[j]);                       // -log_softmax[y]
+                    ++nvalid;
+                }
+                if (with_rce && (in_range[j] || over[j])) {
+                    const float inv = __frcp_rn(sv[j]);
+                    float own = 0.f;                                             // the label's own clamped term
+                    if (in_range[j]) own = fmaxf(ex2_approx(fmaf(xy[j], kLog2e, -(m[j] * kLog2e))), 1e-7f * sv[j]);
+                    rce4 += A * ((rsum[j] - own) * inv);
+                    nover += over[j] ? 1 : 0;
+                }
+            }
+            acc[0] += static_cast<double>(ce4);
+            acc[1] += static_cast<double>(rce4);
+            acc[2] += static_cast<double>(nvalid);
+            acc[3] += static_cast<double>(nbad);
+            acc[4] += static_cast<double>(nover);
         }
     } else {
         const int64_t total = N * P;

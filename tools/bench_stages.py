@@ -254,6 +254,10 @@ def stage_dist_sweep(reps, N, C, K, h, w, tag):
 
 
 STAGES = {
+    "dist_stream_shapes": lambda r: [stage_dist(r, n, 19, 2048, 129, 257, "cfg3_%dimg_shape%d" % (n, sh), True, ops.dist_form(8, sh - 1))
+                                     for n in (2, 4, 8) for sh in (1, 2, 3, 4)],
+    "dist_stream_shapes_k256": lambda r: [stage_dist(r, 16, 13, 256, 81, 241, "k256_shape%d" % sh, True, ops.dist_form(8, sh - 1))
+                                          for sh in (1, 2, 3, 4)],
     "dist_stream_cfg3": lambda r: stage_dist(r, 2, 19, 2048, 129, 257, "cfg3_2img", True, ops.dist_form(8)),
     "dist_stream_cfg3_8": lambda r: stage_dist(r, 8, 19, 2048, 129, 257, "cfg3_8img", True, ops.dist_form(8)),
     "dist_stream_cfg3_4": lambda r: stage_dist(r, 4, 19, 2048, 129, 257, "cfg3_4img", True, ops.dist_form(8)),
