@@ -238,7 +238,8 @@ int tss_proto_update_partial(const float* vectors, const uint8_t* valid, const f
  *   split    0 auto | K split 1, 2, 4 (8: register-pipeline kernel only)
  *   algo     0 auto | TSS_DIST_DIRECT: sum (p - f)^2 as torch.norm does | TSS_DIST_EXPANDED: |f|^2 + |p|^2 - 2 f.p
  *            (half the FP32 work) with every (pixel, class) whose d^2 < 0.5 (|f|^2 + |p|^2) -- the cancellation
- *            region -- recomputed in the direct form; automatic = the streaming kernel (expanded) for K >= 64. */
+ *            region -- recomputed in the direct form; automatic = the streaming kernel (expanded) for K >= 512, the
+ *            thread-level-parallel kernel in its expanded form for 128 <= K < 512, direct below. */
 #define TSS_DIST_DIRECT 1
 #define TSS_DIST_EXPANDED 2
 #define TSS_DIST_FORM(variant, prefetch_plus1, split, algo) \

@@ -255,7 +255,7 @@ struct TlpCfg {
 // stays below 1e-5 relative to d^2 everywhere else.
 constexpr float kExpTheta = 0.5f;
 #ifndef TSS_STREAM_AUTO_BIG
-#define TSS_STREAM_AUTO_BIG 1   // tile shape of the streaming kernel for large batches (set from the measured sweep)
+#define TSS_STREAM_AUTO_BIG 3   // tile shape of the streaming kernel for large batches (profiles/r02_distance_forms.txt)
 #endif
 
 template <int CT>
@@ -495,7 +495,7 @@ __global__ void __launch_bounds__(TlpCfg<CT, PX, PF>::kThreads, 1) distance_tlp_
 }
 
 // ------------------------------------------------------------------------------------------------
-// Streaming form (the default for K >= 64).  The thread-level-parallel kernels above are bound by the latency of their
+// Streaming form (the default for K >= 512; shorter K loops do not amortise the per-unit pipeline fill and epilogue).  The thread-level-parallel kernels above are bound by the latency of their
 // own feature loads (ncu: 7 long-scoreboard stall cycles per issued instruction, DRAM 23 %, FMA pipe 35 %): with C
 // accumulator registers per pixel a warp can keep only a few KB in flight.  Here the loads are the TMA engine's:
 // persistent CTAs, one producer warp that streams (32 channels x 512 pixels) tiles of feat -- and the matching
@@ -811,7 +811,7 @@ template <int CT>
 static int launch_distance(DistArgs& a, int form, cudaStream_t st) {
     const DistForm fm = decode_form(form);
     const bool aligned = ((reinterpret_cast<uintptr_t>(a.feat) | reinterpret_cast<uintptr_t>(a.protos)) & 15) == 0;   // bulk copies
-    if (aligned && (fm.variant == 8 || (fm.variant == 0 && fm.algo != 1 && fm.prefetch < 0 && fm.split == 0 && a.K >= 64)))
+    if (aligned && (fm.variant == 8 || (fm.variant == 0 && fm.algo != 1 && fm.prefetch < 0 && fm.split == 0 && a.K >= 512)))
         return launch_distance_stream<CT>(a, fm.variant == 8 ? fm.prefetch + 1 : 0, st);   // variant 8: `prefetch` selects the tile shape
     {
         const int r = launch_distance_auto<CT>(a, fm, st);
@@ -1005,7 +1005,7 @@ extern "C" int tss_proto_distance(const float* feat, const float* protos, int64_
     {
         const DistForm fm = decode_form(form);
         TSS_REQUIRE(form >= 0 && form < (1 << 16) && (fm.variant == 0 || fm.variant == 1 || fm.variant == 2 || fm.variant == 4 || fm.variant == 8) &&
-                    fm.prefetch <= 2 && (fm.split == 0 || fm.split == 1 || fm.split == 2 || fm.split == 4 || fm.split == 8) &&
+                    fm.prefetch <= (fm.variant == 8 ? 3 : 2) && (fm.split == 0 || fm.split == 1 || fm.split == 2 || fm.split == 4 || fm.split == 8) &&
                     fm.algo <= 2, TSS_E_ARG, "tss_proto_distance: bad form 0x%x", form);
     }
     TSS_REQUIRE(channels % 32 == 0, TSS_E_ARG, "tss_proto_distance: channels (%lld) must be a multiple of 32", static_cast<long long>(channels));
