@@ -451,10 +451,18 @@ def weak_param_table(weak_params, n: int):
     return np.asarray(rows, np.int32).reshape(n, 6), extents
 
 
-def full2weak(feat: torch.Tensor, weak_params) -> torch.Tensor:
-    """SelfTrain.full2weak in one gather pass (tss_full2weak)."""
-    f = _dev(feat, torch.float32, "feat")
-    n, k, h, w = f.shape
+@dataclass
+class WeakTable:
+    """weak_params of one batch after the reference's int(./4) arithmetic, resident on the device: build it once per
+    batch (weak_table) and hand it to full2weak / prototype_distance_sampled -- e.g. outside a CUDA-graph capture."""
+    params: torch.Tensor       # [N,6] int32 on device
+    th: int
+    tw: int
+
+
+def weak_table(weak_params, n: int, device) -> WeakTable:
+    if isinstance(weak_params, WeakTable):
+        return weak_params
     table, extents = weak_param_table(weak_params, n)
     if len(set(extents)) != 1:
         raise RuntimeError("full2weak: crops differ in size across the batch %s (torch.cat raises in the reference)"
@@ -464,7 +472,15 @@ def full2weak(feat: torch.Tensor, weak_params) -> torch.Tensor:
         raise RuntimeError("full2weak: empty crop %s" % (extents[0],))
     if (table[:, 0] < 1).any() or (table[:, 1] < 1).any():
         raise RuntimeError("full2weak: resized extent below 1")
-    params = torch.from_numpy(table).to(f.device)
+    return WeakTable(torch.from_numpy(table).to(device), th, tw)
+
+
+def full2weak(feat: torch.Tensor, weak_params) -> torch.Tensor:
+    """SelfTrain.full2weak in one gather pass (tss_full2weak).  ``weak_params``: the reference's dict or a WeakTable."""
+    f = _dev(feat, torch.float32, "feat")
+    n, k, h, w = f.shape
+    wt = weak_table(weak_params, n, f.device)
+    params, th, tw = wt.params, wt.th, wt.tw
     out = torch.empty((n, k, th, tw), dtype=torch.float32, device=f.device)
     check(lib().tss_full2weak(_ptr(f), n, k, h, w, _ptr(params), th, tw, _ptr(out), _stream()), "tss_full2weak")
     return out
@@ -518,17 +534,9 @@ def prototype_distance_sampled(feat8: torch.Tensor, quarter_hw: Sequence[int], w
     if p.shape[1] != k:
         raise ValueError("protos [C,%d] do not match feat channels %d" % (p.shape[1], k))
     Hq, Wq = int(quarter_hw[0]), int(quarter_hw[1])
-    table, extents = weak_param_table(weak_params, n)
-    if len(set(extents)) != 1:
-        raise RuntimeError("full2weak: crops differ in size across the batch %s (torch.cat raises in the reference)"
-                           % sorted(set(extents)))
-    th, tw = extents[0]
-    if th <= 0 or tw <= 0:
-        raise RuntimeError("full2weak: empty crop %s" % (extents[0],))
-    if (table[:, 0] < 1).any() or (table[:, 1] < 1).any():
-        raise RuntimeError("full2weak: resized extent below 1")
     dev = f.device
-    params = torch.from_numpy(table).to(dev)
+    wtab = weak_table(weak_params, n, dev)
+    params, th, tw = wtab.params, wtab.th, wtab.tw
     dist = torch.empty((n, c, th, tw), dtype=torch.float32, device=dev) if want_dist else None
     wt = torch.empty((n, c, th, tw), dtype=torch.float32, device=dev) if want_weight else None
     sf = hd = lab = None
