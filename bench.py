@@ -61,7 +61,8 @@ CONFIGS = {
     "cfg4": dict(frames=16, H=320, W=640, h=41, w=81, C=13, K=256, thr=0.3, keep=(5, 11), ignore=12, kind="self_train_round",
                  total_frames=10000,
                  title="cfg4: self-training round over 10k synthetic 640x320 frames, 16 frames/GPU/step: pseudo-labels, "
-                       "prototype update (exchange), rectified labels from the 1/8 features, CE+RCE forward+backward at 1/4"),
+                       "prototype update (exchange), rectified labels from the 1/8 features (interpolation to 1/4, full2weak, "
+                       "distances, weights), CE+RCE forward+backward at 1/4 with the upsample and its adjoint"),
     # configs[4]: evaluation sweep over 50k label maps
     "cfg5": dict(frames=1024, H=256, W=512, C=19, kind="eval_sweep", total_frames=50000,
                  title="cfg5: confusion-matrix mIoU over 50k synthetic 19-class 256x512 uint8 label maps, 1024 maps/GPU/step"),
@@ -623,8 +624,7 @@ def run_b200(args, cfg):
         """cfg4: rectified labels from the 1/8 features (fused sampling), then CE + RCE forward and backward at 1/4"""
         logits, feat, gt, soft, hard = sets[i % n_sets]
         q = (c["H"] // 4, c["W"] // 4)
-        lab = ops.prototype_distance_sampled(feat, q, identity_weak, bank.protos, temperature=0.5, soft=soft, hard=hard,
-                                             train_thred=0.0, ignore_index=c["ignore"])[2]
+        lab = ops.rectify_from_stride8(feat, q, identity_weak, bank.protos, 0.5, soft, hard, 0.0, c["ignore"])[1]
         x = ops.upsample_bilinear(logits, q).requires_grad_(True)
         loss = ops.ce_rce(x, lab.reshape(frames, *q), c["ignore"], 0.1, 1.0)[0]
         g, = torch.autograd.grad(loss, x)

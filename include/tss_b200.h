@@ -254,12 +254,13 @@ int tss_proto_distance(const float* feat, const float* protos, int64_t n_img, in
  * resize to (rh, rw), crop at (y0, x0), optional mirror; `params` as in tss_full2weak) -> :160-165, :139-142, :106-112
  * evaluated per OUTPUT pixel [N, TH*TW] with the two ATen operation sequences reproduced on the fly: neither the
  * [N,K,Hq,Wq] nor the [N,K,TH,TW] tensor is written.  Outputs / soft / hard / label as in tss_proto_distance
- * (P = TH*TW); direct-difference form; channels % 4 == 0. */
+ * (P = TH*TW); direct-difference form; channels % 4 == 0.  flags: 0, or 1 = four channels' taps in flight per thread
+ * (more registers, half the resident warps: A/B of the two forms). */
 int tss_proto_distance_sampled(const float* feat8, const float* protos, int64_t n_img, int64_t channels, int h8,
                                int w8, int Hq, int Wq, const int32_t* params, int TH, int TW, int num_classes,
                                float temperature, float* dist_out, float* weight_out, const float* soft,
                                const void* hard, int hard_dtype, float train_thred, int ignore_index,
-                               int64_t* label_out, void* stream);
+                               int64_t* label_out, int flags, void* stream);
 
 /* A9   full2weak -- SelfTrain.full2weak (self_training.py:145-158): per image bilinear
  * (align_corners=True) resize of feat [N,K,h,w] to (rh, rw), crop [y0:y0+TH, x0:x0+TW], optional mirror

@@ -41,7 +41,7 @@ _SIGNATURES = {
     "tss_proto_distance": (c_int, [c_vp, c_vp, c_i64, c_i64, c_i64, c_int, c_f32, c_vp, c_vp, c_vp, c_vp, c_int,
                                    c_f32, c_int, c_vp, c_int, c_vp]),
     "tss_proto_distance_sampled": (c_int, [c_vp, c_vp, c_i64, c_i64, c_int, c_int, c_int, c_int, c_vp, c_int, c_int, c_int,
-                                           c_f32, c_vp, c_vp, c_vp, c_vp, c_int, c_f32, c_int, c_vp, c_vp]),
+                                           c_f32, c_vp, c_vp, c_vp, c_vp, c_int, c_f32, c_int, c_vp, c_int, c_vp]),
     "tss_full2weak": (c_int, [c_vp, c_i64, c_i64, c_int, c_int, c_vp, c_int, c_int, c_vp, c_vp]),
     "tss_one_hot_overflow": (c_int, [c_vp, c_i64, c_i64, c_int, c_int, c_vp, c_vp]),
     "tss_loss_workspace_bytes": (c_sz, []),

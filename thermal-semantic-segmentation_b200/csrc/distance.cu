@@ -872,8 +872,10 @@ __device__ __forceinline__ float axis_scale(int n_in, int n_out) {
 
 constexpr int kSampThreads = 128;
 
-template <int CT>
-__global__ void __launch_bounds__(kSampThreads) distance_sampled_kernel(const DistArgs a, const SampleArgs sp) {
+// KS = channels sampled per step (their 16 KS tap loads are in flight together): 4 at 241 registers (2 CTAs per SM), 2
+// under a 128-register cap (4 CTAs per SM)
+template <int CT, int KS>
+__global__ void __launch_bounds__(kSampThreads, KS == 4 ? 1 : 4) distance_sampled_kernel(const DistArgs a, const SampleArgs sp) {
     extern __shared__ __align__(16) float ps[];   // [CT][K + 4]
     const int K = static_cast<int>(a.K), PS = K + 4;
     for (int i = threadIdx.x; i < CT * K; i += kSampThreads) {
@@ -921,6 +923,7 @@ __global__ void __launch_bounds__(kSampThreads) distance_sampled_kernel(const Di
         float v[4];
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
+            if (KS == 2 && q == 2) asm volatile("" ::: "memory");   // keep the two halves' loads apart (register cap)
             const float* ch = f + (k0 + q) * plane8;
             float Q[2][2];
 #pragma unroll
@@ -952,14 +955,21 @@ __global__ void __launch_bounds__(kSampThreads) distance_sampled_kernel(const Di
 }
 
 template <int CT>
-static int launch_distance_sampled(const DistArgs& a, const SampleArgs& sp, cudaStream_t st) {
+static int launch_distance_sampled(const DistArgs& a, const SampleArgs& sp, int flags, cudaStream_t st) {
     const size_t smem = sizeof(float) * CT * static_cast<size_t>(a.K + 4);
     TSS_REQUIRE(smem <= 226 * 1024, TSS_E_ARG, "tss_proto_distance_sampled: %d x %lld prototypes do not fit shared memory", CT,
                 static_cast<long long>(a.K));
-    cudaError_t e = cudaFuncSetAttribute(distance_sampled_kernel<CT>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
-    if (e != cudaSuccess) return cuda_status(e, "tss_proto_distance_sampled: smem attribute");
     dim3 grid(static_cast<unsigned>((sp.TH * sp.TW + kSampThreads - 1) / kSampThreads), static_cast<unsigned>(a.N));
-    distance_sampled_kernel<CT><<<grid, kSampThreads, smem, st>>>(a, sp);
+    cudaError_t e;
+    if (flags & 1) {
+        e = cudaFuncSetAttribute(distance_sampled_kernel<CT, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+        if (e != cudaSuccess) return cuda_status(e, "tss_proto_distance_sampled: smem attribute");
+        distance_sampled_kernel<CT, 4><<<grid, kSampThreads, smem, st>>>(a, sp);
+    } else {
+        e = cudaFuncSetAttribute(distance_sampled_kernel<CT, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+        if (e != cudaSuccess) return cuda_status(e, "tss_proto_distance_sampled: smem attribute");
+        distance_sampled_kernel<CT, 2><<<grid, kSampThreads, smem, st>>>(a, sp);
+    }
     TSS_LAUNCH_CHECK("tss_proto_distance_sampled");
     return TSS_OK;
 }
@@ -970,9 +980,10 @@ extern "C" int tss_proto_distance_sampled(const float* feat8, const float* proto
                                           int w8, int Hq, int Wq, const int32_t* params, int TH, int TW, int num_classes,
                                           float temperature, float* dist_out, float* weight_out, const float* soft,
                                           const void* hard, int hard_dtype, float train_thred, int ignore_index,
-                                          int64_t* label_out, void* stream) {
+                                          int64_t* label_out, int flags, void* stream) {
     using namespace tss;
     TSS_REQUIRE(feat8 && protos && params, TSS_E_ARG, "tss_proto_distance_sampled: null pointer");
+    TSS_REQUIRE(flags == 0 || flags == 1, TSS_E_ARG, "tss_proto_distance_sampled: bad flags %d", flags);
     TSS_REQUIRE(n_img >= 0 && n_img <= 65535 && channels > 0 && h8 > 0 && w8 > 0 && Hq > 0 && Wq > 0 && TH > 0 && TW > 0, TSS_E_ARG,
                 "tss_proto_distance_sampled: bad extents");
     TSS_REQUIRE(channels % 4 == 0, TSS_E_ARG, "tss_proto_distance_sampled: channels (%lld) must be a multiple of 4", static_cast<long long>(channels));
@@ -987,12 +998,12 @@ extern "C" int tss_proto_distance_sampled(const float* feat8, const float* proto
     a.KC = 0;
     SampleArgs sp{params, h8, w8, Hq, Wq, TH, TW};
     cudaStream_t st = as_stream(stream);
-    if (num_classes <= 4) return launch_distance_sampled<4>(a, sp, st);
-    if (num_classes <= 8) return launch_distance_sampled<8>(a, sp, st);
-    if (num_classes <= 13) return launch_distance_sampled<13>(a, sp, st);
-    if (num_classes <= 16) return launch_distance_sampled<16>(a, sp, st);
-    if (num_classes <= 19) return launch_distance_sampled<19>(a, sp, st);
-    return launch_distance_sampled<20>(a, sp, st);
+    if (num_classes <= 4) return launch_distance_sampled<4>(a, sp, flags, st);
+    if (num_classes <= 8) return launch_distance_sampled<8>(a, sp, flags, st);
+    if (num_classes <= 13) return launch_distance_sampled<13>(a, sp, flags, st);
+    if (num_classes <= 16) return launch_distance_sampled<16>(a, sp, flags, st);
+    if (num_classes <= 19) return launch_distance_sampled<19>(a, sp, flags, st);
+    return launch_distance_sampled<20>(a, sp, flags, st);
 }
 
 extern "C" int tss_proto_distance(const float* feat, const float* protos, int64_t n_img, int64_t channels,

@@ -513,11 +513,12 @@ class SelfTrain:
         batch, _, w, h = threshold_arg.shape
         if a.proto_rectify:
             # :69 (interpolation to the quarter map) + :82,:136-165 (full2weak, distances, weights) + :103-112
-            # (rectify) in ONE kernel reading the 1/8-stride features: no [N,K,H/4,W/4] / [N,K,64,128] tensors
+            # (rectify): at the reference's batch sizes ONE kernel reading the 1/8-stride features, no [N,K,H/4,W/4] /
+            # [N,K,64,128] tensors (ops.rectify_from_stride8 switches to the materialising form for large batches)
             hard_lp = ops.resize_nearest_u8(target_lp_hard.to(torch.uint8), tuple(threshold_arg.shape[2:]), rule="torch")
-            threshold_arg = ops.prototype_distance_sampled(
-                ema_feat8, quarter, target_weak_params, self._protos(), temperature=a.proto_temperature, soft=threshold_arg,
-                hard=hard_lp, train_thred=a.train_thred, ignore_index=a.ignore_index)[2]
+            threshold_arg = ops.rectify_from_stride8(
+                ema_feat8, quarter, target_weak_params, self._protos(), a.proto_temperature, threshold_arg, hard_lp,
+                a.train_thred, a.ignore_index)[1]
 
         loss_target_pseudo = self.target_loss(target_out["out"], threshold_arg.reshape([batch, w, h]))
         loss_target_pseudo.backward()

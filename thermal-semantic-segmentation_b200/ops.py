@@ -523,7 +523,7 @@ def prototype_distance(feat: torch.Tensor, protos: torch.Tensor, temperature: fl
 def prototype_distance_sampled(feat8: torch.Tensor, quarter_hw: Sequence[int], weak_params, protos: torch.Tensor,
                                temperature: float = 1.0, want_dist: bool = False, want_weight: bool = False,
                                soft: Optional[torch.Tensor] = None, hard: Optional[torch.Tensor] = None,
-                               train_thred: float = 0.0, ignore_index: int = 255):
+                               train_thred: float = 0.0, ignore_index: int = 255, flags: int = 0):
     """get_prototype_weight / the rectify block on the network's own 1/8-stride features: the interpolation to the
     quarter map (self_training.py:69) and full2weak (:145-158) are evaluated inside the distance kernel
     (tss_proto_distance_sampled).  Returns (dist, weight, label) at the weak view's [N, ., TH, TW]."""
@@ -553,8 +553,33 @@ def prototype_distance_sampled(feat8: torch.Tensor, quarter_hw: Sequence[int], w
             hd_dt = _DT[hd.dtype]
     check(lib().tss_proto_distance_sampled(_ptr(f), _ptr(p), n, k, h8, w8, Hq, Wq, _ptr(params), th, tw, c, float(temperature),
                                            _ptr(dist), _ptr(wt), _ptr(sf), _ptr(hd), hd_dt, float(train_thred),
-                                           int(ignore_index), _ptr(lab), _stream()), "tss_proto_distance_sampled")
+                                           int(ignore_index), _ptr(lab), int(flags), _stream()), "tss_proto_distance_sampled")
     return dist, wt, lab
+
+
+FUSED_SAMPLING_MAX_WORK = 1 << 24   # pixel-channels: above this the two materialising passes + streaming distance kernel win
+
+
+def rectify_from_stride8(feat8: torch.Tensor, quarter_hw: Sequence[int], weak_params, protos: torch.Tensor,
+                         temperature: float, soft: torch.Tensor, hard: Optional[torch.Tensor], train_thred: float,
+                         ignore_index: int, want_weight: bool = False, fused: Optional[bool] = None):
+    """self_training.py:69 + :82 + :103-112 from the network's 1/8-stride features: (weights | None, labels).
+    Small problems (the reference's own batches: 2-4 frames, 64x128 crops, 256 channels) run the ONE fused sampling
+    kernel -- no intermediate tensor; large batches (measured on B200: 16 x 256 x 80 x 160 takes 688 us fused against
+    119 + 74 us) interpolate to the quarter map, apply full2weak and go through the streaming distance kernel, whose
+    feature loads are TMA bulk copies.  Same arithmetic either way (both reproduce the two ATen interpolation stages)."""
+    n, k = feat8.shape[0], feat8.shape[1]
+    wt = weak_table(weak_params, n, feat8.device)
+    if fused is None:
+        fused = n * k * wt.th * wt.tw <= FUSED_SAMPLING_MAX_WORK
+    if fused:
+        _, w, lab = prototype_distance_sampled(feat8, quarter_hw, wt, protos, temperature=temperature, want_weight=want_weight,
+                                               soft=soft, hard=hard, train_thred=train_thred, ignore_index=ignore_index)
+        return w, lab
+    fw = full2weak(upsample_bilinear(feat8, quarter_hw), wt)
+    _, w, lab = prototype_distance(fw, protos, temperature=temperature, want_dist=False, want_weight=want_weight, soft=soft,
+                                   hard=hard, train_thred=train_thred, ignore_index=ignore_index)
+    return w, lab
 
 
 # ------------------------------------------------------------------------------------------- A11-A13
