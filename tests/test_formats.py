@@ -70,3 +70,22 @@ def test_load_hard_batch_matches_reference_reader(tmp_path):
         assert (got[k].cpu().numpy() == ref).all()
     raw = formats.load_hard_batch(d, names, 13, "cuda", threshold=None)
     assert (raw.cpu().numpy() == label).all()
+
+
+@pytest.mark.gpu
+def test_load_soft_batch_matches_loader_resize(tmp_path):
+    """soft .npy maps -> device -> the loader's bilinear resize (utils/self_train_augmentation.py:21-24)"""
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("needs a CUDA device")
+    from b200seg import formats
+    from oracle import label_path as O
+    r = np.random.RandomState(5)
+    names = ["a_%d.png" % i for i in range(3)]
+    maps = [r.dirichlet(np.ones(13), size=(9, 17)).transpose(2, 0, 1).astype(np.float32) for _ in names]
+    for n, m in zip(names, maps):
+        np.save(os.path.join(str(tmp_path), n.replace(".png", ".npy")), m)
+    out = formats.load_soft_batch(str(tmp_path), names, (320, 700), "cuda")
+    ref = O.upsample_bilinear_ac(torch.from_numpy(np.stack(maps)), (320, 700))
+    assert tuple(out.shape) == (3, 13, 320, 700)
+    assert (out.cpu() - ref).abs().max().item() <= 2e-6

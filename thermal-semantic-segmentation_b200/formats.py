@@ -3,7 +3,8 @@
 Writers  -- generate_pseudo_label.py:78 (soft: ``<name>.npy`` = fp32 [C,h,w] probabilities),
             :91 (hard: ``<name>.png`` = 8-bit grayscale class map), :94 (``<name>_conf.npy`` = fp16 [H,W]).
 Readers  -- data/freiburg_dataset.py:108-125 (np.load of the soft map; PNG + _conf.npy, then the threshold /
-            whitelist block and the NEAREST resize, which run on the device here).
+            whitelist block and the NEAREST resize, which run on the device here), and the loader-side bilinear
+            resize of the soft map to the image size (utils/self_train_augmentation.py:21-24).
 Driver   -- generate_pl (generate_pseudo_label.py:60-96) with the fused kernels; files written by either
             implementation are read by the other.
 
@@ -94,6 +95,16 @@ def load_hard_batch(path_lp: str, img_names: Sequence[str], num_classes: int, de
     conf_t = torch.from_numpy(np.stack(confs)).pin_memory().to(dev, non_blocking=True)
     return dropin.threshold_block(lab_t, conf_t, num_classes, threshold=threshold, ignore_index=ignore_index, keep=keep,
                                   size_wh=size_wh)
+
+
+def load_soft_batch(path_soft: str, img_names: Sequence[str], size_hw: Sequence[int], device) -> torch.Tensor:
+    """The reader side of the soft pseudo-labels: ``<name>.npy`` fp32 [C,h,w] maps (data/freiburg_dataset.py:109-110)
+    -> pinned host -> device, then the loader's bilinear align_corners=True resize to the image size
+    (utils/self_train_augmentation.py:21-24: ``F.interpolate(lpsoft.unsqueeze(0), size=[H, W], ...)``) in one kernel
+    for the whole batch.  Returns fp32 [N,C,H,W] on ``device`` (what ``step()`` upsamples again at self_training.py:62)."""
+    maps = [read_soft(path_soft, name) for name in img_names]
+    host = torch.from_numpy(np.stack(maps).astype(np.float32, copy=False)).pin_memory()
+    return ops.upsample_bilinear(host.to(torch.device(device), non_blocking=True), (int(size_hw[0]), int(size_hw[1])))
 
 
 @torch.no_grad()
