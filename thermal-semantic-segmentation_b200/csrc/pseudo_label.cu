@@ -296,14 +296,25 @@ struct UpCfg {  // register budget: 96 (20 warps/SM) holds C <= 13; 19 classes n
 
 template <int C, int MODE, bool COOP, int OUTS>
 __global__ void __launch_bounds__(UpCfg<C>::kWarpsPerSM * 32, 1)
-pl_up_kernel(const PLArgs a, int64_t total_rows, int rows_per_seg, int col_blocks) {
+pl_up_kernel(const PLArgs a, int64_t total_rows, int rows_per_seg, int col_blocks, int tab_rows) {
     // blockIdx.y = row segment, so the image / row bookkeeping and every row base address are uniform
     // across the CTA (uniform datapath); warps of a CTA take neighbouring column blocks.
     const int lane = threadIdx.x & 31;
     const int cb = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    if (cb >= col_blocks) return;
     const int64_t g0 = static_cast<int64_t>(blockIdx.y) * rows_per_seg;
     const int64_t g1 = min(g0 + rows_per_seg, total_rows);
+    // The vertical taps depend on the output row alone and every warp of the CTA walks the same rows: they are
+    // computed once per CTA into shared memory (one broadcast 128-bit load per row instead of two int<->float
+    // conversions on the XU pipe -- the busiest pipe of this kernel -- and eight more instructions per warp and row).
+    extern __shared__ __align__(16) int4 ytab[];
+    if (tab_rows > 0) {
+        for (int r = threadIdx.x; r < static_cast<int>(g1 - g0); r += blockDim.x) {
+            const Tap t = make_tap(a.sy, static_cast<int>((g0 + r) % a.H), a.h);
+            ytab[r] = make_int4(t.i0, t.i1, __float_as_int(t.l0), __float_as_int(t.l1));
+        }
+        __syncthreads();
+    }
+    if (cb >= col_blocks) return;
     const int gx = cb * kUpBlockPx + 2 * lane;
     const bool active = gx < a.W;              // W is even on this path: both pixels valid or neither
     const int gxc = active ? gx : a.W - 2;
@@ -327,8 +338,15 @@ pl_up_kernel(const PLArgs a, int64_t total_rows, int rows_per_seg, int col_block
     float p_sa = 1.f, p_sb = 1.f;
     int p_ia = 0, p_ib = 0;
     int64_t off = g0 * a.W + gx;
-    for (int rows_left = static_cast<int>(g1 - g0); rows_left > 0; --rows_left) {
-        const Tap ty = make_tap(a.sy, y, a.h);
+    const int n_rows = static_cast<int>(g1 - g0);
+    for (int r = 0; r < n_rows; ++r) {
+        Tap ty;
+        if (tab_rows > 0) {
+            const int4 t = ytab[r];
+            ty.i0 = t.x; ty.i1 = t.y; ty.l0 = __int_as_float(t.z); ty.l1 = __int_as_float(t.w);
+        } else {
+            ty = make_tap(a.sy, y, a.h);
+        }
         if (fresh || ty.i0 != cur0 || ty.i1 != cur1) {
             if (fresh) {
                 const float* img = a.src + n * img_stride;
@@ -371,16 +389,21 @@ pl_up_kernel(const PLArgs a, int64_t total_rows, int rows_per_seg, int col_block
         // class and pixel plus ONE packed FFMA per class for the pixel pair, instead of compare + select chains
         // on the (half-rate) ALU pipe.  Exact: every partial value is an integer <= C.
         f32x2 hidx = pack2(0.f, 0.f);
+#ifndef TSS_PL_EXP
+#define TSS_PL_EXP 0   // experiment builds only (tools/pl_experiments.sh): 1 = no argmax chain, 2 = no exponentials, 4 = no stores
+#endif
+#if !(TSS_PL_EXP & 1)
 #pragma unroll
         for (int c = C - 2; c >= 0; --c) {
             const f32x2 ne = pack2(set_neu(va[c], ma), set_neu(vb[c], mb));
             hidx = fma2(ne, hidx, ne);
         }
+#endif
         float fia, fib;
         unpack2(add2(hidx, pack2(8388608.f, 8388608.f)), fia, fib);  // integer in the low mantissa bits
         const int ia = __float_as_int(fia) & 0xff, ib = __float_as_int(fib) & 0xff;
         float sa = ma, sb = mb;  // UP_ARGMAX: the "confidence" is the max logit
-        if (MODE == TSS_PL_UP_SOFTMAX) {
+        if (MODE == TSS_PL_UP_SOFTMAX && !(TSS_PL_EXP & 2)) {
             const f32x2 l2e = pack2(kLog2e, kLog2e);
             const f32x2 nmb = pack2(-(ma * kLog2e), -(mb * kLog2e));
             f32x2 acc[4];
@@ -401,7 +424,7 @@ pl_up_kernel(const PLArgs a, int64_t total_rows, int rows_per_seg, int col_block
         p_off = off;
         p_sa = sa; p_sb = sb; p_ia = ia; p_ib = ib;
 #else
-        up_emit<MODE, OUTS>(a, active, off, sa, sb, ia, ib);
+        up_emit<MODE, OUTS>(a, (TSS_PL_EXP & 4) ? (active && sa == -123.f) : active, off, sa, sb, ia, ib);
 #endif
         off += a.W;  // rows of consecutive images are contiguous in every [N,H,W] output
         if (++y == a.H) { y = 0; ++n; fresh = true; }
@@ -604,10 +627,11 @@ static int launch_up(const PLArgs& a, int64_t n_img, int flags, cudaStream_t st)
     // SM cannot hold CTAs of two kernels that ask for different L1 / shared splits -- so this kernel (which uses no
     // shared memory) asks for the same split; on its own it keeps the default (largest L1).
     const int carve = (sm_warps > 0 || cta_warps > 0) ? static_cast<int>(cudaSharedmemCarveoutMaxShared) : static_cast<int>(cudaSharedmemCarveoutDefault);
+    const int tab_rows = r <= 2048 ? r : 0;   // per-CTA vertical tap table (16 B per row of the segment), else computed per row
     auto go = [&](auto kern) -> cudaError_t {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
         if (e != cudaSuccess) return e;
-        kern<<<grid, block, 0, st>>>(a, total_rows, r, col_blocks);
+        kern<<<grid, block, static_cast<size_t>(tab_rows) * sizeof(int4), st>>>(a, total_rows, r, col_blocks, tab_rows);
         return cudaSuccess;
     };
     cudaError_t e;
