@@ -294,8 +294,68 @@ struct UpCfg {  // register budget: 96 (20 warps/SM) holds C <= 13; 19 classes n
     static constexpr int kWarpsPerSM = C <= 13 ? TSS_UP_WARPS13 : 16;
 };
 
-template <int C, int MODE, bool COOP, int OUTS>
-__global__ void __launch_bounds__(UpCfg<C>::kWarpsPerSM * 32, 1)
+// the per-row arithmetic of pl_up_kernel for NR output rows that share one bracket of source rows (A, B): every stage
+// loops over the NR rows inside its class loop, so that the rows' dependency chains (max tree, argmax Horner chain,
+// exponent sums) are interleaved in one instruction stream -- ILP for a kernel whose largest stall is the fixed-latency
+// dependency wait
+template <int C, int MODE, int OUTS, int NR>
+__device__ __forceinline__ void up_rows(const PLArgs& a, const f32x2 (&A)[C], const f32x2 (&B)[C], const float (&l0)[NR],
+                                        const float (&l1)[NR], bool active, int64_t off) {
+    float va[NR][C], vb[NR][C];
+#pragma unroll
+    for (int c = 0; c < C; ++c)
+#pragma unroll
+        for (int j = 0; j < NR; ++j)
+            unpack2(fma2(pack2(l1[j], l1[j]), B[c], mul2(pack2(l0[j], l0[j]), A[c])), va[j][c], vb[j][c]);
+    float ma[NR], mb[NR];
+#pragma unroll
+    for (int j = 0; j < NR; ++j) { ma[j] = va[j][0]; mb[j] = vb[j][0]; }
+#pragma unroll
+    for (int c = 1; c < C; ++c)
+#pragma unroll
+        for (int j = 0; j < NR; ++j) { ma[j] = fmaxf(ma[j], va[j][c]); mb[j] = fmaxf(mb[j], vb[j][c]); }
+    f32x2 hidx[NR];
+#pragma unroll
+    for (int j = 0; j < NR; ++j) hidx[j] = pack2(0.f, 0.f);
+#pragma unroll
+    for (int c = C - 2; c >= 0; --c)
+#pragma unroll
+        for (int j = 0; j < NR; ++j) {
+            const f32x2 ne = pack2(set_neu(va[j][c], ma[j]), set_neu(vb[j][c], mb[j]));
+            hidx[j] = fma2(ne, hidx[j], ne);
+        }
+    float sa[NR], sb[NR];
+    if (MODE == TSS_PL_UP_SOFTMAX) {
+        const f32x2 l2e = pack2(kLog2e, kLog2e);
+        f32x2 nmb[NR], acc[NR][4];
+#pragma unroll
+        for (int j = 0; j < NR; ++j) nmb[j] = pack2(-(ma[j] * kLog2e), -(mb[j] * kLog2e));
+#pragma unroll
+        for (int c = 0; c < C; ++c)
+#pragma unroll
+            for (int j = 0; j < NR; ++j) {
+                float ta_, tb_;
+                unpack2(fma2(pack2(va[j][c], vb[j][c]), l2e, nmb[j]), ta_, tb_);
+                const f32x2 e = pack2(ex2_approx(ta_), ex2_approx(tb_));
+                acc[j][c & 3] = c < 4 ? e : add2(acc[j][c & 3], e);
+            }
+#pragma unroll
+        for (int j = 0; j < NR; ++j) unpack2(add2(add2(acc[j][0], acc[j][1]), add2(acc[j][2], acc[j][3])), sa[j], sb[j]);
+    } else {
+#pragma unroll
+        for (int j = 0; j < NR; ++j) { sa[j] = ma[j]; sb[j] = mb[j]; }
+    }
+#pragma unroll
+    for (int j = 0; j < NR; ++j) {
+        float fia, fib;
+        unpack2(add2(hidx[j], pack2(8388608.f, 8388608.f)), fia, fib);  // integer in the low mantissa bits
+        up_emit<MODE, OUTS>(a, active, off + j * static_cast<int64_t>(a.W), sa[j], sb[j], __float_as_int(fia) & 0xff,
+                            __float_as_int(fib) & 0xff);
+    }
+}
+
+template <int C, int MODE, bool COOP, int OUTS, int NR>
+__global__ void __launch_bounds__(NR == 2 ? 384 : UpCfg<C>::kWarpsPerSM * 32, 1)
 pl_up_kernel(const PLArgs a, int64_t total_rows, int rows_per_seg, int col_blocks, int tab_rows) {
     // blockIdx.y = row segment, so the image / row bookkeeping and every row base address are uniform
     // across the CTA (uniform datapath); warps of a CTA take neighbouring column blocks.
@@ -375,6 +435,19 @@ pl_up_kernel(const PLArgs a, int64_t total_rows, int rows_per_seg, int col_block
             cur0 = ty.i0;
             cur1 = ty.i1;
             fresh = false;
+        }
+        if (NR == 2 && tab_rows > 0 && r + 1 < n_rows && y + 1 < a.H) {
+            // the next output row lies between the same two source rows: both rows in one instruction stream
+            const int4 t1 = ytab[r + 1];
+            if (t1.x == cur0 && t1.y == cur1) {
+                const float l0[2] = {ty.l0, __int_as_float(t1.z)}, l1[2] = {ty.l1, __int_as_float(t1.w)};
+                up_rows<C, MODE, OUTS, 2>(a, A, B, l0, l1, active, off);
+                off += 2 * static_cast<int64_t>(a.W);
+                y += 2;
+                ++r;
+                if (y == a.H) { y = 0; ++n; fresh = true; }
+                continue;
+            }
         }
         // vertical lerp, two pixels per instruction
         const f32x2 ly0 = pack2(ty.l0, ty.l0), ly1 = pack2(ty.l1, ty.l1);
@@ -602,7 +675,9 @@ static int launch_up(const PLArgs& a, int64_t n_img, int flags, cudaStream_t st)
     const int col_blocks = (a.W + kUpBlockPx - 1) / kUpBlockPx;
     int best_wpc = 8, best_cps = 2;
     double best_eff = -1.0;
-    const int kW = (sm_warps >= 3 && sm_warps < UpCfg<C>::kWarpsPerSM) ? sm_warps : UpCfg<C>::kWarpsPerSM;
+    const bool rows2 = (flags & TSS_PL_FLAG_ROWS2) != 0;
+    const int kWmax = rows2 ? 12 : UpCfg<C>::kWarpsPerSM;      // the two-row form holds 170 registers per thread
+    const int kW = (sm_warps >= 3 && sm_warps < kWmax) ? sm_warps : kWmax;
     for (int wpc = (cta_warps ? cta_warps : 4); wpc <= (cta_warps ? cta_warps : kW); ++wpc) {
         const int cps = kW / wpc;                                  // CTAs per SM by registers
         if (cps < 1) break;
@@ -635,12 +710,14 @@ static int launch_up(const PLArgs& a, int64_t n_img, int flags, cudaStream_t st)
         return cudaSuccess;
     };
     cudaError_t e;
-    if (coop && pl_outs)
-        e = go(pl_up_kernel<C, MODE, true, MODE == TSS_PL_UP_SOFTMAX ? kOutsPseudoLabel : kOutsRuntime>);
+    if (coop && pl_outs && rows2 && tab_rows > 0)
+        e = go(pl_up_kernel<C, MODE, true, MODE == TSS_PL_UP_SOFTMAX ? kOutsPseudoLabel : kOutsRuntime, 2>);
+    else if (coop && pl_outs)
+        e = go(pl_up_kernel<C, MODE, true, MODE == TSS_PL_UP_SOFTMAX ? kOutsPseudoLabel : kOutsRuntime, 1>);
     else if (coop)
-        e = go(pl_up_kernel<C, MODE, true, kOutsRuntime>);
+        e = go(pl_up_kernel<C, MODE, true, kOutsRuntime, 1>);
     else
-        e = go(pl_up_kernel<C, MODE, false, kOutsRuntime>);
+        e = go(pl_up_kernel<C, MODE, false, kOutsRuntime, 1>);
     if (e != cudaSuccess) return cuda_status(e, "tss_pseudo_label: carveout attribute");
     TSS_LAUNCH_CHECK("tss_pseudo_label(up)");
     return TSS_OK;
@@ -655,7 +732,7 @@ extern "C" int tss_pseudo_label(const float* src, const float* src_flip, int64_t
     using namespace tss;
     const int g_pl_force_tile = (flags & TSS_PL_FLAG_FORCE_TILE) ? 1 : 0;
     const int sm_warps = (flags >> 8) & 0xff;
-    TSS_REQUIRE((flags >> 24) == 0 && flags >= 0, TSS_E_ARG, "tss_pseudo_label: bad flags 0x%x", flags);
+    TSS_REQUIRE((flags >> 24) == 0 && flags >= 0 && (flags & 0xfc) == 0, TSS_E_ARG, "tss_pseudo_label: bad flags 0x%x", flags);
     TSS_REQUIRE(src != nullptr, TSS_E_ARG, "tss_pseudo_label: null src");
     TSS_REQUIRE(n_img >= 0 && h > 0 && w > 0 && H > 0 && W > 0, TSS_E_ARG, "tss_pseudo_label: bad extents");
     TSS_REQUIRE(n_img <= 65535, TSS_E_ARG, "tss_pseudo_label: at most 65535 images per call");

@@ -24,11 +24,14 @@ PL_FLAG_FORCE_TILE = 1
 DIST_DIRECT, DIST_EXPANDED = 1, 2
 
 
-def pl_flags(force_tile: bool = False, sm_warps: int = 0, cta_warps: int = 0, waves: int = 0) -> int:
+PL_FLAG_ROWS2 = 2
+
+
+def pl_flags(force_tile: bool = False, sm_warps: int = 0, cta_warps: int = 0, waves: int = 0, rows2: bool = False) -> int:
     """`flags` of tss_pseudo_label: A/B switch of the tile kernel; warps per SM, warps per CTA and number of waves of
     the register-resident kernel (co-resident forms)."""
-    return (PL_FLAG_FORCE_TILE if force_tile else 0) | ((int(sm_warps) & 0xff) << 8) | ((int(cta_warps) & 0xf) << 16) | \
-        ((int(waves) & 0xf) << 20)
+    return (PL_FLAG_FORCE_TILE if force_tile else 0) | (PL_FLAG_ROWS2 if rows2 else 0) | ((int(sm_warps) & 0xff) << 8) | \
+        ((int(cta_warps) & 0xf) << 16) | ((int(waves) & 0xf) << 20)
 
 
 # The co-resident step form measured best on B200 at the cfg2 shape (profiles/r02_overlap_sweep.txt): pseudo-label kernel
