@@ -778,7 +778,11 @@ def run_b200(args, cfg):
     t_wall1 = time.perf_counter()
     launches = launches_per_step * steps
     ms = torch.tensor([ev0.elapsed_time(ev1)], device=dev)
+    ms_per_rank = [float(ms.item())]
     if ws > 1:
+        every = [torch.empty_like(ms) for _ in range(ws)]
+        dist.all_gather(every, ms)
+        ms_per_rank = [float(t.item()) for t in every]
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     ms = float(ms.item())
     with np.errstate(all="ignore"):
@@ -897,6 +901,7 @@ def run_b200(args, cfg):
                    "parallelism": "image-sharded x%d; collectives: prototype means [%d,%d,%s] fp32 per rank and step (%s), "
                                   "confusion [%d,%d] int64 once" % (ws, frames, C, c.get("K", "-"), exchange, C, C),
                    "miou": miou, "bank_max_spread_over_ranks": bank_spread, "bank_vs_sequential_rel": bank_vs_seq,
+                   "ms_per_step_by_rank": [round(t / steps, 5) for t in ms_per_rank],
                    "host_numa": numa},
         "parity_checked": parity is not None, "parity": parity,
         "stages_ms": {k: round(v, 5) for k, v in stage_ms.items()},
