@@ -641,9 +641,11 @@ def run_b200(args, cfg):
             cs = stage_sums(i)
             lab = stage_distance(i)
             return cs, lab
-        if mode == "coresident":
+        if mode in ("coresident", "coresident_hist_main"):
             cs = stage_sums(i, co_nc, side)      # label kernel here, accumulate kernel on the high-priority fork
             pl = stage_pl(i, co_pl)
+            if mode == "coresident_hist_main":   # confusion matrix behind the pseudo-label kernel instead of on the tail stream
+                stage_hist(i, pl)
             extra = stage_round_tail(i) if kind == "self_train_round" else None
             cur.wait_stream(side)
         else:
@@ -654,7 +656,8 @@ def run_b200(args, cfg):
 
     def build_graphs(mode):
         mains = [GraphedCall(lambda i=i: main_step(i, mode), warmup=1) for i in range(n_sets)]
-        tails = [GraphedCall(lambda i=i: stage_tail(i, mains[i].out[0], mains[i].out[1][0] if kind != "proto_distance" else None),
+        hist_in_tail = kind != "proto_distance" and mode != "coresident_hist_main"
+        tails = [GraphedCall(lambda i=i: stage_tail(i, mains[i].out[0], mains[i].out[1][0] if hist_in_tail else None),
                              warmup=1) for i in range(n_sets)] if has_proto else None
         return mains, tails
 
@@ -706,7 +709,8 @@ def run_b200(args, cfg):
 
     # ---- choose the step form: the co-resident form (pseudo-label on 12 warps/SM + accumulate on 5) against the serial
     # one, each timed over a few untimed-region replays; every rank takes the same decision (all-reduced times)
-    modes = ["serial"] if kind in ("eval_sweep", "proto_distance") else (["coresident", "serial"] if args.overlap == "auto" else [args.overlap])
+    modes = ["serial"] if kind in ("eval_sweep", "proto_distance") else (
+        ["coresident", "serial"] if args.overlap == "auto" else [args.overlap])
     trial = {}
     built = {}
     for m in modes:
@@ -733,8 +737,8 @@ def run_b200(args, cfg):
             out["means"] = ops.class_finalize(stage_sums(0))
             out["dist_label"], out["protos"] = stage_distance(0), bank.protos.clone()
         else:
-            out["pl"] = stage_pl(0, co_pl if mode == "coresident" else 0)
-            out["means"] = ops.class_finalize(stage_sums(0, co_nc if mode == "coresident" else 0))
+            out["pl"] = stage_pl(0, co_pl if mode != "serial" else 0)
+            out["means"] = ops.class_finalize(stage_sums(0, co_nc if mode != "serial" else 0))
         torch.cuda.synchronize()
         parity = parity_check(c, ops, out, sets[0])
         if not parity_ok(parity):
@@ -894,8 +898,10 @@ def run_b200(args, cfg):
                    "l2": "inputs rotate over %d resident sets (working set %d MB > 126 MB L2)" % (
                        n_sets, n_sets * sum(t.numel() * t.element_size() for t in sets[0]) // 2 ** 20),
                    "launch": "one CUDA-graph replay per step for the kernels (%s form: %s) + one for the prototype tail on its own "
-                             "stream, %d kernels per step" % (mode, {"coresident": "pseudo-label kernel in 3-warp CTAs and the "
-                             "accumulate kernel (6 consumer warps, high-priority capture fork) resident on the same SMs", "serial": "one stream"}[mode],
+                             "stream, %d kernels per step" % (mode, {"coresident": "pseudo-label kernel in 4-warp CTAs, two waves, and the "
+                             "accumulate kernel (6 consumer warps, high-priority capture fork) resident on the same SMs; confusion "
+                             "matrix on the tail stream", "coresident_hist_main": "as coresident, confusion matrix behind the "
+                             "pseudo-label kernel", "serial": "one stream"}[mode],
                              launches_per_step),
                    "step_form_trials_ms": {k: round(v, 5) for k, v in trial.items()},
                    "parallelism": "image-sharded x%d; collectives: prototype means [%d,%d,%s] fp32 per rank and step (%s), "
@@ -1118,7 +1124,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-parity", action="store_true", help="skip the in-run oracle check of one frame")
     ap.add_argument("--no-aux", action="store_true", help="skip the aux_stages timings of the default line")
-    ap.add_argument("--overlap", default="auto", choices=["auto", "coresident", "serial"],
+    ap.add_argument("--overlap", default="auto", choices=["auto", "coresident", "coresident_hist_main", "serial"],
                     help="step form: pseudo-label and accumulate kernels resident together, one after the other, or the faster "
                          "of the two measured before the timed region (default)")
     ap.add_argument("--coresident", default="", help="sm_warps,cta_warps,waves,consumer_warps of the co-resident form (tuning)")

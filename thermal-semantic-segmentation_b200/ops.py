@@ -35,8 +35,8 @@ def pl_flags(force_tile: bool = False, sm_warps: int = 0, cta_warps: int = 0, wa
 
 
 # The co-resident step form measured best on B200 at the cfg2 shape (profiles/r02_overlap_sweep.txt): pseudo-label kernel
-# in 3-warp CTAs, two waves, up to 15 warps per SM; accumulate kernel with 6 consumer warps on a high-priority stream
-CORESIDENT_PL_FLAGS = pl_flags(sm_warps=15, cta_warps=3, waves=2)
+# in 4-warp CTAs, two waves, up to 16 warps per SM; accumulate kernel with 6 consumer warps on a high-priority stream
+CORESIDENT_PL_FLAGS = pl_flags(sm_warps=16, cta_warps=4, waves=2)
 CORESIDENT_CONSUMERS = 6
 
 
