@@ -287,14 +287,17 @@ int tss_one_hot_overflow(const float* label, int64_t n_img, int64_t plane, int n
  * on (outside [0, C], or == C without rce), pixels labelled exactly C with rce: one_hot(label, C+1)[:, :C]
  * accepts them, their clamped one-hot row is all 1e-4, so they add -log(1e-4) sum_c clamp(p_c) to the rce sum and
  * count in its mask, while CrossEntropyLoss has no term for them}.  The host mirror forms
- * ce = out[0]/out[2], rce = out[1]/(out[2] + out[4] + 1e-6).  workspace: tss_loss_workspace_bytes(). */
+ * ce = out[0]/out[2], rce = out[1]/(out[2] + out[4] + 1e-6).  workspace: tss_loss_workspace_bytes() bytes; its trailing
+ * 16 bytes hold a ticket counter that MUST BE ZERO when the call is issued and is left zero by every call (allocate once
+ * with zeros, reuse; one workspace per stream): the CTA that draws the last ticket does the fixed-order final reduction,
+ * so forward = ONE launch. */
 size_t tss_loss_workspace_bytes(void);
 int tss_ce_rce_fwd(const float* logits, const void* target, int target_dtype, int64_t n_img,
                    int num_classes, int64_t plane, int ignore_index, int with_rce, double* out,
                    void* workspace, void* stream);
 /* The same, and losses (DEVICE, 3 floats) = {alpha ce + beta rce, ce, rce} formed in the reduction kernel with the
  * reference's arithmetic (fp64 division, fp32 rounding, fp32 mix; ce_sum != 0: reduction='sum' for ce), so the op
- * is two launches with no scalar follow-up (self_training.py:114-118). */
+ * is one launch with no scalar follow-up (self_training.py:114-118). */
 int tss_ce_rce_fwd_mix(const float* logits, const void* target, int target_dtype, int64_t n_img,
                        int num_classes, int64_t plane, int ignore_index, int with_rce, double alpha,
                        double beta, int ce_sum, double* out, float* losses, void* workspace, void* stream);

@@ -716,9 +716,11 @@ static int launch_distance_stream(DistArgs& a, int shape, cudaStream_t st) {
         shape = big >= (kNumSMs * 7) / 8 ? TSS_STREAM_AUTO_BIG : 1;
     }
     switch (shape) {
+#ifdef TSS_STREAM_ALL_SHAPES   // the two shapes that lost the sweep (profiles/r02_distance_forms.txt) are built on request only
         case 2: return launch_distance_stream_cfg<CT, 512, 32, 4, 4>(a, st);
-        case 3: return launch_distance_stream_cfg<CT, 1024, 16, 8, 4>(a, st);
         case 4: return launch_distance_stream_cfg<CT, 1024, 16, 16, 2>(a, st);
+#endif
+        case 3: return launch_distance_stream_cfg<CT, 1024, 16, 8, 4>(a, st);
         default: return launch_distance_stream_cfg<CT, 512, 32, 8, 2>(a, st);
     }
 }
@@ -998,10 +1000,8 @@ extern "C" int tss_proto_distance_sampled(const float* feat8, const float* proto
     a.KC = 0;
     SampleArgs sp{params, h8, w8, Hq, Wq, TH, TW};
     cudaStream_t st = as_stream(stream);
-    if (num_classes <= 4) return launch_distance_sampled<4>(a, sp, flags, st);
-    if (num_classes <= 8) return launch_distance_sampled<8>(a, sp, flags, st);
+    // class-count specialisations: Freiburg (13), Cityscapes (19), and 20; smaller counts run the next one up (guarded)
     if (num_classes <= 13) return launch_distance_sampled<13>(a, sp, flags, st);
-    if (num_classes <= 16) return launch_distance_sampled<16>(a, sp, flags, st);
     if (num_classes <= 19) return launch_distance_sampled<19>(a, sp, flags, st);
     return launch_distance_sampled<20>(a, sp, flags, st);
 }
@@ -1030,10 +1030,8 @@ extern "C" int tss_proto_distance(const float* feat, const float* protos, int64_
     a.temperature = temperature; a.train_thred = train_thred; a.hard_dtype = hard_dtype; a.ignore = ignore_index;
     a.KC = 0;  // chosen per class-count specialisation in launch_distance
     cudaStream_t st = as_stream(stream);
-    if (num_classes <= 4) return launch_distance<4>(a, form, st);
-    if (num_classes <= 8) return launch_distance<8>(a, form, st);
+    // class-count specialisations: Freiburg (13), Cityscapes (19), and 20; smaller counts run the next one up (guarded)
     if (num_classes <= 13) return launch_distance<13>(a, form, st);
-    if (num_classes <= 16) return launch_distance<16>(a, form, st);
     if (num_classes <= 19) return launch_distance<19>(a, form, st);
     return launch_distance<20>(a, form, st);
 }

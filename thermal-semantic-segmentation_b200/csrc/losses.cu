@@ -82,36 +82,50 @@ struct LossMix {
     int with_rce, ce_sum;
 };
 
-__global__ void __launch_bounds__(256) reduce_partials_kernel(const double* __restrict__ part, int blocks, double* __restrict__ out,
-                                                              const LossMix mix = LossMix{nullptr, 0.f, 0.f, 0, 0}) {
-    __shared__ double sh[kAcc][8];
+// Final reduction of the per-CTA partials in a FIXED order (bit-reproducible), executed by whichever CTA finishes last:
+// every CTA stores its partials, fences, and takes a ticket; the CTA that draws the last ticket reduces all partials
+// (read past L1) and resets the ticket to zero for the next call.  One launch instead of two.
+__device__ __forceinline__ void finish_if_last(const double* __restrict__ part, unsigned int* ticket, double* __restrict__ out,
+                                               const LossMix& mix) {
+    __shared__ bool last;
+    __shared__ double sh[kAcc][kLossThreads / 32];
+    __shared__ double tot[kAcc];
+    __threadfence();     // this CTA's partials are visible device-wide ...
+    __syncthreads();     // ... for every thread that stored one, before the ticket is drawn
+    if (threadIdx.x == 0) last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (!last) return;
+    __threadfence();
+    const int blocks = static_cast<int>(gridDim.x);
     double v[kAcc] = {0, 0, 0, 0, 0};
-    for (int b = threadIdx.x; b < blocks; b += 256)
+    for (int b = threadIdx.x; b < blocks; b += kLossThreads)
 #pragma unroll
-        for (int i = 0; i < kAcc; ++i) v[i] += part[b * kAccStride + i];
+        for (int i = 0; i < kAcc; ++i) v[i] += __ldcg(part + b * kAccStride + i);
 #pragma unroll
     for (int i = 0; i < kAcc; ++i) v[i] = warp_sum_d(v[i]);
     if ((threadIdx.x & 31) == 0)
 #pragma unroll
         for (int i = 0; i < kAcc; ++i) sh[i][threadIdx.x >> 5] = v[i];
     __syncthreads();
-    __shared__ double tot[kAcc];
     if (threadIdx.x < kAcc) {
         double t = 0.0;
-        for (int w = 0; w < 8; ++w) t += sh[threadIdx.x][w];
+        for (int w = 0; w < kLossThreads / 32; ++w) t += sh[threadIdx.x][w];
         out[threadIdx.x] = t;
         tot[threadIdx.x] = t;
     }
     __syncthreads();
-    if (mix.losses != nullptr && threadIdx.x == 0) {
-        const double valid = tot[2];
-        const float ce = static_cast<float>(mix.ce_sum ? tot[0] : tot[0] / valid);   // mean: nan when nothing is valid, as torch
-        const float rce = static_cast<float>(tot[1] / (valid + tot[4] + 1e-6));      // the rce mask is label != ignore
-        float t = __fmul_rn(mix.alpha, ce);
-        if (mix.with_rce) t = __fadd_rn(t, __fmul_rn(mix.beta, rce));
-        mix.losses[0] = t;
-        mix.losses[1] = ce;
-        mix.losses[2] = rce;
+    if (threadIdx.x == 0) {
+        *ticket = 0u;
+        if (mix.losses != nullptr) {
+            const double valid = tot[2];
+            const float ce = static_cast<float>(mix.ce_sum ? tot[0] : tot[0] / valid);   // mean: nan when nothing is valid, as torch
+            const float rce = static_cast<float>(tot[1] / (valid + tot[4] + 1e-6));      // the rce mask is label != ignore
+            float t = __fmul_rn(mix.alpha, ce);
+            if (mix.with_rce) t = __fadd_rn(t, __fmul_rn(mix.beta, rce));
+            mix.losses[0] = t;
+            mix.losses[1] = ce;
+            mix.losses[2] = rce;
+        }
     }
 }
 
@@ -153,7 +167,7 @@ __device__ __forceinline__ void ce_rce_pixel(const PixelSoftmax<CT, EXACT>& sm, 
 template <int CT, bool EXACT, typename T, bool VEC>
 __global__ void __launch_bounds__(kLossThreads)
 ce_rce_fwd_kernel(const float* __restrict__ logits, const void* __restrict__ target, int64_t N, int C, int64_t P,
-                  int ignore, int with_rce, double* __restrict__ part) {
+                  int ignore, int with_rce, double* __restrict__ part, unsigned int* ticket, double* __restrict__ out, const LossMix mix) {
     double acc[kAcc] = {0, 0, 0, 0, 0};
     const float A = rce_log_floor();
     const int64_t first = blockIdx.x * static_cast<int64_t>(kLossThreads) + threadIdx.x;
@@ -269,6 +283,7 @@ ce_rce_fwd_kernel(const float* __restrict__ logits, const void* __restrict__ tar
         }
     }
     block_reduce(acc, part + blockIdx.x * kAccStride);
+    finish_if_last(part, ticket, out, mix);
 }
 
 // upstream gradients {g_total, g_ce, g_rce} (DEVICE) + the forward's sums: the backward kernel forms its own scales
@@ -347,7 +362,7 @@ __device__ __forceinline__ float focal_weight(float pt, float gamma) {
 template <int CT, bool EXACT, typename T>
 __global__ void __launch_bounds__(kLossThreads)
 focal_fwd_kernel(const float* __restrict__ logits, const void* __restrict__ target, int64_t N, int C, int64_t P,
-                 float gamma, const float* __restrict__ alpha, double* __restrict__ part) {
+                 float gamma, const float* __restrict__ alpha, double* __restrict__ part, unsigned int* ticket, double* __restrict__ out) {
     double acc[kAcc] = {0, 0, 0, 0, 0};
     const int64_t total = N * P;
     const int Cc = EXACT ? CT : C;   // per-class guards fold at compile time when EXACT
@@ -366,6 +381,7 @@ focal_fwd_kernel(const float* __restrict__ logits, const void* __restrict__ targ
         acc[1] += 1.0;
     }
     block_reduce(acc, part + blockIdx.x * kAccStride);
+    finish_if_last(part, ticket, out, LossMix{nullptr, 0.f, 0.f, 0, 0});
 }
 
 template <int CT, bool EXACT, typename T>
@@ -447,7 +463,12 @@ static int check_loss_args(const char* who, const void* logits, const void* targ
 
 }  // namespace tss
 
-extern "C" size_t tss_loss_workspace_bytes(void) { return static_cast<size_t>(tss::kLossMaxBlocks) * tss::kAccStride * sizeof(double); }
+extern "C" size_t tss_loss_workspace_bytes(void) { return static_cast<size_t>(tss::kLossMaxBlocks) * tss::kAccStride * sizeof(double) + 16; }
+namespace tss {
+static inline unsigned int* ticket_of(void* workspace) {   // the trailing 16 bytes of the workspace
+    return reinterpret_cast<unsigned int*>(static_cast<char*>(workspace) + static_cast<size_t>(kLossMaxBlocks) * kAccStride * sizeof(double));
+}
+}  // namespace tss
 
 static int ce_rce_fwd_impl(const float* logits, const void* target, int target_dtype, int64_t n_img, int num_classes,
                            int64_t plane, int ignore_index, int with_rce, double* out, void* workspace, void* stream,
@@ -477,13 +498,12 @@ static int ce_rce_fwd_impl(const float* logits, const void* target, int target_d
     const bool vec = plane % 4 == 0 && (reinterpret_cast<uintptr_t>(logits) & 15) == 0;
     const int grid = loss_grid(vec ? n_img * plane / 4 : n_img * plane);
     double* part = static_cast<double*>(workspace);
+    unsigned int* ticket = ticket_of(workspace);
     if (vec) TSS_DISPATCH_CT_TV(ce_rce_fwd_kernel, true, num_classes, target_dtype, grid, st, logits, target, n_img, num_classes, plane,
-                                ignore_index, with_rce, part);
+                                ignore_index, with_rce, part, ticket, out, mix);
     else TSS_DISPATCH_CT_TV(ce_rce_fwd_kernel, false, num_classes, target_dtype, grid, st, logits, target, n_img, num_classes, plane,
-                            ignore_index, with_rce, part);
+                            ignore_index, with_rce, part, ticket, out, mix);
     TSS_LAUNCH_CHECK("tss_ce_rce_fwd");
-    reduce_partials_kernel<<<1, 256, 0, st>>>(part, grid, out, mix);
-    TSS_LAUNCH_CHECK("tss_ce_rce_fwd(reduce)");
     return TSS_OK;
 }
 
@@ -525,10 +545,8 @@ extern "C" int tss_focal_fwd(const float* logits, const void* target, int target
     const int grid = loss_grid(n_img * plane);
     double* part = static_cast<double*>(workspace);
     TSS_DISPATCH_CT_T(focal_fwd_kernel, num_classes, target_dtype, grid, st, logits, target, n_img, num_classes, plane, gamma,
-                      alpha, part);
+                      alpha, part, ticket_of(workspace), out);
     TSS_LAUNCH_CHECK("tss_focal_fwd");
-    reduce_partials_kernel<<<1, 256, 0, st>>>(part, grid, out);
-    TSS_LAUNCH_CHECK("tss_focal_fwd(reduce)");
     return TSS_OK;
 }
 

@@ -586,8 +586,21 @@ def rectify_from_stride8(feat8: torch.Tensor, quarter_hw: Sequence[int], weak_pa
 
 
 # ------------------------------------------------------------------------------------------- A11-A13
+_LOSS_WS = {}
+
+
 def _loss_workspace(dev) -> torch.Tensor:
-    return torch.empty(int(lib().tss_loss_workspace_bytes()), dtype=torch.uint8, device=dev)
+    """Partials + ticket counter of the loss kernels.  The ticket must be zero at launch and every launch leaves it zero:
+    one zero-initialised workspace per (device, stream) is allocated once and reused.  Inside a CUDA-graph capture a
+    fresh zeroed workspace is taken from the graph's pool (the zero fill is a node of the graph)."""
+    nbytes = int(lib().tss_loss_workspace_bytes())
+    if torch.cuda.is_current_stream_capturing():
+        return torch.zeros(nbytes, dtype=torch.uint8, device=dev)
+    key = (torch.device(dev).index, torch.cuda.current_stream(dev).cuda_stream)
+    ws = _LOSS_WS.get(key)
+    if ws is None:
+        ws = _LOSS_WS[key] = torch.zeros(nbytes, dtype=torch.uint8, device=dev)
+    return ws
 
 
 class _CeRce(torch.autograd.Function):

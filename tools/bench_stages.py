@@ -201,7 +201,7 @@ def stage_loss(reps, N, C, H, W, tag):
     report("ce_rce_fwd_" + tag, [N, C, H, W], med, mn, nb + 8 * N * H * W, N * H * W, 2, "ops.ce_rce: int64 targets as the reference; includes ~8 scalar torch kernels (mean, alpha/beta mix)")
 
     out4 = torch.empty(8, dtype=torch.float64, device=dev)
-    wsp = torch.empty(int(ops.lib().tss_loss_workspace_bytes()), dtype=torch.uint8, device=dev)
+    wsp = torch.zeros(int(ops.lib().tss_loss_workspace_bytes()), dtype=torch.uint8, device=dev)
 
     def fwd_abi(x, y):   # the two forward launches alone (sums in fp64), without the scalar torch arithmetic of ops.ce_rce
         ops.check(ops.lib().tss_ce_rce_fwd(x.data_ptr(), y.data_ptr(), 2, N, C, H * W, 255, 1, out4.data_ptr(), wsp.data_ptr(),
