@@ -577,7 +577,8 @@ def run_b200(args, cfg):
     # capture fork: the HBM-bound accumulate kernel beside the XU-bound pseudo-label kernel; high priority, so that the block
     # scheduler places its one CTA per SM before it fills the SM with pseudo-label CTAs
     side = torch.cuda.Stream(dev, priority=-1)
-    tail = torch.cuda.Stream(dev)    # confusion matrix, finalize / exchange / update of step i beside the kernels of step i+1
+    # confusion matrix, finalize / exchange / update of step i beside the kernels of step i+1
+    tail = torch.cuda.Stream(dev, priority=-1) if args.tail_priority else torch.cuda.Stream(dev)
     co_pl, co_nc = ops.CORESIDENT_PL_FLAGS, ops.CORESIDENT_CONSUMERS
     if args.coresident:
         v = [int(x) for x in args.coresident.split(",")]
@@ -710,7 +711,8 @@ def run_b200(args, cfg):
     # ---- choose the step form: the co-resident form (pseudo-label on 12 warps/SM + accumulate on 5) against the serial
     # one, each timed over a few untimed-region replays; every rank takes the same decision (all-reduced times)
     modes = ["serial"] if kind in ("eval_sweep", "proto_distance") else (
-        ["coresident", "serial"] if args.overlap == "auto" else [args.overlap])
+        (["coresident", "coresident_hist_main", "serial"] if ws > 1 else ["coresident", "serial"]) if args.overlap == "auto"
+        else [args.overlap])   # N > 1: the longer tail (exchange, update over every rank's images) prefers the confusion matrix on the main stream
     trial = {}
     built = {}
     for m in modes:
@@ -1127,6 +1129,7 @@ def main():
     ap.add_argument("--overlap", default="auto", choices=["auto", "coresident", "coresident_hist_main", "serial"],
                     help="step form: pseudo-label and accumulate kernels resident together, one after the other, or the faster "
                          "of the two measured before the timed region (default)")
+    ap.add_argument("--tail-priority", type=int, default=0, help="1 = the tail stream gets the high stream priority (tuning)")
     ap.add_argument("--coresident", default="", help="sm_warps,cta_warps,waves,consumer_warps of the co-resident form (tuning)")
     ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
                     help="N > 1 prototype exchange: peer-memory stores from the finalize kernel (default) or NCCL all_gather")
