@@ -102,6 +102,9 @@ int tss_softmax_nchw(const float* logits, float* probs, int64_t n_img, int num_c
 /* two output rows that share a bracket of source rows are processed in one instruction stream (instruction-level
  * parallelism across their dependency chains; 170 registers per thread, 12 warps per SM) */
 #define TSS_PL_FLAG_ROWS2 2
+/* the 13-class register-resident kernel compiled under a 96-register cap (20 warps per SM alone): more of its warps fit
+ * beside a co-resident kernel's CTA; same results bit for bit */
+#define TSS_PL_FLAG_REGS96 4
 #define TSS_PL_FLAG_SM_WARPS(w) (((w) & 0xff) << 8)
 /* co-resident scheduling: fixed CTA size in warps (3..8), and the number of waves the rows are cut into (1..15): many
  * small CTAs let the block scheduler refill an SM with pseudo-label CTAs as the accumulate kernel's CTAs retire */

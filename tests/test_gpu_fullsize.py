@@ -48,8 +48,9 @@ def test_cfg2_full_size_against_oracle(ops):
     # the co-resident form of the same kernel (12 warps per SM) must give the same bytes
     pl12 = ops.pseudo_label(dl, size=(H, W), thr=0.3, keep=(5, 11), ignore_index=12, flags=ops.pl_flags(sm_warps=12))
     assert torch.equal(pl.label, pl12.label) and torch.equal(pl.conf16, pl12.conf16) and torch.equal(pl.label_thr, pl12.label_thr)
-    # ... and so must the multi-wave small-CTA form and the two-rows-per-instruction-stream form
-    for fl in (ops.CORESIDENT_PL_FLAGS, ops.pl_flags(rows2=True), ops.pl_flags(sm_warps=12, cta_warps=3, waves=2, rows2=True)):
+    # ... and so must the multi-wave small-CTA form, the two-rows-per-instruction-stream form and the 96-register build
+    for fl in (ops.CORESIDENT_PL_FLAGS, ops.pl_flags(rows2=True), ops.pl_flags(sm_warps=12, cta_warps=3, waves=2, rows2=True),
+               ops.pl_flags(regs96=True), ops.pl_flags(sm_warps=20, cta_warps=4, waves=2, regs96=True)):
         alt = ops.pseudo_label(dl, size=(H, W), thr=0.3, keep=(5, 11), ignore_index=12, flags=fl)
         assert torch.equal(pl.label, alt.label) and torch.equal(pl.conf16, alt.conf16) and torch.equal(pl.label_thr, alt.label_thr)
     thr16 = float(np.float16(0.3))

@@ -354,8 +354,11 @@ __device__ __forceinline__ void up_rows(const PLArgs& a, const f32x2 (&A)[C], co
     }
 }
 
-template <int C, int MODE, bool COOP, int OUTS, int NR>
-__global__ void __launch_bounds__(NR == 2 ? 384 : UpCfg<C>::kWarpsPerSM * 32, 1)
+// RC = register class: 0 = the 128-register cap (16 warps per SM alone), 1 = a 96-register cap (20 warps per SM; a few
+// spilled words at C = 13): TSS_PL_FLAG_REGS96, for the co-resident forms where the other kernel's CTA leaves only
+// about 43 K registers per SM -- 13 warps of this class instead of 10.
+template <int C, int MODE, bool COOP, int OUTS, int NR, int RC = 0>
+__global__ void __launch_bounds__(NR == 2 ? 384 : (RC == 1 ? 640 : UpCfg<C>::kWarpsPerSM * 32), 1)
 pl_up_kernel(const PLArgs a, int64_t total_rows, int rows_per_seg, int col_blocks, int tab_rows) {
     // blockIdx.y = row segment, so the image / row bookkeeping and every row base address are uniform
     // across the CTA (uniform datapath); warps of a CTA take neighbouring column blocks.
@@ -676,7 +679,8 @@ static int launch_up(const PLArgs& a, int64_t n_img, int flags, cudaStream_t st)
     int best_wpc = 8, best_cps = 2;
     double best_eff = -1.0;
     const bool rows2 = (flags & TSS_PL_FLAG_ROWS2) != 0;
-    const int kWmax = rows2 ? 12 : UpCfg<C>::kWarpsPerSM;      // the two-row form holds 170 registers per thread
+    const bool regs96 = (flags & TSS_PL_FLAG_REGS96) != 0 && C <= 13 && !rows2;
+    const int kWmax = rows2 ? 12 : (regs96 ? 20 : UpCfg<C>::kWarpsPerSM);  // the two-row form holds 170 registers per thread
     const int kW = (sm_warps >= 3 && sm_warps < kWmax) ? sm_warps : kWmax;
     for (int wpc = (cta_warps ? cta_warps : 4); wpc <= (cta_warps ? cta_warps : kW); ++wpc) {
         const int cps = kW / wpc;                                  // CTAs per SM by registers
@@ -712,6 +716,8 @@ static int launch_up(const PLArgs& a, int64_t n_img, int flags, cudaStream_t st)
     cudaError_t e;
     if (coop && pl_outs && rows2 && tab_rows > 0)
         e = go(pl_up_kernel<C, MODE, true, MODE == TSS_PL_UP_SOFTMAX ? kOutsPseudoLabel : kOutsRuntime, 2>);
+    else if (coop && pl_outs && regs96)
+        e = go(pl_up_kernel<C <= 13 ? C : 13, MODE, true, MODE == TSS_PL_UP_SOFTMAX ? kOutsPseudoLabel : kOutsRuntime, 1, 1>);
     else if (coop && pl_outs)
         e = go(pl_up_kernel<C, MODE, true, MODE == TSS_PL_UP_SOFTMAX ? kOutsPseudoLabel : kOutsRuntime, 1>);
     else if (coop)
@@ -732,7 +738,7 @@ extern "C" int tss_pseudo_label(const float* src, const float* src_flip, int64_t
     using namespace tss;
     const int g_pl_force_tile = (flags & TSS_PL_FLAG_FORCE_TILE) ? 1 : 0;
     const int sm_warps = (flags >> 8) & 0xff;
-    TSS_REQUIRE((flags >> 24) == 0 && flags >= 0 && (flags & 0xfc) == 0, TSS_E_ARG, "tss_pseudo_label: bad flags 0x%x", flags);
+    TSS_REQUIRE((flags >> 24) == 0 && flags >= 0 && (flags & 0xf8) == 0, TSS_E_ARG, "tss_pseudo_label: bad flags 0x%x", flags);
     TSS_REQUIRE(src != nullptr, TSS_E_ARG, "tss_pseudo_label: null src");
     TSS_REQUIRE(n_img >= 0 && h > 0 && w > 0 && H > 0 && W > 0, TSS_E_ARG, "tss_pseudo_label: bad extents");
     TSS_REQUIRE(n_img <= 65535, TSS_E_ARG, "tss_pseudo_label: at most 65535 images per call");

@@ -25,12 +25,15 @@ DIST_DIRECT, DIST_EXPANDED = 1, 2
 
 
 PL_FLAG_ROWS2 = 2
+PL_FLAG_REGS96 = 4
 
 
-def pl_flags(force_tile: bool = False, sm_warps: int = 0, cta_warps: int = 0, waves: int = 0, rows2: bool = False) -> int:
+def pl_flags(force_tile: bool = False, sm_warps: int = 0, cta_warps: int = 0, waves: int = 0, rows2: bool = False,
+             regs96: bool = False) -> int:
     """`flags` of tss_pseudo_label: A/B switch of the tile kernel; warps per SM, warps per CTA and number of waves of
     the register-resident kernel (co-resident forms)."""
-    return (PL_FLAG_FORCE_TILE if force_tile else 0) | (PL_FLAG_ROWS2 if rows2 else 0) | ((int(sm_warps) & 0xff) << 8) | \
+    return (PL_FLAG_FORCE_TILE if force_tile else 0) | (PL_FLAG_ROWS2 if rows2 else 0) | (PL_FLAG_REGS96 if regs96 else 0) | \
+        ((int(sm_warps) & 0xff) << 8) | \
         ((int(cta_warps) & 0xf) << 16) | ((int(waves) & 0xf) << 20)
 
 

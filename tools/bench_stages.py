@@ -76,14 +76,14 @@ def g(seed):
     return torch.Generator(device=dev).manual_seed(seed)
 
 
-def stage_pl_low(reps, N, C, h, w, H, W, tag, sm_warps=0, cta_warps=0, waves=0, rows2=False):
+def stage_pl_low(reps, N, C, h, w, H, W, tag, sm_warps=0, cta_warps=0, waves=0, rows2=False, regs96=False):
     nb = 4 * N * C * h * w
     sets = [(3.0 * torch.randn(N, C, h, w, generator=g(s), device=dev),) for s in range(copies_for(nb + 4 * N * H * W))]
     thr, keep = 0.3, ((5, 11) if C == 13 else None)
     fn = lambda x: ops.pseudo_label(x, size=(H, W), thr=thr, keep=keep, ignore_index=C - 1 if C == 13 else 255,
-                                    flags=ops.pl_flags(sm_warps=sm_warps, cta_warps=cta_warps, waves=waves, rows2=rows2))
+                                    flags=ops.pl_flags(sm_warps=sm_warps, cta_warps=cta_warps, waves=waves, rows2=rows2, regs96=regs96))
     med, mn = timed(fn, sets, reps)
-    report("pl_low_" + tag + ("_w%d" % sm_warps if sm_warps else "") + ("_rows2" if rows2 else ""), [N, C, h, w, H, W], med, mn, nb + N * H * W * 4, N * H * W, 1,
+    report("pl_low_" + tag + ("_w%d" % sm_warps if sm_warps else "") + ("_rows2" if rows2 else "") + ("_regs96" if regs96 else ""), [N, C, h, w, H, W], med, mn, nb + N * H * W * 4, N * H * W, 1,
            "XU/issue-bound (C ex2 per px), not HBM: see DESIGN.md section 4")
 
 
@@ -121,7 +121,7 @@ def stage_proto(reps, N, C, K, h, w, tag, consumer_warps=0, sums_only=False):
            "labels + accumulate" if sums_only else "labels + accumulate + finalize/sequential update")
 
 
-def stage_overlap(reps, pl_warps, nc, cta_warps=0, waves=0, prio=False, label_first=False, rows2=False):
+def stage_overlap(reps, pl_warps, nc, cta_warps=0, waves=0, prio=False, label_first=False, rows2=False, regs96=False):
     """cfg2: the pseudo-label kernel (pl_warps per SM) and labels + accumulate (nc consumer warps) on two forked capture
     streams -- both resident on every SM -- against the same two run one after the other."""
     N, C, K, h, w, H, W = 16, 13, 256, 81, 241, 640, 1920
@@ -133,7 +133,7 @@ def stage_overlap(reps, pl_warps, nc, cta_warps=0, waves=0, prio=False, label_fi
     def fn(logits, feat):
         cur = torch.cuda.current_stream(dev)
         if pl_warps:
-            fl = ops.pl_flags(sm_warps=pl_warps, cta_warps=cta_warps, waves=waves, rows2=rows2)
+            fl = ops.pl_flags(sm_warps=pl_warps, cta_warps=cta_warps, waves=waves, rows2=rows2, regs96=regs96)
             if label_first:   # the label kernel alone first, then accumulate and pseudo-label become ready together
                 from b200seg.ops import _ptr, _stream, check, lib
                 import ctypes
@@ -161,7 +161,7 @@ def stage_overlap(reps, pl_warps, nc, cta_warps=0, waves=0, prio=False, label_fi
     med, mn = timed(fn, sets, reps)
     alg = 4 * N * C * h * w + N * H * W * 4 + 4 * N * (K + C) * h * w
     tag = "overlap_pl%d_nc%d" % (pl_warps, nc) + ("_cta%d_wv%d" % (cta_warps, waves) if cta_warps else "") + ("_prio" if prio else "") + \
-        ("_lf" if label_first else "") + ("_rows2" if rows2 else "")
+        ("_lf" if label_first else "") + ("_rows2" if rows2 else "") + ("_regs96" if regs96 else "")
     report(tag if pl_warps else "serial_pl16_nc%d" % (nc or 16), [N, C, K, h, w, H, W], med, mn, alg,
            N * H * W, 3, "pseudo-label + labels + accumulate (no finalize, no confusion)")
 
@@ -317,6 +317,24 @@ STAGES = {
     "ov_r2_12_4_c4w2": lambda r: stage_overlap(r, 12, 4, 4, 2, True, False, True),
     "ov_r2_12_8_c3w2": lambda r: stage_overlap(r, 12, 8, 3, 2, True, False, True),
     "ov_r2_12_16_c3w2": lambda r: stage_overlap(r, 12, 16, 3, 2, True, False, True),
+    "pl96": lambda r: stage_pl_low(r, 16, 13, 81, 241, 640, 1920, "cfg2", 0, 0, 0, False, True),
+    "pl96_c4w2": lambda r: stage_pl_low(r, 16, 13, 81, 241, 640, 1920, "cfg2_c4w2", 20, 4, 2, False, True),
+    "ov_16_6_c4w2_plf": lambda r: stage_overlap(r, 16, 6, 4, 2, True, True),
+    "ov96_12_6_c4w2_plf": lambda r: stage_overlap(r, 12, 6, 4, 2, True, True, False, True),
+    "ov96_12_6_c3w2_plf": lambda r: stage_overlap(r, 12, 6, 3, 2, True, True, False, True),
+    "ov96_12_6_c4w3_plf": lambda r: stage_overlap(r, 12, 6, 4, 3, True, True, False, True),
+    "ov96_13_6_c4w2_plf": lambda r: stage_overlap(r, 13, 6, 4, 2, True, True, False, True),
+    "ov96_13_6_c3w2_plf": lambda r: stage_overlap(r, 13, 6, 3, 2, True, True, False, True),
+    "ov96_13_6_c4w3_plf": lambda r: stage_overlap(r, 13, 6, 4, 3, True, True, False, True),
+    "ov96_16_6_c4w2_plf": lambda r: stage_overlap(r, 16, 6, 4, 2, True, True, False, True),
+    "ov96_16_6_c3w2_plf": lambda r: stage_overlap(r, 16, 6, 3, 2, True, True, False, True),
+    "ov96_16_6_c4w3_plf": lambda r: stage_overlap(r, 16, 6, 4, 3, True, True, False, True),
+    "ov96_20_6_c4w2_plf": lambda r: stage_overlap(r, 20, 6, 4, 2, True, True, False, True),
+    "ov96_20_6_c3w2_plf": lambda r: stage_overlap(r, 20, 6, 3, 2, True, True, False, True),
+    "ov96_20_6_c4w3_plf": lambda r: stage_overlap(r, 20, 6, 4, 3, True, True, False, True),
+    "ov96_20_8_c4w2_plf": lambda r: stage_overlap(r, 20, 8, 4, 2, True, True, False, True),
+    "ov96_20_4_c4w2_plf": lambda r: stage_overlap(r, 20, 4, 4, 2, True, True, False, True),
+    "ov96_20_6_c5w2_plf": lambda r: stage_overlap(r, 20, 6, 5, 2, True, True, False, True),
     "pl_argmax_cfg2": lambda r: stage_pl_argmax(r, 16, 13, 81, 241, 640, 1920, "cfg2"),
     "pl_c3w2": lambda r: stage_pl_low(r, 16, 13, 81, 241, 640, 1920, "cfg2_c3w2", 0, 3, 2),
     "overlap_cfg2_10_6": lambda r: stage_overlap(r, 10, 6),
