@@ -200,6 +200,23 @@ int tss_proto_finalize_update(const float* sums, const void* records, int64_t n_
                               float* protos, float* num, int mode, int start_mean, double momentum,
                               double cap, void* stream);
 
+/* A5 without allocations or caller workspace.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that
+ * forbid it).  Steps 1-3 above in one call -- tss_proto_labels (no labels_val, no confidence gate, overflow channel =
+ * num_classes: the Class_Features form, cal_prototype.py:118-144), tss_proto_accumulate, tss_proto_finalize -- with the
+ * scratch they pass to each other (tile records, segment labels, the [N,C,K] sums) in a file-scope
+ * `static __device__` array of TSS_NOALLOC_SCRATCH_BYTES inside the library (every GPU that loads the library holds it
+ * until the process exits).  Outputs are those of tss_proto_finalize, all caller-owned.  The call allocates and frees
+ * nothing.  Needed scratch = up256(tss_proto_records_bytes(N, P)) + up256(N*P) + up256(4*N*C*K) bytes (up256 = rounded
+ * up to 256); a batch that needs more is rejected with TSS_E_ARG and a message naming both numbers (cfg2, 16 x 13 x 256
+ * x 81 x 241, needs 1.63 MB).  Every call on a device shares the one array, and it keeps the last call's contents (the
+ * label kernel rewrites all it will read and zeroes the sums in its own launch): calls that can overlap on the GPU --
+ * different streams, or graph branches without an edge between them -- RACE; issue them on one stream. */
+#define TSS_NOALLOC_SCRATCH_BYTES (4 << 20)
+int tss_class_means_noalloc(const float* feat, const float* logits, int64_t n_img, int num_classes,
+                            int64_t channels, int64_t plane, int min_pixels, int32_t* count_all,
+                            int32_t* count_gated, float* vectors, uint8_t* valid, float* vector_sum, void* stream);
+
 /* A6   sequential prototype update -- update_objective_SingleVector (cal_prototype.py:153-169,
  * self_training.py:211-227) applied to the vectors of one batch in the reference's list order
  * (image-major, then class).  Classes are independent, so one thread block walks each class's images

@@ -32,6 +32,7 @@ _SIGNATURES = {
     "tss_proto_labels": (c_int, [c_vp, c_vp, c_i64, c_int, c_i64, c_int, c_int, c_f32, c_vp, c_vp, c_vp, c_i64, c_vp]),
     "tss_proto_accumulate": (c_int, [c_vp, c_vp, c_i64, c_i64, c_i64, c_int, c_vp, c_int, c_int, c_vp]),
     "tss_proto_finalize": (c_int, [c_vp, c_vp, c_i64, c_int, c_i64, c_i64, c_int, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
+    "tss_class_means_noalloc": (c_int, [c_vp, c_vp, c_i64, c_int, c_i64, c_i64, c_int, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "tss_proto_finalize_scatter": (c_int, [c_vp, c_vp, c_i64, c_int, c_i64, c_i64, c_int, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_int, c_vp]),
     "tss_proto_finalize_update": (c_int, [c_vp, c_vp, c_i64, c_int, c_i64, c_i64, c_int, c_vp, c_vp, c_vp, c_vp, c_vp,
                                           c_vp, c_vp, c_int, c_int, c_f64, c_f64, c_vp]),

@@ -20,6 +20,7 @@
 //                        accumulator per class when the class changes -- no atomics, no select chains.
 //                        Global fp32 reductions happen once per class per (image, channel group) per warp.
 #include "common.cuh"
+#include <mutex>
 
 namespace tss {
 
@@ -823,4 +824,74 @@ extern "C" int tss_proto_update_partial(const float* vectors, const uint8_t* val
                                                                              total, contrib_count, partial, scale0, num_after);
     TSS_LAUNCH_CHECK("tss_proto_update_partial");
     return TSS_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// tss_class_means_noalloc: the three steps of A5 (labels -> segmented sums -> means) for callers that cannot allocate.
+// No counterpart in the reference.  The scratch the three kernels hand to
+// each other (tile records, per-pixel segment labels, the [N,C,K] sums) lives in ONE file-scope device array, so the
+// call performs no cudaMalloc / cudaFree and takes no caller workspace.  In host code `g_noalloc_scratch` is only a
+// stand-in for the symbol: its device address is looked up once per device with cudaGetSymbolAddress (with that device
+// current) and that pointer is what the kernels receive.
+namespace tss {
+static __device__ __align__(256) unsigned char g_noalloc_scratch[TSS_NOALLOC_SCRATCH_BYTES];
+
+constexpr int kNoallocMaxDevices = 64;
+static std::mutex g_noalloc_mutex;
+static unsigned char* g_noalloc_ptr[kNoallocMaxDevices] = {};
+
+static int noalloc_scratch(unsigned char** out) {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return cuda_status(e, "tss_class_means_noalloc: cudaGetDevice");
+    TSS_REQUIRE(dev >= 0 && dev < kNoallocMaxDevices, TSS_E_ARG, "tss_class_means_noalloc: device ordinal %d outside [0, %d)", dev,
+                kNoallocMaxDevices);
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (g_noalloc_ptr[dev] == nullptr) {
+        unsigned char* p = nullptr;
+        e = cudaGetSymbolAddress((void**)&p, g_noalloc_scratch);   // this device's copy of the array
+        if (e != cudaSuccess) return cuda_status(e, "tss_class_means_noalloc: cudaGetSymbolAddress");
+        TSS_REQUIRE(p != nullptr, TSS_E_ARG, "tss_class_means_noalloc: null scratch address");
+        g_noalloc_ptr[dev] = p;
+    }
+    *out = g_noalloc_ptr[dev];
+    return TSS_OK;
+}
+
+static inline size_t up256(size_t v) { return (v + 255) & ~static_cast<size_t>(255); }
+}  // namespace tss
+
+extern "C" int tss_class_means_noalloc(const float* feat, const float* logits, int64_t n_img, int num_classes,
+                                       int64_t channels, int64_t plane, int min_pixels, int32_t* count_all,
+                                       int32_t* count_gated, float* vectors, uint8_t* valid, float* vector_sum,
+                                       void* stream) {
+    using namespace tss;
+    TSS_REQUIRE(feat && logits && count_all && count_gated && vectors && valid && vector_sum, TSS_E_ARG,
+                "tss_class_means_noalloc: null pointer");
+    TSS_REQUIRE(n_img >= 0 && n_img <= 65535 && plane > 0 && channels > 0 && channels % 32 == 0, TSS_E_ARG,
+                "tss_class_means_noalloc: bad extents (channels must be a multiple of 32)");
+    TSS_REQUIRE(num_classes >= 1 && num_classes <= TSS_MAX_CLASSES, TSS_E_CLASSES, "tss_class_means_noalloc: num_classes %d",
+                num_classes);
+    if (n_img == 0) return TSS_OK;
+    // scratch layout: [records | segment labels | sums], each part rounded up to 256 bytes
+    const size_t rec_bytes = up256(tss_proto_records_bytes(n_img, plane));
+    const size_t seg_bytes = up256(static_cast<size_t>(n_img) * static_cast<size_t>(plane));
+    const size_t sums_elems = static_cast<size_t>(n_img) * num_classes * static_cast<size_t>(channels);
+    const size_t need = rec_bytes + seg_bytes + up256(sums_elems * sizeof(float));
+    TSS_REQUIRE(need <= static_cast<size_t>(TSS_NOALLOC_SCRATCH_BYTES), TSS_E_ARG,
+                "tss_class_means_noalloc: this batch needs %zu bytes of scratch, the built-in array holds %zu "
+                "(TSS_NOALLOC_SCRATCH_BYTES): use tss_proto_labels / _accumulate / _finalize with caller memory",
+                need, static_cast<size_t>(TSS_NOALLOC_SCRATCH_BYTES));
+    unsigned char* base = nullptr;
+    if (int r = noalloc_scratch(&base)) return r;
+    void* records = base;
+    uint8_t* seg = base + rec_bytes;
+    float* sums = reinterpret_cast<float*>(base + rec_bytes + seg_bytes);
+    // the array keeps the previous call's contents: the label kernel rewrites every record and segment label it will be
+    // read for and zeroes the sums in the same launch (sums_to_zero), so nothing else has to be cleared
+    if (int r = tss_proto_labels(logits, nullptr, n_img, num_classes, plane, num_classes, 0, -1.0f, seg, records, sums,
+                                 static_cast<int64_t>(sums_elems), stream)) return r;
+    if (int r = tss_proto_accumulate(feat, records, n_img, channels, plane, num_classes, sums, 0, 0, stream)) return r;
+    return tss_proto_finalize(sums, records, n_img, num_classes, channels, plane, min_pixels, count_all, count_gated, vectors,
+                              valid, vector_sum, stream);
 }
