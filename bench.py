@@ -440,6 +440,11 @@ def parity_check(cfg, ops, out, data):
         gt0 = data[2][0].cpu().numpy().reshape(-1).astype(np.int64)
         h, _ = ops.confusion_matrix(pl.label[0].reshape(-1), data[2][0].reshape(-1), C)
         res["hist_exact"] = bool(np.array_equal(h.cpu().numpy(), O.fast_hist(lab.reshape(-1).astype(np.int64), gt0, C)))
+        if data[2].dtype == torch.uint8:   # the same matrix from inside the pseudo-label kernel (tss_pseudo_label_hist)
+            hf = torch.zeros(C, C, dtype=torch.int64, device=data[0].device)
+            plf = ops.pseudo_label(data[0][:1], size=(cfg["H"], cfg["W"]), thr=cfg["thr"], keep=cfg["keep"], ignore_index=cfg["ignore"],
+                                   flags=ops.CORESIDENT_PL_FLAGS, gt=data[2][:1], hist=hf)
+            res["hist_exact"] = res["hist_exact"] and bool(torch.equal(hf, h)) and bool(torch.equal(plf.label, pl.label[:1]))
     if "means" in out:
         m = out["means"]
         vr, ir = O.class_mean_vectors(feat, logits, C)
@@ -593,8 +598,10 @@ def run_b200(args, cfg):
         identity_weak = ops.weak_table(identity_weak, frames, dev)      # device table built once, outside the graph capture
 
     # ---- stages
-    def stage_pl(i, flags=0):
-        return ops.pseudo_label(sets[i % n_sets][0], size=size, thr=c["thr"], keep=c["keep"], ignore_index=c["ignore"], flags=flags)
+    def stage_pl(i, flags=0, with_hist=False):
+        # with_hist: the confusion matrix of (gt, label) is accumulated inside the pseudo-label kernel (tss_pseudo_label_hist)
+        return ops.pseudo_label(sets[i % n_sets][0], size=size, thr=c["thr"], keep=c["keep"], ignore_index=c["ignore"], flags=flags,
+                                gt=sets[i % n_sets][2] if with_hist else None, hist=meter.hist if with_hist else None)
 
     def stage_sums(i, consumer_warps=0, accumulate_stream=None):
         return ops.class_sums(sets[i % n_sets][1], sets[i % n_sets][0], C, consumer_warps=consumer_warps,
@@ -642,9 +649,9 @@ def run_b200(args, cfg):
             cs = stage_sums(i)
             lab = stage_distance(i)
             return cs, lab
-        if mode in ("coresident", "coresident_hist_main"):
+        if mode in ("coresident", "coresident_hist_main", "coresident_hist_fused"):
             cs = stage_sums(i, co_nc, side)      # label kernel here, accumulate kernel on the high-priority fork
-            pl = stage_pl(i, co_pl)
+            pl = stage_pl(i, co_pl, with_hist=(mode == "coresident_hist_fused"))
             if mode == "coresident_hist_main":   # confusion matrix behind the pseudo-label kernel instead of on the tail stream
                 stage_hist(i, pl)
             extra = stage_round_tail(i) if kind == "self_train_round" else None
@@ -657,7 +664,7 @@ def run_b200(args, cfg):
 
     def build_graphs(mode):
         mains = [GraphedCall(lambda i=i: main_step(i, mode), warmup=1) for i in range(n_sets)]
-        hist_in_tail = kind != "proto_distance" and mode != "coresident_hist_main"
+        hist_in_tail = kind != "proto_distance" and mode not in ("coresident_hist_main", "coresident_hist_fused")
         tails = [GraphedCall(lambda i=i: stage_tail(i, mains[i].out[0], mains[i].out[1][0] if hist_in_tail else None),
                              warmup=1) for i in range(n_sets)] if has_proto else None
         return mains, tails
@@ -711,7 +718,7 @@ def run_b200(args, cfg):
     # ---- choose the step form: the co-resident form (pseudo-label on 12 warps/SM + accumulate on 5) against the serial
     # one, each timed over a few untimed-region replays; every rank takes the same decision (all-reduced times)
     modes = ["serial"] if kind in ("eval_sweep", "proto_distance") else (
-        (["coresident", "coresident_hist_main", "serial"] if ws > 1 else ["coresident", "serial"]) if args.overlap == "auto"
+(["coresident", "coresident_hist_main", "serial"] if ws > 1 else ["coresident", "serial"]) if args.overlap == "auto"
         else [args.overlap])   # N > 1: the longer tail (exchange, update over every rank's images) prefers the confusion matrix on the main stream
     trial = {}
     built = {}
@@ -903,7 +910,8 @@ def run_b200(args, cfg):
                              "stream, %d kernels per step" % (mode, {"coresident": "pseudo-label kernel in 4-warp CTAs, two waves, and the "
                              "accumulate kernel (6 consumer warps, high-priority capture fork) resident on the same SMs; confusion "
                              "matrix on the tail stream", "coresident_hist_main": "as coresident, confusion matrix behind the "
-                             "pseudo-label kernel", "serial": "one stream"}[mode],
+                             "pseudo-label kernel", "coresident_hist_fused": "as coresident, confusion matrix accumulated inside "
+                             "the pseudo-label kernel (tss_pseudo_label_hist)", "serial": "one stream"}[mode],
                              launches_per_step),
                    "step_form_trials_ms": {k: round(v, 5) for k, v in trial.items()},
                    "parallelism": "image-sharded x%d; collectives: prototype means [%d,%d,%s] fp32 per rank and step (%s), "
@@ -1126,7 +1134,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-parity", action="store_true", help="skip the in-run oracle check of one frame")
     ap.add_argument("--no-aux", action="store_true", help="skip the aux_stages timings of the default line")
-    ap.add_argument("--overlap", default="auto", choices=["auto", "coresident", "coresident_hist_main", "serial"],
+    ap.add_argument("--overlap", default="auto", choices=["auto", "coresident", "coresident_hist_main", "coresident_hist_fused", "serial"],
                     help="step form: pseudo-label and accumulate kernels resident together, one after the other, or the faster "
                          "of the two measured before the timed region (default)")
     ap.add_argument("--tail-priority", type=int, default=0, help="1 = the tail stream gets the high stream priority (tuning)")

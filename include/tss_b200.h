@@ -122,6 +122,19 @@ int tss_pseudo_label(const float* src, const float* src_flip, int64_t n_img, int
                      float* conf32_out, uint8_t* label_thr_out, const float* thr_host,
                      const uint8_t* keep_host, int ignore_index, int flags, void* stream);
 
+/* A1-A4 + A14 in one pass: tss_pseudo_label plus the confusion matrix of (gt, label) -- utils/eval_tools.py:4-9
+ * (_fast_hist) applied to the labels of generate_pseudo_label.py:85 / segmentation_evaluate.py:42 (upsample ->
+ * argmax -> evaluate is the loop body of seg_validate, segmentation_evaluate.py:38-44,77-79).
+ * gt [N,H,W] uint8; hist [C*C] int64 ACCUMULATED, rows = ground truth; a pixel counts iff gt < C (labels are
+ * always in range here, so there is no bad-key counter).  Where the register-resident kernel applies the histogram is
+ * accumulated inside it (one 16-bit load per pixel pair, shared-memory atomics, one global atomic per non-zero bin and
+ * CTA); for every other shape the histogram kernel of tss_confusion runs on label_out (which must then be non-NULL). */
+int tss_pseudo_label_hist(const float* src, const float* src_flip, int64_t n_img, int num_classes, int h, int w,
+                          int H, int W, int mode, int flip, uint8_t* label_out, uint16_t* conf16_out,
+                          float* conf32_out, uint8_t* label_thr_out, const float* thr_host,
+                          const uint8_t* keep_host, int ignore_index, const uint8_t* gt, int64_t* hist, int flags,
+                          void* stream);
+
 /* A1   plain bilinear upsample, align_corners=True: self_training.py:62,69-77 (soft labels, feat, out).
  * src [planes, h, w] -> dst [planes, H, W] fp32. */
 int tss_upsample_bilinear(const float* src, float* dst, int64_t planes, int h, int w, int H, int W,

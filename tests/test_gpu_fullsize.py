@@ -161,3 +161,32 @@ def test_cfg5_full_size_against_oracle(ops):
     h = ops.confusion_matrix(torch.from_numpy(pred).cuda().reshape(-1), torch.from_numpy(gt).cuda().reshape(-1), c)[0]
     assert np.array_equal(h.cpu().numpy(), O.fast_hist(pred.reshape(-1).astype(np.int64),
                                                         np.where(gt == 255, -1, gt).reshape(-1).astype(np.int64), c))
+
+
+@pytest.mark.parametrize("shape", [(16, 13, 81, 241, 640, 1920), (2, 19, 129, 257, 1024, 2048), (3, 13, 41, 81, 320, 640),
+                                   (2, 13, 40, 80, 321, 642), (2, 7, 41, 81, 320, 640)])
+def test_pseudo_label_with_fused_confusion_matrix(ops, shape):
+    """tss_pseudo_label_hist: same labels / confidences as tss_pseudo_label, and the matrix np.bincount gives on them
+    (utils/eval_tools.py:4-9), for the register-resident kernel (first three shapes, every launch form) and for the shapes
+    that fall back to the histogram kernel (odd upsampling factor with 13 classes is still fused; 7 classes is not)."""
+    n, c, h, w, H, W = shape
+    g = torch.Generator().manual_seed(sum(shape))
+    logits = (3.0 * torch.randn(n, c, h, w, generator=g)).cuda()
+    gt = torch.randint(0, c + 2, (n, H, W), generator=g).to(torch.uint8)       # c, c + 1 = not a class: left out
+    gt[:, ::5, ::3] = 255
+    dg = gt.cuda()
+    base = ops.pseudo_label(logits, size=(H, W), thr=0.3, ignore_index=c - 1)
+    ref = O.fast_hist(base.label.cpu().numpy().reshape(-1).astype(np.int64),
+                      np.where(gt.numpy() >= c, -1, gt.numpy()).reshape(-1).astype(np.int64), c)
+    for fl in (0, ops.CORESIDENT_PL_FLAGS, ops.pl_flags(sm_warps=12, cta_warps=3, waves=3)):
+        hist = torch.zeros(c, c, dtype=torch.int64, device="cuda")
+        got = ops.pseudo_label(logits, size=(H, W), thr=0.3, ignore_index=c - 1, flags=fl, gt=dg, hist=hist)
+        assert torch.equal(got.label, base.label) and torch.equal(got.conf16, base.conf16) and torch.equal(got.label_thr, base.label_thr)
+        assert np.array_equal(hist.cpu().numpy(), ref)
+        # accumulated, not overwritten
+        ops.pseudo_label(logits, size=(H, W), thr=0.3, ignore_index=c - 1, flags=fl, gt=dg, hist=hist)
+        assert np.array_equal(hist.cpu().numpy(), 2 * ref)
+    # argmax-only mode (segmentation_evaluate.py:39,42) without the confidence output
+    hist = torch.zeros(c, c, dtype=torch.int64, device="cuda")
+    got = ops.pseudo_label(logits, size=(H, W), mode=ops.PL_UP_ARGMAX, want_conf16=False, gt=dg, hist=hist)
+    assert torch.equal(got.label, base.label) and np.array_equal(hist.cpu().numpy(), ref)

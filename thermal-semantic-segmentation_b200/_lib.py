@@ -24,6 +24,8 @@ _SIGNATURES = {
     "tss_softmax_nchw": (c_int, [c_vp, c_vp, c_i64, c_int, c_i64, c_vp]),
     "tss_pseudo_label": (c_int, [c_vp, c_vp, c_i64, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_vp, c_vp,
                                  c_vp, c_vp, c_vp, c_vp, c_int, c_int, c_vp]),
+    "tss_pseudo_label_hist": (c_int, [c_vp, c_vp, c_i64, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_vp, c_vp,
+                                      c_vp, c_vp, c_vp, c_vp, c_int, c_vp, c_vp, c_int, c_vp]),
     "tss_upsample_bilinear": (c_int, [c_vp, c_vp, c_i64, c_int, c_int, c_int, c_int, c_vp]),
     "tss_upsample_bilinear_adjoint": (c_int, [c_vp, c_vp, c_i64, c_int, c_int, c_int, c_int, c_vp]),
     "tss_threshold_labels": (c_int, [c_vp, c_vp, c_i64, c_int, c_vp, c_vp, c_int, c_vp, c_vp]),

@@ -27,6 +27,8 @@ struct PLArgs {
     __half* conf16;
     float* conf32;
     uint8_t* label_thr;
+    const uint8_t* gt;             // fused confusion matrix (register-resident kernel only): ground truth [N,H,W] uint8 ...
+    unsigned long long* hist;      // ... and the [C,C] int64 matrix it accumulates into (rows = ground truth)
     int C, h, w, H, W;
     float sy, sx;
     int mode, flip;
@@ -357,7 +359,12 @@ __device__ __forceinline__ void up_rows(const PLArgs& a, const f32x2 (&A)[C], co
 // RC = register class: 0 = the 128-register cap (16 warps per SM alone), 1 = a 96-register cap (20 warps per SM; a few
 // spilled words at C = 13): TSS_PL_FLAG_REGS96, for the co-resident forms where the other kernel's CTA leaves only
 // about 43 K registers per SM -- 13 warps of this class instead of 10.
-template <int C, int MODE, bool COOP, int OUTS, int NR, int RC = 0>
+// HIST: the confusion matrix of (ground truth, label) is accumulated in the same pass (utils/eval_tools.py:4-9 on the
+// labels of generate_pseudo_label.py:85 / segmentation_evaluate.py:42): one 16-bit load of the pixel pair's ground
+// truth per row and two shared-memory atomics on a C x C int32 matrix per CTA -- LSU work in a kernel bound by the XU
+// pipe and the issue slots -- flushed with one 64-bit global atomic per non-zero bin when the CTA ends.  The separate
+// histogram kernel re-reads labels and ground truth (2 B/px) and takes 23 us at cfg2.
+template <int C, int MODE, bool COOP, int OUTS, int NR, int RC = 0, bool HIST = false>
 __global__ void __launch_bounds__(NR == 2 ? 384 : (RC == 1 ? 640 : UpCfg<C>::kWarpsPerSM * 32), 1)
 pl_up_kernel(const PLArgs a, int64_t total_rows, int rows_per_seg, int col_blocks, int tab_rows) {
     // blockIdx.y = row segment, so the image / row bookkeeping and every row base address are uniform
@@ -370,14 +377,17 @@ pl_up_kernel(const PLArgs a, int64_t total_rows, int rows_per_seg, int col_block
     // computed once per CTA into shared memory (one broadcast 128-bit load per row instead of two int<->float
     // conversions on the XU pipe -- the busiest pipe of this kernel -- and eight more instructions per warp and row).
     extern __shared__ __align__(16) int4 ytab[];
+    unsigned int* sh_hist = reinterpret_cast<unsigned int*>(ytab + tab_rows);  // HIST: C*C bins behind the tap table
     if (tab_rows > 0) {
         for (int r = threadIdx.x; r < static_cast<int>(g1 - g0); r += blockDim.x) {
             const Tap t = make_tap(a.sy, static_cast<int>((g0 + r) % a.H), a.h);
             ytab[r] = make_int4(t.i0, t.i1, __float_as_int(t.l0), __float_as_int(t.l1));
         }
-        __syncthreads();
     }
-    if (cb >= col_blocks) return;
+    if (HIST)
+        for (int i = threadIdx.x; i < C * C; i += blockDim.x) sh_hist[i] = 0u;
+    if (tab_rows > 0 || HIST) __syncthreads();
+    if (!HIST && cb >= col_blocks) return;   // (with HIST every warp stays for the flush at the end)
     const int gx = cb * kUpBlockPx + 2 * lane;
     const bool active = gx < a.W;              // W is even on this path: both pixels valid or neither
     const int gxc = active ? gx : a.W - 2;
@@ -401,7 +411,7 @@ pl_up_kernel(const PLArgs a, int64_t total_rows, int rows_per_seg, int col_block
     float p_sa = 1.f, p_sb = 1.f;
     int p_ia = 0, p_ib = 0;
     int64_t off = g0 * a.W + gx;
-    const int n_rows = static_cast<int>(g1 - g0);
+    const int n_rows = (HIST && cb >= col_blocks) ? 0 : static_cast<int>(g1 - g0);
     for (int r = 0; r < n_rows; ++r) {
         Tap ty;
         if (tab_rows > 0) {
@@ -439,6 +449,8 @@ pl_up_kernel(const PLArgs a, int64_t total_rows, int rows_per_seg, int col_block
             cur1 = ty.i1;
             fresh = false;
         }
+        unsigned gtp = 0xffffu;   // ground truth of the pixel pair: issued here, consumed after the row's arithmetic
+        if (HIST && active) gtp = *reinterpret_cast<const uint16_t*>(a.gt + off);
         if (NR == 2 && tab_rows > 0 && r + 1 < n_rows && y + 1 < a.H) {
             // the next output row lies between the same two source rows: both rows in one instruction stream
             const int4 t1 = ytab[r + 1];
@@ -502,12 +514,24 @@ pl_up_kernel(const PLArgs a, int64_t total_rows, int rows_per_seg, int col_block
 #else
         up_emit<MODE, OUTS>(a, (TSS_PL_EXP & 4) ? (active && sa == -123.f) : active, off, sa, sb, ia, ib);
 #endif
+        if (HIST) {   // a pixel counts iff its ground truth is a class (inactive lanes carry 0xff)
+            const unsigned ga = gtp & 0xffu, gb = gtp >> 8;
+            if (ga < static_cast<unsigned>(C)) atomicAdd(&sh_hist[ga * C + ia], 1u);
+            if (gb < static_cast<unsigned>(C)) atomicAdd(&sh_hist[gb * C + ib], 1u);
+        }
         off += a.W;  // rows of consecutive images are contiguous in every [N,H,W] output
         if (++y == a.H) { y = 0; ++n; fresh = true; }
     }
 #if TSS_UP_PIPE
     up_emit<MODE, OUTS>(a, p_valid, p_off, p_sa, p_sb, p_ia, p_ib);
 #endif
+    if (HIST) {
+        __syncthreads();
+        for (int i = threadIdx.x; i < C * C; i += blockDim.x) {
+            const unsigned int v = sh_hist[i];
+            if (v) atomicAdd(&a.hist[i], static_cast<unsigned long long>(v));
+        }
+    }
 }
 
 // full-resolution input: grid-stride over pixel quads of the flattened [N, H*W] map
@@ -707,14 +731,21 @@ static int launch_up(const PLArgs& a, int64_t n_img, int flags, cudaStream_t st)
     // shared memory) asks for the same split; on its own it keeps the default (largest L1).
     const int carve = (sm_warps > 0 || cta_warps > 0) ? static_cast<int>(cudaSharedmemCarveoutMaxShared) : static_cast<int>(cudaSharedmemCarveoutDefault);
     const int tab_rows = r <= 2048 ? r : 0;   // per-CTA vertical tap table (16 B per row of the segment), else computed per row
+    const bool hist = a.hist != nullptr;
     auto go = [&](auto kern) -> cudaError_t {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
         if (e != cudaSuccess) return e;
-        kern<<<grid, block, static_cast<size_t>(tab_rows) * sizeof(int4), st>>>(a, total_rows, r, col_blocks, tab_rows);
+        const size_t smem = static_cast<size_t>(tab_rows) * sizeof(int4) + (hist ? static_cast<size_t>(C) * C * sizeof(unsigned int) : 0);
+        kern<<<grid, block, smem, st>>>(a, total_rows, r, col_blocks, tab_rows);
         return cudaSuccess;
     };
+    constexpr int kOutsFast = MODE == TSS_PL_UP_SOFTMAX ? kOutsPseudoLabel : kOutsRuntime;
     cudaError_t e;
-    if (coop && pl_outs && rows2 && tab_rows > 0)
+    if (hist && pl_outs)          // (a histogram only comes here when the cooperative form applies: see pseudo_label_impl)
+        e = go(pl_up_kernel<C, MODE, true, kOutsFast, 1, 0, true>);
+    else if (hist)
+        e = go(pl_up_kernel<C, MODE, true, kOutsRuntime, 1, 0, true>);
+    else if (coop && pl_outs && rows2 && tab_rows > 0)
         e = go(pl_up_kernel<C, MODE, true, MODE == TSS_PL_UP_SOFTMAX ? kOutsPseudoLabel : kOutsRuntime, 2>);
     else if (coop && pl_outs && regs96)
         e = go(pl_up_kernel<C <= 13 ? C : 13, MODE, true, MODE == TSS_PL_UP_SOFTMAX ? kOutsPseudoLabel : kOutsRuntime, 1, 1>);
@@ -731,11 +762,12 @@ static int launch_up(const PLArgs& a, int64_t n_img, int flags, cudaStream_t st)
 
 }  // namespace tss
 
-extern "C" int tss_pseudo_label(const float* src, const float* src_flip, int64_t n_img, int num_classes, int h, int w,
-                                int H, int W, int mode, int flip, uint8_t* label_out, uint16_t* conf16_out,
-                                float* conf32_out, uint8_t* label_thr_out, const float* thr_host,
-                                const uint8_t* keep_host, int ignore_index, int flags, void* stream) {
-    using namespace tss;
+namespace tss {
+static int pseudo_label_impl(const float* src, const float* src_flip, int64_t n_img, int num_classes, int h, int w,
+                             int H, int W, int mode, int flip, uint8_t* label_out, uint16_t* conf16_out,
+                             float* conf32_out, uint8_t* label_thr_out, const float* thr_host,
+                             const uint8_t* keep_host, int ignore_index, const uint8_t* gt, int64_t* hist, int flags,
+                             void* stream) {
     const int g_pl_force_tile = (flags & TSS_PL_FLAG_FORCE_TILE) ? 1 : 0;
     const int sm_warps = (flags >> 8) & 0xff;
     TSS_REQUIRE((flags >> 24) == 0 && flags >= 0 && (flags & 0xf8) == 0, TSS_E_ARG, "tss_pseudo_label: bad flags 0x%x", flags);
@@ -757,6 +789,8 @@ extern "C" int tss_pseudo_label(const float* src, const float* src_flip, int64_t
     a.conf16 = reinterpret_cast<__half*>(conf16_out);
     a.conf32 = conf32_out;
     a.label_thr = label_thr_out;
+    a.gt = nullptr;
+    a.hist = nullptr;
     a.C = num_classes; a.h = h; a.w = w; a.H = H; a.W = W;
     a.sy = scale_of(h, H);
     a.sx = scale_of(w, W);
@@ -766,6 +800,25 @@ extern "C" int tss_pseudo_label(const float* src, const float* src_flip, int64_t
     auto al = [](const void* p, uintptr_t m) { return p == nullptr || (reinterpret_cast<uintptr_t>(p) & (m - 1)) == 0; };
     a.vec_ok = (W % 4 == 0) && al(label_out, 4) && al(conf16_out, 8) && al(conf32_out, 16) && al(label_thr_out, 4);
     a.TY = 0; a.NR = 0;
+    if (hist != nullptr) {
+        // the confusion matrix: fused into the register-resident kernel where that one runs (cooperative row loads,
+        // per-CTA counts below 2^32), else the histogram kernel over the labels just written
+        const bool fast = !g_pl_force_tile && !(h == H && w == W) && flip == TSS_FLIP_NONE &&
+                          (mode == TSS_PL_UP_SOFTMAX || mode == TSS_PL_UP_ARGMAX) && (W % 2 == 0) && W >= 2 && al(label_out, 2) &&
+                          al(conf16_out, 4) && al(conf32_out, 8) && al(label_thr_out, 2) && al(gt, 2) &&
+                          (num_classes == 13 || num_classes == 19) && static_cast<int64_t>(num_classes) * h * w < (1ll << 30) &&
+                          (a.sx * 63.0f + 3.0f) < 32.0f && !(flags & (TSS_PL_FLAG_ROWS2 | TSS_PL_FLAG_REGS96)) &&
+                          n_img * static_cast<int64_t>(H) * W <= (1ll << 38);
+        if (!fast) {
+            TSS_REQUIRE(label_out != nullptr, TSS_E_ARG, "tss_pseudo_label_hist: this shape needs label_out for the histogram pass");
+            const int rc = pseudo_label_impl(src, src_flip, n_img, num_classes, h, w, H, W, mode, flip, label_out, conf16_out,
+                                             conf32_out, label_thr_out, thr_host, keep_host, ignore_index, nullptr, nullptr, flags, stream);
+            if (rc != TSS_OK) return rc;
+            return tss_confusion(label_out, gt, TSS_U8, n_img * static_cast<int64_t>(H) * W, num_classes, hist, nullptr, TSS_HIST_AUTO, stream);
+        }
+        a.gt = gt;
+        a.hist = reinterpret_cast<unsigned long long*>(hist);
+    }
 
     if (h == H && w == W && flip == TSS_FLIP_NONE && !g_pl_force_tile) {
         // full-resolution input: straight 128-bit loads, no staging
@@ -817,6 +870,26 @@ extern "C" int tss_pseudo_label(const float* src, const float* src_flip, int64_t
     if (num_classes <= 13) return launch_tile<13>(a, n_img, best_sm, st);
     if (num_classes <= 19) return launch_tile<19>(a, n_img, best_sm, st);
     return launch_tile<TSS_MAX_CLASSES>(a, n_img, best_sm, st);
+}
+}  // namespace tss
+
+extern "C" int tss_pseudo_label(const float* src, const float* src_flip, int64_t n_img, int num_classes, int h, int w,
+                                int H, int W, int mode, int flip, uint8_t* label_out, uint16_t* conf16_out,
+                                float* conf32_out, uint8_t* label_thr_out, const float* thr_host,
+                                const uint8_t* keep_host, int ignore_index, int flags, void* stream) {
+    return tss::pseudo_label_impl(src, src_flip, n_img, num_classes, h, w, H, W, mode, flip, label_out, conf16_out, conf32_out,
+                                  label_thr_out, thr_host, keep_host, ignore_index, nullptr, nullptr, flags, stream);
+}
+
+extern "C" int tss_pseudo_label_hist(const float* src, const float* src_flip, int64_t n_img, int num_classes, int h, int w,
+                                     int H, int W, int mode, int flip, uint8_t* label_out, uint16_t* conf16_out,
+                                     float* conf32_out, uint8_t* label_thr_out, const float* thr_host,
+                                     const uint8_t* keep_host, int ignore_index, const uint8_t* gt, int64_t* hist, int flags,
+                                     void* stream) {
+    using namespace tss;
+    TSS_REQUIRE(gt != nullptr && hist != nullptr, TSS_E_ARG, "tss_pseudo_label_hist: null gt / hist");
+    return pseudo_label_impl(src, src_flip, n_img, num_classes, h, w, H, W, mode, flip, label_out, conf16_out, conf32_out,
+                             label_thr_out, thr_host, keep_host, ignore_index, gt, hist, flags, stream);
 }
 
 extern "C" int tss_softmax_nchw(const float* logits, float* probs, int64_t n_img, int num_classes, int64_t plane,

@@ -248,8 +248,13 @@ def validate_batch(outputs: torch.Tensor, label: torch.Tensor, meter: ConfusionM
                    ignore_index: Optional[int] = None):
     """seg_validate's per-batch work (segmentation_evaluate.py:38-44) without leaving the device: bilinear
     upsample + argmax fused, histogram accumulated.  Returns (predictions uint8 [N,H,W], CE loss or None)."""
-    pl = ops.pseudo_label(outputs, size=size, mode=ops.PL_UP_ARGMAX, want_conf16=False)
-    meter.add(pl.label, label)
+    n = outputs.shape[0]
+    if isinstance(label, torch.Tensor) and label.is_cuda and label.dtype == torch.uint8 and label.numel() == n * size[0] * size[1]:
+        # uint8 ground truth already on the device: the matrix is accumulated inside the upsample + argmax kernel
+        pl = ops.pseudo_label(outputs, size=size, mode=ops.PL_UP_ARGMAX, want_conf16=False, gt=label.contiguous(), hist=meter.hist)
+    else:
+        pl = ops.pseudo_label(outputs, size=size, mode=ops.PL_UP_ARGMAX, want_conf16=False)
+        meter.add(pl.label, label)
     loss = None
     if ignore_index is not None:
         loss = ops.cross_entropy(ops.upsample_bilinear(outputs, size), label, ignore_index)

@@ -133,8 +133,11 @@ class PseudoLabels:
 def pseudo_label(src: torch.Tensor, size: Optional[Sequence[int]] = None, mode: int = PL_UP_SOFTMAX,
                  src_flip: Optional[torch.Tensor] = None, flip: int = FLIP_NONE, thr=None, keep=None,
                  ignore_index: int = 255, want_label: bool = True, want_conf16: bool = True,
-                 want_conf32: bool = False, want_thr: Optional[bool] = None, flags: int = 0) -> PseudoLabels:
-    """Fused upsample -> softmax -> argmax/confidence -> storage casts -> threshold (tss_pseudo_label)."""
+                 want_conf32: bool = False, want_thr: Optional[bool] = None, flags: int = 0,
+                 gt: Optional[torch.Tensor] = None, hist: Optional[torch.Tensor] = None) -> PseudoLabels:
+    """Fused upsample -> softmax -> argmax/confidence -> storage casts -> threshold (tss_pseudo_label).
+    With ``gt`` ([N,H,W] uint8) and ``hist`` ([C,C] int64, accumulated in place) the confusion matrix of (gt, label) is
+    taken in the same pass (tss_pseudo_label_hist)."""
     x = _dev(src, torch.float32, "src")
     if x.dim() != 4:
         raise ValueError("src must be [N,C,h,w]")
@@ -155,6 +158,21 @@ def pseudo_label(src: torch.Tensor, size: Optional[Sequence[int]] = None, mode: 
     conf32 = torch.empty((n, H, W), dtype=torch.float32, device=dev) if want_conf32 else None
     label_thr = torch.empty((n, H, W), dtype=torch.uint8, device=dev) if want_thr else None
     thr_arr, keep_arr = _host_tables(c, thr, keep)
+    if (gt is None) != (hist is None):
+        raise ValueError("gt and hist go together")
+    if gt is not None:
+        if gt.dtype != torch.uint8 or hist.dtype != torch.int64 or not hist.is_contiguous():
+            raise ValueError("gt must be uint8 and hist a contiguous int64 tensor (it is accumulated in place)")
+        g = _dev(gt, torch.uint8, "gt")
+        hh = _dev(hist, torch.int64, "hist")
+        if g.numel() != n * H * W or hh.numel() != c * c:
+            raise ValueError("gt must be [N,H,W] and hist [C,C]")
+        check(lib().tss_pseudo_label_hist(_ptr(x), _ptr(x2), n, c, h, w, H, W, mode, flip, _ptr(label), _ptr(conf16),
+                                          _ptr(conf32), _ptr(label_thr),
+                                          ctypes.cast(thr_arr, ctypes.c_void_p) if thr_arr is not None else None,
+                                          ctypes.cast(keep_arr, ctypes.c_void_p) if keep_arr is not None else None,
+                                          int(ignore_index), _ptr(g), _ptr(hh), int(flags), _stream()), "tss_pseudo_label_hist")
+        return PseudoLabels(label, conf16, conf32, label_thr)
     check(lib().tss_pseudo_label(_ptr(x), _ptr(x2), n, c, h, w, H, W, mode, flip, _ptr(label), _ptr(conf16),
                                  _ptr(conf32), _ptr(label_thr),
                                  ctypes.cast(thr_arr, ctypes.c_void_p) if thr_arr is not None else None,

@@ -87,6 +87,26 @@ def stage_pl_low(reps, N, C, h, w, H, W, tag, sm_warps=0, cta_warps=0, waves=0, 
            "XU/issue-bound (C ex2 per px), not HBM: see DESIGN.md section 4")
 
 
+def stage_pl_hist(reps, N, C, h, w, H, W, tag, fused, flags=0):
+    """pseudo-labels + confusion matrix: inside the pseudo-label kernel (fused) or as the separate histogram kernel"""
+    nb = 4 * N * C * h * w
+    sets = [(3.0 * torch.randn(N, C, h, w, generator=g(s), device=dev),
+             torch.randint(0, C, (N, H, W), generator=g(70 + s), device=dev, dtype=torch.int64).to(torch.uint8))
+            for s in range(copies_for(nb + 6 * N * H * W))]
+    hist = torch.zeros(C, C, dtype=torch.int64, device=dev)
+    thr, keep = 0.3, ((5, 11) if C == 13 else None)
+
+    def fn(x, gt):
+        if fused:
+            return ops.pseudo_label(x, size=(H, W), thr=thr, keep=keep, ignore_index=C - 1, flags=flags, gt=gt, hist=hist)
+        pl = ops.pseudo_label(x, size=(H, W), thr=thr, keep=keep, ignore_index=C - 1, flags=flags)
+        ops.confusion_matrix(pl.label.reshape(-1), gt.reshape(-1), C, hist)
+        return pl
+    med, mn = timed(fn, sets, reps)
+    report("pl_hist_%s_%s" % ("fused" if fused else "separate", tag), [N, C, h, w, H, W], med, mn, nb + N * H * W * 5, N * H * W,
+           1 if fused else 2, "pseudo-labels + confusion matrix")
+
+
 def stage_pl_argmax(reps, N, C, h, w, H, W, tag):
     nb = 4 * N * C * h * w
     sets = [(3.0 * torch.randn(N, C, h, w, generator=g(s), device=dev),) for s in range(copies_for(nb + 4 * N * H * W))]
@@ -335,6 +355,11 @@ STAGES = {
     "ov96_20_8_c4w2_plf": lambda r: stage_overlap(r, 20, 8, 4, 2, True, True, False, True),
     "ov96_20_4_c4w2_plf": lambda r: stage_overlap(r, 20, 4, 4, 2, True, True, False, True),
     "ov96_20_6_c5w2_plf": lambda r: stage_overlap(r, 20, 6, 5, 2, True, True, False, True),
+    "pl_hist_fused": lambda r: stage_pl_hist(r, 16, 13, 81, 241, 640, 1920, "cfg2", True),
+    "pl_hist_separate": lambda r: stage_pl_hist(r, 16, 13, 81, 241, 640, 1920, "cfg2", False),
+    "pl_hist_fused_co": lambda r: stage_pl_hist(r, 16, 13, 81, 241, 640, 1920, "cfg2_c4w2", True, ops.CORESIDENT_PL_FLAGS),
+    "pl_hist_fused_city": lambda r: stage_pl_hist(r, 4, 19, 129, 257, 1024, 2048, "city19", True),
+    "pl_hist_separate_city": lambda r: stage_pl_hist(r, 4, 19, 129, 257, 1024, 2048, "city19", False),
     "pl_argmax_cfg2": lambda r: stage_pl_argmax(r, 16, 13, 81, 241, 640, 1920, "cfg2"),
     "pl_c3w2": lambda r: stage_pl_low(r, 16, 13, 81, 241, 640, 1920, "cfg2_c3w2", 0, 3, 2),
     "overlap_cfg2_10_6": lambda r: stage_overlap(r, 10, 6),
