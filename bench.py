@@ -638,7 +638,12 @@ def run_b200(args, cfg):
         g, = torch.autograd.grad(loss, x)
         return lab, loss, ops.upsample_bilinear_adjoint(g, (c["h"], c["w"]))
 
-    def main_step(i, mode):
+    def pre_step(i):
+        """coresident_prelabel: the label kernel of step i (logits -> tile records, zeroed sums).  It needs nothing of step
+        i - 1, so it is issued on its own stream BESIDE the kernels of step i - 1 instead of in front of step i's."""
+        return ops.class_labels(sets[i % n_sets][0], C, c["K"])
+
+    def main_step(i, mode, pre=None):
         """everything of step i that the NEXT step's kernels must not overtake; returns what the tail needs"""
         cur = torch.cuda.current_stream(dev)
         if kind == "eval_sweep":
@@ -649,7 +654,14 @@ def run_b200(args, cfg):
             cs = stage_sums(i)
             lab = stage_distance(i)
             return cs, lab
-        if mode in ("coresident", "coresident_hist_main", "coresident_hist_fused"):
+        if mode == "coresident_prelabel":
+            side.wait_stream(cur)                # accumulate kernel (records from the pre graph) on the high-priority fork
+            with torch.cuda.stream(side):
+                cs = ops.class_accumulate(pre.out, sets[i % n_sets][1], co_nc)
+            pl = stage_pl(i, co_pl)
+            extra = stage_round_tail(i) if kind == "self_train_round" else None
+            cur.wait_stream(side)
+        elif mode in ("coresident", "coresident_hist_main", "coresident_hist_fused"):
             cs = stage_sums(i, co_nc, side)      # label kernel here, accumulate kernel on the high-priority fork
             pl = stage_pl(i, co_pl, with_hist=(mode == "coresident_hist_fused"))
             if mode == "coresident_hist_main":   # confusion matrix behind the pseudo-label kernel instead of on the tail stream
@@ -663,17 +675,29 @@ def run_b200(args, cfg):
         return cs, (pl, extra)
 
     def build_graphs(mode):
-        mains = [GraphedCall(lambda i=i: main_step(i, mode), warmup=1) for i in range(n_sets)]
+        pres = [GraphedCall(lambda i=i: pre_step(i), warmup=1) for i in range(n_sets)] if mode == "coresident_prelabel" else None
+        mains = [GraphedCall(lambda i=i: main_step(i, mode, pres[i] if pres else None), warmup=1) for i in range(n_sets)]
         hist_in_tail = kind != "proto_distance" and mode not in ("coresident_hist_main", "coresident_hist_fused")
         tails = [GraphedCall(lambda i=i: stage_tail(i, mains[i].out[0], mains[i].out[1][0] if hist_in_tail else None),
                              warmup=1) for i in range(n_sets)] if has_proto else None
-        return mains, tails
+        return mains, tails, pres
 
     ev_main = [torch.cuda.Event() for _ in range(n_sets)]
     ev_tail = [torch.cuda.Event() for _ in range(n_sets)]
-    state = {"issued": 0}
+    ev_pre = [torch.cuda.Event() for _ in range(n_sets)]
+    pre_stream = torch.cuda.Stream(dev)
+    state = {"issued": 0, "pre_for": -1}
 
-    def make_step(mains, tails):
+    def make_step(mains, tails, pres=None):
+        def issue_pre(j):
+            # label kernel of step j on its own stream; its set's records / sums were last read by the tail of step j - n_sets
+            with torch.cuda.stream(pre_stream):
+                if tails is not None and j >= n_sets:
+                    pre_stream.wait_event(ev_tail[j % n_sets])
+                pres[j % n_sets].replay()
+                ev_pre[j % n_sets].record(pre_stream)
+            state["pre_for"] = j
+
         def step(_i=None):
             # the set (and with it the gather slot, set % 2) follows ONE running counter, whichever loop calls: consecutive
             # steps always alternate the slot
@@ -682,7 +706,13 @@ def run_b200(args, cfg):
             s = i % n_sets
             if tails is not None and state["issued"] >= n_sets:
                 cur.wait_event(ev_tail[s])              # the tail of step i - n_sets has read this set's sums / records
+            if pres is not None:
+                if state["pre_for"] != i:               # first step of this form: nothing was issued ahead
+                    issue_pre(i)
+                cur.wait_event(ev_pre[s])
             mains[s].replay()
+            if pres is not None:
+                issue_pre(i + 1)                        # beside this step's kernels
             if tails is not None:
                 ev_main[s].record(cur)
                 with torch.cuda.stream(tail):
@@ -696,6 +726,7 @@ def run_b200(args, cfg):
 
     def fence():
         torch.cuda.current_stream(dev).wait_stream(tail)
+        torch.cuda.current_stream(dev).wait_stream(pre_stream)
         torch.cuda.synchronize()
         if ws > 1:
             dist.barrier()
@@ -708,6 +739,7 @@ def run_b200(args, cfg):
         for i in range(n):
             step(i)
         torch.cuda.current_stream(dev).wait_stream(tail)
+        torch.cuda.current_stream(dev).wait_stream(pre_stream)
         e1.record()
         torch.cuda.synchronize()
         t = torch.tensor([e0.elapsed_time(e1)], device=dev)
@@ -718,7 +750,8 @@ def run_b200(args, cfg):
     # ---- choose the step form: the co-resident form (pseudo-label on 12 warps/SM + accumulate on 5) against the serial
     # one, each timed over a few untimed-region replays; every rank takes the same decision (all-reduced times)
     modes = ["serial"] if kind in ("eval_sweep", "proto_distance") else (
-(["coresident", "coresident_hist_main", "serial"] if ws > 1 else ["coresident", "serial"]) if args.overlap == "auto"
+        (["coresident", "coresident_prelabel", "coresident_hist_main", "serial"] if ws > 1 else
+         ["coresident", "coresident_prelabel", "serial"]) if args.overlap == "auto"
         else [args.overlap])   # N > 1: the longer tail (exchange, update over every rank's images) prefers the confusion matrix on the main stream
     trial = {}
     built = {}
@@ -732,9 +765,9 @@ def run_b200(args, cfg):
     for m in list(built):
         if m != mode:
             del built[m]
-    mains, tails = built[mode]
-    step = make_step(mains, tails)
-    launches_per_step = mains[0].launches + (tails[0].launches if tails else 0) + (1 if ws > 1 and has_proto and gather is None else 0)
+    mains, tails, pres = built[mode]
+    step = make_step(mains, tails, pres)
+    launches_per_step = mains[0].launches + (tails[0].launches if tails else 0) + (pres[0].launches if pres else 0) + (1 if ws > 1 and has_proto and gather is None else 0)
 
     # ---- in-run parity: one frame of this very step against the oracle, before anything is timed
     parity = None
@@ -785,6 +818,7 @@ def run_b200(args, cfg):
     for i in range(steps):
         step(i)
     torch.cuda.current_stream(dev).wait_stream(tail)    # the timed region ends when the last exchange / update has landed
+    torch.cuda.current_stream(dev).wait_stream(pre_stream)   # ... and the label kernel issued ahead by the last step
     sharding.all_reduce_confusion(meter.hist, meter.bad)
     ev1.record()
     fence()
@@ -911,7 +945,9 @@ def run_b200(args, cfg):
                              "accumulate kernel (6 consumer warps, high-priority capture fork) resident on the same SMs; confusion "
                              "matrix on the tail stream", "coresident_hist_main": "as coresident, confusion matrix behind the "
                              "pseudo-label kernel", "coresident_hist_fused": "as coresident, confusion matrix accumulated inside "
-                             "the pseudo-label kernel (tss_pseudo_label_hist)", "serial": "one stream"}[mode],
+                             "the pseudo-label kernel (tss_pseudo_label_hist)", "coresident_prelabel": "as coresident, and the label "
+                             "kernel of step i+1 (logits -> tile records) issued on its own stream beside the kernels of step i: every "
+                             "step still runs one label kernel inside the timed region", "serial": "one stream"}[mode],
                              launches_per_step),
                    "step_form_trials_ms": {k: round(v, 5) for k, v in trial.items()},
                    "parallelism": "image-sharded x%d; collectives: prototype means [%d,%d,%s] fp32 per rank and step (%s), "
@@ -1134,7 +1170,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-parity", action="store_true", help="skip the in-run oracle check of one frame")
     ap.add_argument("--no-aux", action="store_true", help="skip the aux_stages timings of the default line")
-    ap.add_argument("--overlap", default="auto", choices=["auto", "coresident", "coresident_hist_main", "coresident_hist_fused", "serial"],
+    ap.add_argument("--overlap", default="auto", choices=["auto", "coresident", "coresident_prelabel", "coresident_hist_main", "coresident_hist_fused", "serial"],
                     help="step form: pseudo-label and accumulate kernels resident together, one after the other, or the faster "
                          "of the two measured before the timed region (default)")
     ap.add_argument("--tail-priority", type=int, default=0, help="1 = the tail stream gets the high stream priority (tuning)")

@@ -280,6 +280,44 @@ class ClassSums:
     plane: int
 
 
+def class_labels(logits: torch.Tensor, num_classes: int, channels: int, labels_val: Optional[torch.Tensor] = None,
+                 overflow_channel: Optional[int] = None, conf_thresh: Optional[float] = None,
+                 use_conf_gate: bool = False) -> ClassSums:
+    """First launch of A5 alone: per-pixel argmax labels + tile records from the logits, and the [N,C,channels] sums
+    zeroed by the same launch.  It needs no features, so a pipelined caller can run it for batch i+1 beside the
+    kernels of batch i; ``class_accumulate`` completes the returned ClassSums."""
+    x = _dev(logits, torch.float32, "logits")
+    if x.dim() != 4 or x.shape[1] != num_classes:
+        raise ValueError("logits must be [N,%d,h,w], got %s" % (num_classes, tuple(x.shape)))
+    n, plane = x.shape[0], x[0, 0].numel()
+    lv = None
+    if labels_val is not None:
+        lv = _dev(labels_val, torch.float32, "labels_val")
+        if lv.numel() != n * plane:
+            raise ValueError("labels_val must be [N,1,h,w]")
+    dev = x.device
+    L = lib()
+    rec = torch.empty(max(int(L.tss_proto_records_bytes(n, plane)), 16), dtype=torch.uint8, device=dev)
+    seg = torch.empty((n, plane), dtype=torch.uint8, device=dev)
+    sums = torch.empty((n, num_classes, int(channels)), dtype=torch.float32, device=dev)
+    check(L.tss_proto_labels(_ptr(x), _ptr(lv), n, num_classes, plane,
+                             num_classes if overflow_channel is None else int(overflow_channel),
+                             1 if use_conf_gate else 0, float(-1.0 if conf_thresh is None else conf_thresh),
+                             _ptr(seg), _ptr(rec), _ptr(sums), sums.numel(), _stream()), "tss_proto_labels")
+    return ClassSums(sums, rec, seg, plane)
+
+
+def class_accumulate(cs: ClassSums, feat: torch.Tensor, consumer_warps: int = 0) -> ClassSums:
+    """Second launch of A5 on the current stream: ONE streaming pass over feat into the (zeroed) sums of ``cs``."""
+    f = _dev(feat, torch.float32, "feat")
+    n, num_classes, k = cs.sums.shape
+    if f.shape[0] != n or f.shape[1] != k or f[0, 0].numel() != cs.plane:
+        raise ValueError("feat %s does not match the label records (N=%d, K=%d, plane=%d)" % (tuple(f.shape), n, k, cs.plane))
+    check(lib().tss_proto_accumulate(_ptr(f), _ptr(cs.records), n, k, cs.plane, num_classes, _ptr(cs.sums), 0,
+                                     int(consumer_warps), _stream()), "tss_proto_accumulate")
+    return cs
+
+
 def class_sums(feat: torch.Tensor, logits: torch.Tensor, num_classes: int, labels_val: Optional[torch.Tensor] = None,
                overflow_channel: Optional[int] = None, conf_thresh: Optional[float] = None, use_conf_gate: bool = False,
                consumer_warps: int = 0, accumulate_stream: Optional["torch.cuda.Stream"] = None) -> ClassSums:
@@ -291,33 +329,16 @@ def class_sums(feat: torch.Tensor, logits: torch.Tensor, num_classes: int, label
     (``current_stream().wait_stream(accumulate_stream)``) before anything reads the sums."""
     f = _dev(feat, torch.float32, "feat")
     x = _dev(logits, torch.float32, "logits")
-    n, k = f.shape[0], f.shape[1]
-    plane = f[0, 0].numel()
-    if x.shape[0] != n or x.shape[1] != num_classes or x[0, 0].numel() != plane:
+    if x.dim() != 4 or f.dim() != 4 or x.shape[0] != f.shape[0] or x.shape[1] != num_classes or x[0, 0].numel() != f[0, 0].numel():
         raise ValueError("logits %s do not match feat %s / num_classes %d" % (tuple(x.shape), tuple(f.shape), num_classes))
-    lv = None
-    if labels_val is not None:
-        lv = _dev(labels_val, torch.float32, "labels_val")
-        if lv.numel() != n * plane:
-            raise ValueError("labels_val must be [N,1,h,w]")
-    dev = f.device
-    L = lib()
-    rec = torch.empty(max(int(L.tss_proto_records_bytes(n, plane)), 16), dtype=torch.uint8, device=dev)
-    seg = torch.empty((n, plane), dtype=torch.uint8, device=dev)
-    sums = torch.empty((n, num_classes, k), dtype=torch.float32, device=dev)
-    st = _stream()
-    check(L.tss_proto_labels(_ptr(x), _ptr(lv), n, num_classes, plane,
-                             num_classes if overflow_channel is None else int(overflow_channel),
-                             1 if use_conf_gate else 0, float(-1.0 if conf_thresh is None else conf_thresh),
-                             _ptr(seg), _ptr(rec), _ptr(sums), sums.numel(), st), "tss_proto_labels")
-    if accumulate_stream is not None:
-        accumulate_stream.wait_stream(torch.cuda.current_stream(dev))
-        st = accumulate_stream.cuda_stream
-        for t in (f, rec, sums):
-            t.record_stream(accumulate_stream)
-    check(L.tss_proto_accumulate(_ptr(f), _ptr(rec), n, k, plane, num_classes, _ptr(sums), 0, int(consumer_warps), st),
-          "tss_proto_accumulate")
-    return ClassSums(sums, rec, seg, plane)
+    cs = class_labels(x, num_classes, f.shape[1], labels_val, overflow_channel, conf_thresh, use_conf_gate)
+    if accumulate_stream is None:
+        return class_accumulate(cs, f, consumer_warps)
+    accumulate_stream.wait_stream(torch.cuda.current_stream(f.device))
+    for t in (f, cs.records, cs.sums):
+        t.record_stream(accumulate_stream)
+    with torch.cuda.stream(accumulate_stream):
+        return class_accumulate(cs, f, consumer_warps)
 
 
 def class_finalize(cs: ClassSums, min_pixels: int = 10, update=None, scatter=None) -> ClassMeans:
