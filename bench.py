@@ -760,7 +760,9 @@ def run_b200(args, cfg):
         st = make_step(*built[m])
         for i in range(2 * n_sets):      # consecutive steps must alternate the gather slot: always whole rounds of the sets
             st(i)
-        trial[m] = time_steps(st, 3 * n_sets)
+        # N > 1: the ranks enter a trial with some skew and the exchange barrier turns it into step time, so the trials are
+        # longer there (and the better of two counts) -- a 12-step trial could not tell forms 10 us apart
+        trial[m] = time_steps(st, 3 * n_sets) if ws == 1 else min(time_steps(st, 12 * n_sets), time_steps(st, 12 * n_sets))
     mode = min(trial, key=trial.get)
     for m in list(built):
         if m != mode:
