@@ -686,7 +686,16 @@ def run_b200(args, cfg):
     ev_tail = [torch.cuda.Event() for _ in range(n_sets)]
     ev_pre = [torch.cuda.Event() for _ in range(n_sets)]
     pre_stream = torch.cuda.Stream(dev)
+    # --main-streams 2: consecutive steps' kernel graphs alternate between two streams, so that step i+1's kernels fill the
+    # SMs while step i's last CTAs drain (steps read different input sets; the prototype bank is updated in order on the
+    # tail stream either way)
+    main_streams = [torch.cuda.Stream(dev) for _ in range(args.main_streams)] if args.main_streams > 1 else []
     state = {"issued": 0, "pre_for": -1}
+
+    def join_all():
+        cur = torch.cuda.current_stream(dev)
+        for st_ in [tail, pre_stream] + main_streams:
+            cur.wait_stream(st_)
 
     def make_step(mains, tails, pres=None):
         def issue_pre(j):
@@ -702,7 +711,15 @@ def run_b200(args, cfg):
             # the set (and with it the gather slot, set % 2) follows ONE running counter, whichever loop calls: consecutive
             # steps always alternate the slot
             i = state["issued"]
-            cur = torch.cuda.current_stream(dev)
+            if main_streams:
+                cur = main_streams[i % len(main_streams)]
+                with torch.cuda.stream(cur):
+                    step_on(cur, i)
+            else:                                        # (no stream context: cfg1's 22 us steps are bound by host launch time)
+                step_on(torch.cuda.current_stream(dev), i)
+            state["issued"] += 1
+
+        def step_on(cur, i):
             s = i % n_sets
             if tails is not None and state["issued"] >= n_sets:
                 cur.wait_event(ev_tail[s])              # the tail of step i - n_sets has read this set's sums / records
@@ -721,12 +738,10 @@ def run_b200(args, cfg):
                     if ws > 1 and gather is None:
                         bank.update_gathered(means)
                     ev_tail[s].record(tail)
-            state["issued"] += 1
         return step
 
     def fence():
-        torch.cuda.current_stream(dev).wait_stream(tail)
-        torch.cuda.current_stream(dev).wait_stream(pre_stream)
+        join_all()
         torch.cuda.synchronize()
         if ws > 1:
             dist.barrier()
@@ -738,8 +753,7 @@ def run_b200(args, cfg):
         e0.record()
         for i in range(n):
             step(i)
-        torch.cuda.current_stream(dev).wait_stream(tail)
-        torch.cuda.current_stream(dev).wait_stream(pre_stream)
+        join_all()
         e1.record()
         torch.cuda.synchronize()
         t = torch.tensor([e0.elapsed_time(e1)], device=dev)
@@ -819,8 +833,7 @@ def run_b200(args, cfg):
     ev0.record()
     for i in range(steps):
         step(i)
-    torch.cuda.current_stream(dev).wait_stream(tail)    # the timed region ends when the last exchange / update has landed
-    torch.cuda.current_stream(dev).wait_stream(pre_stream)   # ... and the label kernel issued ahead by the last step
+    join_all()    # the timed region ends when the last exchange / update has landed (and the label kernel issued ahead by the last step)
     sharding.all_reduce_confusion(meter.hist, meter.bad)
     ev1.record()
     fence()
@@ -1175,6 +1188,7 @@ def main():
     ap.add_argument("--overlap", default="auto", choices=["auto", "coresident", "coresident_prelabel", "coresident_hist_main", "coresident_hist_fused", "serial"],
                     help="step form: pseudo-label and accumulate kernels resident together, one after the other, or the faster "
                          "of the two measured before the timed region (default)")
+    ap.add_argument("--main-streams", type=int, default=1, help="2 = consecutive steps' kernel graphs alternate between two streams (tuning)")
     ap.add_argument("--tail-priority", type=int, default=0, help="1 = the tail stream gets the high stream priority (tuning)")
     ap.add_argument("--coresident", default="", help="sm_warps,cta_warps,waves,consumer_warps of the co-resident form (tuning)")
     ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
