@@ -785,6 +785,82 @@ def run_b200(args, cfg):
     step = make_step(mains, tails, pres)
     launches_per_step = mains[0].launches + (tails[0].launches if tails else 0) + (pres[0].launches if pres else 0) + (1 if ws > 1 and has_proto and gather is None else 0)
 
+    # ---- G consecutive steps as ONE graph (--steps-per-graph): the same kernels with the same dependencies -- label kernel
+    # of step j+1 beside step j, accumulate fork, tail stream -- captured once for G steps, so that the host issues one
+    # launch per G steps instead of three graph launches and six event calls per step.  Built to test whether the step loop
+    # at N = 8 (0.18 ms/step in every form, 0.154 at N = 1) is bound by host launch work: it is not (see below).
+    class _Held:
+        def __init__(self, out):
+            self.out = out
+
+    def capture_block(G):
+        keep = []
+        hist_in_tail = mode not in ("coresident_hist_main", "coresident_hist_fused")
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            cur = torch.cuda.current_stream(dev)
+            pre_j, ev_pre_j = None, None
+
+            def fork_pre(j):
+                pre_stream.wait_stream(cur)
+                with torch.cuda.stream(pre_stream):
+                    held = _Held(pre_step(j))
+                    ev = torch.cuda.Event()
+                    ev.record(pre_stream)
+                keep.append(held)
+                return held, ev
+            if mode == "coresident_prelabel":
+                pre_j, ev_pre_j = fork_pre(0)
+            for j in range(G):
+                if mode == "coresident_prelabel":
+                    cur.wait_event(ev_pre_j)
+                    this_pre = pre_j
+                    if j + 1 < G:
+                        pre_j, ev_pre_j = fork_pre(j + 1)     # beside step j's kernels
+                    cs, rest = main_step(j, mode, this_pre)
+                else:
+                    cs, rest = main_step(j, mode)
+                keep.append((cs, rest))
+                ev = torch.cuda.Event()
+                ev.record(cur)
+                with torch.cuda.stream(tail):
+                    tail.wait_event(ev)
+                    keep.append(stage_tail(j, cs, rest[0] if hist_in_tail else None))
+            for st_ in ((tail, pre_stream) if mode == "coresident_prelabel" else (tail,)):
+                cur.wait_stream(st_)          # every stream that joined the capture returns to it
+        return g, keep
+
+    block = {"graph": None, "G": 0}
+
+    def run_steps(n):
+        """issue exactly n steps: whole blocks where a block graph exists (they start on an even step: the gather slot
+        alternates with the step index), single steps otherwise"""
+        done = 0
+        while done < n:
+            G = block["G"]
+            if block["graph"] is not None and n - done >= G and state["issued"] % 2 == 0:
+                join_all()                       # after whatever single steps left on the tail / label streams
+                block["graph"].replay()
+                state["issued"] += G
+                state["pre_for"] = -1
+                done += G
+            else:
+                step()
+                done += 1
+
+    def time_run(n):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        fence()
+        e0.record()
+        run_steps(n)
+        join_all()
+        e1.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if ws > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item()) / n
+
     # ---- in-run parity: one frame of this very step against the oracle, before anything is timed
     parity = None
     if rank == 0 and not args.no_parity:
@@ -820,6 +896,23 @@ def run_b200(args, cfg):
     for i in range(((warm + n_sets - 1) // n_sets) * n_sets):
         step(i)
     fence()
+    block_trial = None
+    want_G = args.steps_per_graph
+    # (measured: 0.163 vs 0.153 ms at N = 1, 0.166 vs 0.166 at N = 2, 0.183 vs 0.180 at N = 8 -- the host keeps up with one graph
+    # per step at every N, so the default stays 1; 0 = time both and keep the faster)
+    if kind == "label_step" and has_proto and mode != "serial" and not (ws > 1 and gather is None) and want_G != 1:
+        G = want_G if want_G > 1 else 8
+        G -= G % 2
+        n_try = 6 * G
+        t_single = min(time_run(n_try), time_run(n_try))
+        block["graph"], block["keep"] = capture_block(G)
+        block["G"] = G
+        run_steps(2 * G)
+        t_block = min(time_run(n_try), time_run(n_try))
+        block_trial = {"steps_per_graph": G, "single_ms": round(t_single, 5), "block_ms": round(t_block, 5)}
+        if want_G <= 1 and t_block >= t_single:          # automatic: keep the blocks only where they are faster
+            block["graph"], block["G"] = None, 0
+        fence()
 
     # ---- device-resident timed region
     sampler = ClockSampler(local_rank) if rank == 0 else None
@@ -831,8 +924,7 @@ def run_b200(args, cfg):
     fence()
     t_wall0 = time.perf_counter()
     ev0.record()
-    for i in range(steps):
-        step(i)
+    run_steps(steps)
     join_all()    # the timed region ends when the last exchange / update has landed (and the label kernel issued ahead by the last step)
     sharding.all_reduce_confusion(meter.hist, meter.bad)
     ev1.record()
@@ -955,7 +1047,9 @@ def run_b200(args, cfg):
         "config": {"workload": workload_name(c), "frames_per_gpu_per_step": frames,
                    "l2": "inputs rotate over %d resident sets (working set %d MB > 126 MB L2)" % (
                        n_sets, n_sets * sum(t.numel() * t.element_size() for t in sets[0]) // 2 ** 20),
-                   "launch": "one CUDA-graph replay per step for the kernels (%s form: %s) + one for the prototype tail on its own "
+                   "launch": ("ONE CUDA-graph replay per %d consecutive steps (kernels, label-ahead and tail streams captured with their "
+                              "dependencies; leftover steps as below); per step: " % block["G"] if block["graph"] is not None else "") +
+                             "one CUDA-graph replay per step for the kernels (%s form: %s) + one for the prototype tail on its own "
                              "stream, %d kernels per step" % (mode, {"coresident": "pseudo-label kernel in 4-warp CTAs, two waves, and the "
                              "accumulate kernel (6 consumer warps, high-priority capture fork) resident on the same SMs; confusion "
                              "matrix on the tail stream", "coresident_hist_main": "as coresident, confusion matrix behind the "
@@ -965,6 +1059,7 @@ def run_b200(args, cfg):
                              "step still runs one label kernel inside the timed region", "serial": "one stream"}[mode],
                              launches_per_step),
                    "step_form_trials_ms": {k: round(v, 5) for k, v in trial.items()},
+                   "steps_per_graph": block["G"] if block["graph"] is not None else 1, "steps_per_graph_trial": block_trial,
                    "parallelism": "image-sharded x%d; collectives: prototype means [%d,%d,%s] fp32 per rank and step (%s), "
                                   "confusion [%d,%d] int64 once" % (ws, frames, C, c.get("K", "-"), exchange, C, C),
                    "miou": miou, "bank_max_spread_over_ranks": bank_spread, "bank_vs_sequential_rel": bank_vs_seq,
@@ -1188,6 +1283,9 @@ def main():
     ap.add_argument("--overlap", default="auto", choices=["auto", "coresident", "coresident_prelabel", "coresident_hist_main", "coresident_hist_fused", "serial"],
                     help="step form: pseudo-label and accumulate kernels resident together, one after the other, or the faster "
                          "of the two measured before the timed region (default)")
+    ap.add_argument("--steps-per-graph", type=int, default=1,
+                    help="G > 1: G consecutive steps are captured as one graph (same kernels and dependencies, one host launch per G "
+                         "steps); 1 (default): one graph per step; 0: both are timed before the timed region and the faster is used")
     ap.add_argument("--main-streams", type=int, default=1, help="2 = consecutive steps' kernel graphs alternate between two streams (tuning)")
     ap.add_argument("--tail-priority", type=int, default=0, help="1 = the tail stream gets the high stream priority (tuning)")
     ap.add_argument("--coresident", default="", help="sm_warps,cta_warps,waves,consumer_warps of the co-resident form (tuning)")
