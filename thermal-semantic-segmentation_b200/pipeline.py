@@ -2,9 +2,10 @@
 segmentation_evaluate.py:38-44,77-79 for batches that live in HOST memory.
 
 The reference moves every batch H2D, runs the label math, and copies every prediction back before the next
-batch starts.  Here five streams overlap the legs of consecutive batches: batch i+1 is uploaded (copy engine,
+batch starts.  Here six streams overlap the legs of consecutive batches: batch i+1 is uploaded (copy engine,
 pinned buffers) while batch i runs through the kernels and batch i-1's labels drain to pinned host memory, with
-two device-side input slots and two host-side output slots.  Inside a batch the XU-bound pseudo-label kernel and
+two device-side input slots and two host-side output slots; the label kernel of a batch (it needs only the logits)
+starts as soon as they are up, while the features still upload and the previous batch's kernels run.  Inside a batch the XU-bound pseudo-label kernel and
 the HBM-bound accumulate kernel share the SMs (two streams, co-resident CTAs), and the latency-bound end of the
 prototype stage -- means, the exchange between GPUs when the batch is image-sharded, the sequential update -- runs
 on a tail stream beside the next batch.  Per batch the PCIe transfer (4*(C+K)*h*w bytes in per frame) is the
@@ -42,6 +43,7 @@ class HostLabelPipeline:
         self.meter = dropin.ConfusionMeter(self.C, self.dev)
         self.s_in, self.s_out = torch.cuda.Stream(self.dev), torch.cuda.Stream(self.dev)
         self.s_side, self.s_tail = torch.cuda.Stream(self.dev, priority=-1), torch.cuda.Stream(self.dev)
+        self.s_pre = torch.cuda.Stream(self.dev)    # label kernel of a batch: as soon as its logits are up, beside the previous batch
         self._in = [None] * self.SLOTS          # device input slots (allocated at first submit)
         self._ready = [torch.cuda.Event() for _ in range(self.SLOTS)]
         self._free = [torch.cuda.Event() for _ in range(self.SLOTS)]
@@ -73,15 +75,29 @@ class HostLabelPipeline:
             if i >= self.SLOTS:
                 self.s_in.wait_event(self._free[s])       # batch i-2 no longer reads this slot
             d_logits.copy_(logits, non_blocking=True)
+            logits_up = torch.cuda.Event()
+            logits_up.record(self.s_in)
             d_feat.copy_(feat, non_blocking=True)
             if gt is not None:
                 d_gt.copy_(gt, non_blocking=True)
             self._ready[s].record(self.s_in)
         cur.wait_event(self._ready[s])
         if self.overlap:
+            # the label kernel needs only the logits (16 MB of the 356 MB of a cfg2 batch): it runs on its own stream while the
+            # features are still uploading and the previous batch's kernels run
+            with torch.cuda.stream(self.s_pre):
+                self.s_pre.wait_event(logits_up)
+                cs = ops.class_labels(d_logits, self.C, self.K, overflow_channel=self.C)
+                labelled = torch.cuda.Event()
+                labelled.record(self.s_pre)
+            for t in (cs.sums, cs.records, cs.seg_label):
+                t.record_stream(cur)
+                t.record_stream(self.s_side)
             # pseudo-labels (XU / issue bound) and the segmented sums (HBM bound) on the same SMs at the same time
-            cs = ops.class_sums(d_feat, d_logits, self.C, overflow_channel=self.C, consumer_warps=ops.CORESIDENT_CONSUMERS,
-                                accumulate_stream=self.s_side)
+            self.s_side.wait_event(labelled)
+            self.s_side.wait_event(self._ready[s])
+            with torch.cuda.stream(self.s_side):
+                ops.class_accumulate(cs, d_feat, ops.CORESIDENT_CONSUMERS)
             pl = ops.pseudo_label(d_logits, size=self.size, thr=self.thr, keep=self.keep, ignore_index=self.ignore,
                                   flags=ops.CORESIDENT_PL_FLAGS)
             if gt is not None:
