@@ -49,6 +49,20 @@ def test_argument_rejection_needs_no_gpu():
     assert L.tss_confusion(p, p, 7, 10, 13, p, None, 0, None) == 1                   # bad dtype
     assert L.tss_proto_accumulate(p, p, 1, 33, 10, 13, p, 1, 0, None) == 1              # channels % 32
     assert L.tss_confusion(p, p, 0, 0, 13, p, None, 0, None) == 0                    # empty input is a no-op
+    # fused pseudo-label + confusion matrix: gt and hist are required, flags are validated
+    assert L.tss_pseudo_label_hist(p, None, 1, 13, 4, 4, 8, 8, 0, 0, p, None, None, None, None, None, 12, None, p, 0, None) == 1
+    assert b"gt" in L.tss_last_error_string()
+    assert L.tss_pseudo_label_hist(p, None, 1, 13, 4, 4, 8, 8, 0, 0, p, None, None, None, None, None, 12, p, p, 0x80, None) == 1
+    assert L.tss_pseudo_label_hist(p, None, 0, 13, 4, 4, 8, 8, 0, 0, p, None, None, None, None, None, 12, p, p, 0, None) == 0   # no images
+    # the no-allocation class-mean entry: rejected before any CUDA call -- null pointer, channels % 32, a batch whose
+    # scratch exceeds the built-in 4 MiB array; an empty batch is a no-op
+    args = (p, p, p, p, p)
+    assert L.tss_class_means_noalloc(None, p, 1, 13, 256, 100, 10, *args, None) == 1
+    assert L.tss_class_means_noalloc(p, p, 1, 13, 48, 100, 10, *args, None) == 1
+    assert L.tss_class_means_noalloc(p, p, 1, 99, 256, 100, 10, *args, None) == 2
+    assert L.tss_class_means_noalloc(p, p, 48, 13, 256, 81 * 241, 10, *args, None) == 1
+    assert b"scratch" in L.tss_last_error_string() and str(4 << 20).encode() in L.tss_last_error_string()
+    assert L.tss_class_means_noalloc(p, p, 0, 13, 256, 100, 10, *args, None) == 0
 
 
 def test_cpu_tensors_are_refused():
