@@ -10,7 +10,9 @@ Default workload (BASELINE.json configs[1], "cfg2"): one STEP = one batch of 16 
     1. fused bilinear upsample -> softmax -> argmax/confidence -> fp16 cast -> class-wise threshold + whitelist
        (uint8 label, fp16 confidence, thresholded uint8 label at 640x1920)            [XU / issue bound]
     2. argmax label + per-(image, class) segmented feature sums                        [HBM bound]
-       -- 1 and 2 run AT THE SAME TIME on every SM (two capture streams, co-resident CTAs) --
+       -- 1 and 2 run AT THE SAME TIME on every SM (two capture streams, co-resident CTAs); the label kernel of 2 needs
+          only the logits, so the one of step i+1 is issued on its own stream beside step i (`coresident_prelabel`; each
+          timed step still runs one, and the timed region waits for the one its last step issued) --
     3. confusion-matrix accumulation of the labels against a uint8 ground-truth map (mIoU at the end),
     4. means + sequential prototype update (+ the exchange between GPUs) on a tail stream, beside the next step.
 
